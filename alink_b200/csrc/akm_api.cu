@@ -1,0 +1,719 @@
+// C ABI of libakm (include/akm.h): handle management and the host-side sequencing of the
+// per-partition work Alink's ComQueue stages perform (KMeansAssignCluster, AllReduce,
+// KMeansUpdateCentroids, KMeansIterTermination, KMeansOutputModel, KMeansModelMapper.map).
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+#include "akm_internal.cuh"
+
+static thread_local std::string g_tls_error;
+
+void akm_set_tls_error(const std::string &s) { g_tls_error = s; }
+
+int akm_fail(akm_handle h, int code, const std::string &msg) {
+    if (h) h->err = msg;
+    g_tls_error = msg;
+    return code;
+}
+
+#define REQUIRE(h, cond, msg) \
+    do { if (!(cond)) return akm_fail((h), AKM_ERR_BADARG, (msg)); } while (0)
+
+static int bind_device(akm_handle h) {
+    if (!h) return akm_fail(nullptr, AKM_ERR_BADARG, "null handle");
+    AKM_CUDA(h, cudaSetDevice(h->device));
+    return AKM_OK;
+}
+
+template <typename T>
+static int dev_alloc(akm_handle h, T **p, size_t count) {
+    *p = nullptr;
+    if (count == 0) count = 1;
+    AKM_CUDA(h, cudaMalloc((void **)p, count * sizeof(T)));
+    return AKM_OK;
+}
+
+template <typename T>
+static void dev_free(T *&p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+static void rowstore_free(RowStore &rs) {
+    dev_free(rs.x32); dev_free(rs.x64); dev_free(rs.xlabel); dev_free(rs.x16); dev_free(rs.xerr);
+    rs.n = rs.cap = 0;
+    rs.x16_valid = false;
+}
+
+// Grow (or create) the exact store so that `need` rows fit; keeps existing rows.
+static int rowstore_reserve(akm_handle h, RowStore &rs, int64_t need) {
+    if (need <= rs.cap) return AKM_OK;
+    int64_t cap = rs.cap == 0 ? need : std::max<int64_t>(need, rs.cap + rs.cap / 2);
+    const size_t d = (size_t)h->d;
+    double *nl = nullptr;
+    AKM_TRY(dev_alloc(h, &nl, (size_t)cap));
+    if (rs.n > 0) AKM_CUDA(h, cudaMemcpyAsync(nl, rs.xlabel, sizeof(double) * (size_t)rs.n, cudaMemcpyDeviceToDevice, h->stream));
+    if (rs.store == 4) {
+        float *nx = nullptr;
+        AKM_TRY(dev_alloc(h, &nx, (size_t)cap * d));
+        if (rs.n > 0) AKM_CUDA(h, cudaMemcpyAsync(nx, rs.x32, sizeof(float) * (size_t)rs.n * d, cudaMemcpyDeviceToDevice, h->stream));
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+        dev_free(rs.x32);
+        rs.x32 = nx;
+    } else {
+        double *nx = nullptr;
+        AKM_TRY(dev_alloc(h, &nx, (size_t)cap * d));
+        if (rs.n > 0) AKM_CUDA(h, cudaMemcpyAsync(nx, rs.x64, sizeof(double) * (size_t)rs.n * d, cudaMemcpyDeviceToDevice, h->stream));
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+        dev_free(rs.x64);
+        rs.x64 = nx;
+    }
+    dev_free(rs.xlabel);
+    rs.xlabel = nl;
+    rs.cap = cap;
+    rs.x16_valid = false;
+    return AKM_OK;
+}
+
+// fp32 -> fp64 storage migration (lossless: every stored value was fp32-exact)
+static int rowstore_widen(akm_handle h, RowStore &rs) {
+    double *nx = nullptr;
+    AKM_TRY(dev_alloc(h, &nx, (size_t)rs.cap * (size_t)h->d));
+    AKM_TRY(launch_widen_rows(h, rs.x32, nx, rs.n * (int64_t)h->d));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    dev_free(rs.x32);
+    rs.x64 = nx;
+    rs.store = 8;
+    rs.x16_valid = false;
+    return AKM_OK;
+}
+
+static int ensure_stage(akm_handle h, size_t bytes) {
+    if (h->stage_bytes >= bytes) return AKM_OK;
+    if (h->stage) cudaFree(h->stage);
+    h->stage = nullptr; h->stage_bytes = 0;
+    AKM_CUDA(h, cudaMalloc(&h->stage, bytes));
+    h->stage_bytes = bytes;
+    return AKM_OK;
+}
+
+enum SrcKind { SRC_HOST_F64, SRC_HOST_F32, SRC_DEV_F32 };
+
+static int upload_pass(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n) {
+    const size_t d = (size_t)h->d;
+    if (kind == SRC_DEV_F32) return launch_prep_rows(h, rs, src, true, rs.n, n);
+    const size_t elt = kind == SRC_HOST_F64 ? 8 : 4;
+    const size_t row_bytes = d * elt;
+    int64_t chunk = (int64_t)std::max<size_t>(1, ((size_t)64 << 20) / row_bytes);
+    chunk = std::min<int64_t>(chunk, n);
+    AKM_TRY(ensure_stage(h, (size_t)chunk * row_bytes));
+    for (int64_t off = 0; off < n; off += chunk) {
+        const int64_t m = std::min<int64_t>(chunk, n - off);
+        AKM_CUDA(h, cudaMemcpyAsync(h->stage, (const char *)src + (size_t)off * row_bytes, (size_t)m * row_bytes,
+                                    cudaMemcpyHostToDevice, h->stream));
+        AKM_TRY(launch_prep_rows(h, rs, h->stage, kind == SRC_HOST_F32, rs.n + off, m));
+    }
+    return AKM_OK;
+}
+
+static int upload_rows(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n) {
+    if (n == 0) return AKM_OK;
+    if (h->metric == AKM_COSINE && rs.store == 4) {
+        if (rs.n > 0) return akm_fail(h, AKM_ERR_STATE, "cosine partitions are always fp64");
+        rowstore_free(rs);
+        rs.store = 8;
+    }
+    AKM_TRY(rowstore_reserve(h, rs, rs.n + n));
+    AKM_CUDA(h, cudaMemsetAsync(h->iscal + 3, 0, sizeof(int), h->stream));
+    AKM_TRY(upload_pass(h, rs, src, kind, n));
+    if (rs.store == 4) {
+        AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 3, h->iscal + 3, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+        if (h->h_iscal[3] != 0) {
+            // some value of this batch is not fp32-representable: keep doubles from now on
+            AKM_TRY(rowstore_widen(h, rs));
+            AKM_TRY(upload_pass(h, rs, src, kind, n));
+        }
+    }
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    rs.n += n;
+    rs.x16_valid = false;
+    return AKM_OK;
+}
+
+static int ensure_labels(akm_handle h, int64_t n) {
+    if (h->labels_cap >= n) return AKM_OK;
+    dev_free(h->labels);
+    AKM_TRY(dev_alloc(h, &h->labels, (size_t)n));
+    h->labels_cap = n;
+    return AKM_OK;
+}
+
+static int ensure_mind(akm_handle h, int64_t n) {
+    if (h->mind_cap >= n) return AKM_OK;
+    dev_free(h->mind);
+    AKM_TRY(dev_alloc(h, &h->mind, (size_t)n));
+    h->mind_cap = n;
+    return AKM_OK;
+}
+
+// cent[0] = CENTROID1, cent[1] = CENTROID2 (the ping-pong pair of the device-resident loop)
+static int ensure_centroids(akm_handle h, int k0) {
+    if (h->cent_cap >= k0) return AKM_OK;
+    // preserve nothing: akm_set_centroids re-uploads after growth
+    for (int i = 0; i < 2; ++i) { dev_free(h->cent[i]); dev_free(h->clabel[i]); }
+    dev_free(h->sum);
+    const size_t kd = (size_t)k0 * (size_t)h->d;
+    for (int i = 0; i < 2; ++i) {
+        AKM_TRY(dev_alloc(h, &h->cent[i], kd));
+        AKM_TRY(dev_alloc(h, &h->clabel[i], (size_t)k0));
+    }
+    AKM_TRY(dev_alloc(h, &h->sum, (size_t)k0 * (size_t)(h->d + 1) + 2));
+    h->cent_cap = k0;
+    return AKM_OK;
+}
+
+static int ensure_kvec(akm_handle h, int k0) {
+    if (h->kvec_cap >= k0) return AKM_OK;
+    dev_free(h->cmap); dev_free(h->shift);
+    AKM_TRY(dev_alloc(h, &h->cmap, (size_t)k0));
+    AKM_TRY(dev_alloc(h, &h->shift, (size_t)k0));
+    h->kvec_cap = k0;
+    return AKM_OK;
+}
+
+// scratch centroid buffers for the host-buffer entry points (they do not disturb the ping-pong state)
+struct Scratch {
+    double *c[2] = {nullptr, nullptr};
+    double *l[2] = {nullptr, nullptr};
+    double *sum = nullptr;
+    int cap = 0;
+    double *dist_all = nullptr; size_t dist_all_count = 0;
+    double *probs = nullptr; size_t probs_count = 0;
+    int64_t *idx64 = nullptr; int64_t idx64_cap = 0;
+};
+
+static Scratch *scratch_of(akm_handle h) {
+    if (!h->sc) h->sc = new Scratch();
+    return h->sc;
+}
+
+static void scratch_free(akm_handle h) {
+    Scratch *e = h->sc;
+    if (!e) return;
+    for (int i = 0; i < 2; ++i) { dev_free(e->c[i]); dev_free(e->l[i]); }
+    dev_free(e->sum); dev_free(e->dist_all); dev_free(e->probs); dev_free(e->idx64);
+    delete e;
+    h->sc = nullptr;
+}
+
+static int ensure_scratch(akm_handle h, int k0) {
+    Scratch *s = scratch_of(h);
+    if (s->cap >= k0) return AKM_OK;
+    for (int i = 0; i < 2; ++i) { dev_free(s->c[i]); dev_free(s->l[i]); }
+    dev_free(s->sum);
+    const size_t kd = (size_t)k0 * (size_t)h->d;
+    for (int i = 0; i < 2; ++i) {
+        AKM_TRY(dev_alloc(h, &s->c[i], kd));
+        AKM_TRY(dev_alloc(h, &s->l[i], (size_t)k0));
+    }
+    AKM_TRY(dev_alloc(h, &s->sum, (size_t)k0 * (size_t)(h->d + 1) + 2));
+    s->cap = k0;
+    return ensure_kvec(h, k0);
+}
+
+// ------------------------------------------------------------------ assignment dispatch
+static int run_assign(akm_handle h, RowStore &rs, const double *C, const double *clabel, int k0, int k,
+                      int32_t *labels, double *mind) {
+    h->stats.rows = rs.n;
+    h->stats.storage_bytes = rs.store;
+    bool use_tensor = false;
+    if (h->engine != AKM_ENGINE_EXACT) {
+        use_tensor = tensor_supported(h, k0) && rs.n > 0;
+        if (h->engine == AKM_ENGINE_TENSOR && !use_tensor && rs.n > 0)
+            return akm_fail(h, AKM_ERR_UNSUPPORTED, "tensor engine does not support this shape");
+    }
+    if (use_tensor) {
+        h->stats.engine_used = AKM_ENGINE_TENSOR;
+        return tensor_assign(h, rs, C, clabel, k0, k, labels, mind);
+    }
+    h->stats.engine_used = AKM_ENGINE_EXACT;
+    h->stats.rows_certified = 0;
+    h->stats.rows_refined = rs.n;
+    return launch_assign_exact(h, rs, nullptr, rs.n, C, clabel, k0, k, labels, mind, nullptr);
+}
+
+static int check_error_flag(akm_handle h) {
+    // h_iscal[2] was copied back by the caller
+    if (h->h_iscal[2] != 0) {
+        cudaMemsetAsync(h->iscal + 2, 0, sizeof(int), h->stream);
+        return akm_fail(h, AKM_ERR_NOFINITE,
+                        "a sample has no distance < Double.MAX_VALUE (Java: getMinPointIndex returns -1)");
+    }
+    return AKM_OK;
+}
+
+// ====================================================================== C ABI
+extern "C" {
+
+const char *akm_version(void) { return "akm 0.1.0 (sm_100a; exact fp64 + tcgen05 search)"; }
+
+const char *akm_last_error(akm_handle h) { return h ? h->err.c_str() : g_tls_error.c_str(); }
+
+int akm_create(int device, int d, int metric, akm_handle *out) {
+    if (!out) return akm_fail(nullptr, AKM_ERR_BADARG, "out is null");
+    *out = nullptr;
+    if (d <= 0) return akm_fail(nullptr, AKM_ERR_BADARG, "vector size must be positive");
+    if (metric != AKM_EUCLIDEAN && metric != AKM_COSINE)
+        return akm_fail(nullptr, AKM_ERR_BADARG, "distanceType must be EUCLIDEAN or COSINE");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0)
+        return akm_fail(nullptr, AKM_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return akm_fail(nullptr, AKM_ERR_BADARG, "bad device ordinal");
+    akm_handle h = new (std::nothrow) akm_handle_s();
+    if (!h) return akm_fail(nullptr, AKM_ERR_OOM, "host allocation failed");
+    h->device = device; h->d = d; h->metric = metric;
+    h->rows.store = (metric == AKM_COSINE) ? 8 : 4;
+    h->batch.store = h->rows.store;
+    int rc = AKM_OK;
+    do {
+        if ((rc = bind_device(h))) break;
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "cudaGetDeviceProperties failed"); break; }
+        h->num_sms = prop.multiProcessorCount;
+        h->smem_optin = prop.sharedMemPerBlockOptin;
+        if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "cudaStreamCreate failed"); break; }
+        h->stream = h->own_stream;
+        if (cudaMalloc((void **)&h->dscal, 8 * sizeof(double)) != cudaSuccess ||
+            cudaMalloc((void **)&h->iscal, 16 * sizeof(int)) != cudaSuccess ||
+            cudaMallocHost((void **)&h->h_dscal, 8 * sizeof(double)) != cudaSuccess ||
+            cudaMallocHost((void **)&h->h_iscal, 16 * sizeof(int)) != cudaSuccess) {
+            rc = akm_fail(h, AKM_ERR_OOM, "scalar buffers allocation failed"); break;
+        }
+        cudaMemsetAsync(h->dscal, 0, 8 * sizeof(double), h->stream);
+        cudaMemsetAsync(h->iscal, 0, 16 * sizeof(int), h->stream);
+        memset(h->h_dscal, 0, 8 * sizeof(double));
+        memset(h->h_iscal, 0, 16 * sizeof(int));
+        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "stream sync failed"); break; }
+    } while (0);
+    if (rc != AKM_OK) { std::string m = h->err; akm_destroy(h); g_tls_error = m; return rc; }
+    *out = h;
+    return AKM_OK;
+}
+
+int akm_destroy(akm_handle h) {
+    if (!h) return AKM_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    nccl_destroy(h);
+    tensor_free(h);
+    scratch_free(h);
+    rowstore_free(h->rows);
+    rowstore_free(h->batch);
+    dev_free(h->labels); dev_free(h->mind);
+    for (int i = 0; i < 2; ++i) { dev_free(h->cent[i]); dev_free(h->clabel[i]); }
+    dev_free(h->sum); dev_free(h->cmap); dev_free(h->shift); dev_free(h->dscal); dev_free(h->iscal);
+    if (h->h_dscal) cudaFreeHost(h->h_dscal);
+    if (h->h_iscal) cudaFreeHost(h->h_iscal);
+    if (h->stage) cudaFree(h->stage);
+    if (h->hstage) cudaFreeHost(h->hstage);
+    for (int i = 0; i < 5; ++i) if (h->pev[i]) cudaEventDestroy(h->pev[i]);
+    if (h->mid_event) cudaEventDestroy(h->mid_event);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+    return AKM_OK;
+}
+
+int akm_set_stream(akm_handle h, void *cuda_stream) {
+    AKM_TRY(bind_device(h));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+    return AKM_OK;
+}
+
+int akm_set_engine(akm_handle h, int engine) {
+    if (!h) return akm_fail(nullptr, AKM_ERR_BADARG, "null handle");
+    REQUIRE(h, engine == AKM_ENGINE_AUTO || engine == AKM_ENGINE_EXACT || engine == AKM_ENGINE_TENSOR, "bad engine");
+    h->engine = engine;
+    return AKM_OK;
+}
+
+int akm_reserve_rows(akm_handle h, int64_t n_total) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, n_total >= 0, "negative row count");
+    return rowstore_reserve(h, h->rows, n_total);
+}
+
+int akm_upload_rows(akm_handle h, const double *x_host, int64_t n) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, n >= 0, "negative row count");
+    REQUIRE(h, n == 0 || x_host, "rows pointer is null");
+    return upload_rows(h, h->rows, x_host, SRC_HOST_F64, n);
+}
+
+int akm_upload_rows_f32(akm_handle h, const float *x_host, int64_t n) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, n >= 0, "negative row count");
+    REQUIRE(h, n == 0 || x_host, "rows pointer is null");
+    return upload_rows(h, h->rows, x_host, SRC_HOST_F32, n);
+}
+
+int akm_upload_rows_device_f32(akm_handle h, const float *x_dev, int64_t n) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, n >= 0, "negative row count");
+    REQUIRE(h, n == 0 || x_dev, "rows pointer is null");
+    return upload_rows(h, h->rows, x_dev, SRC_DEV_F32, n);
+}
+
+int akm_clear_rows(akm_handle h) {
+    AKM_TRY(bind_device(h));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    rowstore_free(h->rows);
+    h->rows.store = (h->metric == AKM_COSINE) ? 8 : 4;
+    return AKM_OK;
+}
+
+int akm_num_rows(akm_handle h, int64_t *n_out, int *bytes_per_value_out) {
+    if (!h) return akm_fail(nullptr, AKM_ERR_BADARG, "null handle");
+    if (n_out) *n_out = h->rows.n;
+    if (bytes_per_value_out) *bytes_per_value_out = h->rows.store;
+    return AKM_OK;
+}
+
+int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, double *sum_out,
+                          double *objective_out, int32_t *labels_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, centroids && sum_out, "centroids / sum_out is null");        // Preconditions.checkNotNull(sumMatrix)
+    REQUIRE(h, k0 > 0 && k >= 0 && k <= k0, "need 0 <= k <= k0 and k0 > 0");
+    const int d = h->d;
+    const size_t L = (size_t)k0 * (size_t)(d + 1);
+    AKM_TRY(ensure_scratch(h, k0));
+    Scratch *s = scratch_of(h);
+    if (h->rows.n == 0) {
+        // "if (trainData == null) return;" happens before the fill in Java; an empty list zero-fills
+        memset(sum_out, 0, L * sizeof(double));
+        if (objective_out) *objective_out = 0.0;
+        return AKM_OK;
+    }
+    AKM_TRY(ensure_labels(h, h->rows.n));
+    AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centroids, sizeof(double) * (size_t)k0 * d, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, /*cos_normalise=*/false));
+    AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], k0, k, h->labels, nullptr));
+    AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], k0, s->sum, s->sum + L));
+    AKM_CUDA(h, cudaMemcpyAsync(sum_out, s->sum, sizeof(double) * L, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (labels_out)
+        AKM_CUDA(h, cudaMemcpyAsync(labels_out, h->labels, sizeof(int32_t) * (size_t)h->rows.n, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (objective_out) *objective_out = h->h_dscal[0];
+    return check_error_flag(h);
+}
+
+int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int step_no, const double *prev,
+                         double *c_out, int *k_out, double *shift_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, sum && c_out && k_out, "sum / c_out / k_out is null");
+    REQUIRE(h, k0 > 0 && k >= 0 && k <= k0, "need 0 <= k <= k0 and k0 > 0");
+    const int d = h->d;
+    const size_t L = (size_t)k0 * (size_t)(d + 1);
+    AKM_TRY(ensure_scratch(h, k0));
+    Scratch *s = scratch_of(h);
+    AKM_CUDA(h, cudaMemcpyAsync(s->sum, sum, sizeof(double) * L, cudaMemcpyHostToDevice, h->stream));
+    const double *dprev = nullptr, *lprev = nullptr;
+    if (prev) {
+        AKM_CUDA(h, cudaMemcpyAsync(s->c[0], prev, sizeof(double) * (size_t)k0 * d, cudaMemcpyHostToDevice, h->stream));
+        AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, false));
+        dprev = s->c[0]; lprev = s->l[0];
+    }
+    // the buffer written at step s is CENTROID1 when s is odd (KMeansUpdateCentroids.java:38-42)
+    AKM_TRY(launch_update(h, s->sum, k, k0, s->c[1], s->l[1], dprev, lprev, (step_no % 2) != 0, 0.0, h->shift, h->iscal));
+    AKM_CUDA(h, cudaMemcpyAsync(c_out, s->c[1], sizeof(double) * (size_t)k0 * d, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    *k_out = h->h_iscal[0];
+    if (shift_out && prev && *k_out > 0) {
+        AKM_CUDA(h, cudaMemcpy(shift_out, h->shift, sizeof(double) * (size_t)(*k_out), cudaMemcpyDeviceToHost));
+    }
+    return AKM_OK;
+}
+
+int akm_set_centroids(akm_handle h, const double *c0, int k0) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, c0, "initial centroids are null");            // KMeansPreallocateCentroid.java:31-32
+    REQUIRE(h, k0 > 0, "need at least one initial centroid");
+    AKM_TRY(ensure_centroids(h, k0));
+    AKM_TRY(ensure_kvec(h, k0));
+    const size_t kd = (size_t)k0 * (size_t)h->d;
+    AKM_CUDA(h, cudaMemcpyAsync(h->cent[0], c0, sizeof(double) * kd, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(launch_prepare_centroids(h, h->cent[0], h->clabel[0], k0, true));
+    AKM_CUDA(h, cudaMemcpyAsync(h->cent[1], h->cent[0], sizeof(double) * kd, cudaMemcpyDeviceToDevice, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->clabel[1], h->clabel[0], sizeof(double) * (size_t)k0, cudaMemcpyDeviceToDevice, h->stream));
+    AKM_CUDA(h, cudaMemsetAsync(h->sum, 0, sizeof(double) * ((size_t)k0 * (h->d + 1) + 2), h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->k0 = k0; h->k = k0; h->step = 0;
+    return AKM_OK;
+}
+
+int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *objective_out) {
+    AKM_TRY(bind_device(h));
+    if (h->k0 <= 0) return akm_fail(h, AKM_ERR_STATE, "akm_set_centroids must be called first");
+    const int d = h->d, k0 = h->k0;
+    const size_t L = (size_t)k0 * (size_t)(d + 1);
+    const int s = ++h->step;
+    const int rd = (s % 2 == 0) ? 0 : 1;   // even: CENTROID1, odd: CENTROID2 (KMeansAssignCluster.java:38-42)
+    const int wr = 1 - rd;
+    AKM_TRY(ensure_labels(h, std::max<int64_t>(h->rows.n, 1)));
+    const bool prof = h->profiling;
+    h->mid_recorded = false;
+    if (prof) cudaEventRecord(h->pev[0], h->stream);
+    AKM_TRY(run_assign(h, h->rows, h->cent[rd], h->clabel[rd], k0, h->k, h->labels, nullptr));
+    if (prof) cudaEventRecord(h->pev[1], h->stream);
+    AKM_TRY(launch_accumulate(h, h->rows, h->labels, h->cent[rd], k0, h->sum, h->sum + L));
+    if (prof) cudaEventRecord(h->pev[2], h->stream);
+    if (h->comm) AKM_TRY(nccl_allreduce_device(h, h->sum, (int64_t)L + 1));
+    AKM_TRY(launch_update(h, h->sum, h->k, k0, h->cent[wr], h->clabel[wr], h->cent[rd], h->clabel[rd],
+                          /*new_is_c1=*/wr == 0, tol, h->shift, h->iscal));
+    if (prof) cudaEventRecord(h->pev[3], h->stream);
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 3 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->k = h->h_iscal[0];
+    if (prof) {
+        float a = 0.f, b = 0.f, c = 0.f, m1 = 0.f;
+        cudaEventElapsedTime(&a, h->pev[0], h->pev[1]);
+        cudaEventElapsedTime(&b, h->pev[1], h->pev[2]);
+        cudaEventElapsedTime(&c, h->pev[2], h->pev[3]);
+        if (h->mid_recorded) {
+            cudaEventElapsedTime(&m1, h->pev[0], h->mid_event);
+            h->prof_ms[0] += m1; h->prof_ms[1] += a - m1;
+        } else if (h->stats.engine_used == AKM_ENGINE_EXACT) {
+            h->prof_ms[1] += a;
+        } else {
+            h->prof_ms[0] += a;
+        }
+        h->prof_ms[2] += b; h->prof_ms[3] += c;
+        h->prof_steps++;
+    }
+    if (converged_out) *converged_out = h->h_iscal[1];
+    if (k_out) *k_out = h->k;
+    if (objective_out) *objective_out = h->h_dscal[0];
+    return check_error_flag(h);
+}
+
+int akm_get_model(akm_handle h, double *c_out, int *k_out, double *weights_out, int *steps_out) {
+    AKM_TRY(bind_device(h));
+    if (h->k0 <= 0) return akm_fail(h, AKM_ERR_STATE, "no centroids set");
+    const int d = h->d, k0 = h->k0;
+    // newest buffer = the one written by the last step (larger stamp, KMeansOutputModel.java:50-54)
+    const int newest = (h->step == 0) ? 1 : ((h->step % 2 == 0) ? 1 : 0);
+    if (c_out) AKM_CUDA(h, cudaMemcpyAsync(c_out, h->cent[newest], sizeof(double) * (size_t)k0 * d, cudaMemcpyDeviceToHost, h->stream));
+    if (weights_out) {
+        // weight_j = buffer[j*(d+1)+d] of the last all-reduced pass, uncompacted (KMeansOutputModel.java:60-68)
+        AKM_CUDA(h, cudaMemcpy2DAsync(weights_out, sizeof(double), h->sum + d, sizeof(double) * (size_t)(d + 1),
+                                      sizeof(double), (size_t)k0, cudaMemcpyDeviceToHost, h->stream));
+    }
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (k_out) *k_out = h->k;
+    if (steps_out) *steps_out = h->step;
+    return AKM_OK;
+}
+
+int akm_get_labels(akm_handle h, int32_t *labels_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, labels_out, "labels_out is null");
+    if (h->rows.n == 0) return AKM_OK;
+    if (!h->labels || h->labels_cap < h->rows.n) return akm_fail(h, AKM_ERR_STATE, "no assignment pass has run");
+    AKM_CUDA(h, cudaMemcpyAsync(labels_out, h->labels, sizeof(int32_t) * (size_t)h->rows.n, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AKM_OK;
+}
+
+// ---------------------------------------------------------------- prediction
+static int predict_store(akm_handle h, RowStore &rs, const double *dC, const double *dl, int k, int64_t *idx_out,
+                         double *dist_out, double *probs_out) {
+    Scratch *s = scratch_of(h);
+    const int64_t n = rs.n;
+    if (n == 0) return AKM_OK;
+    AKM_TRY(ensure_labels(h, n));
+    AKM_TRY(ensure_mind(h, n));
+    if (s->idx64_cap < n) {
+        dev_free(s->idx64);
+        AKM_TRY(dev_alloc(h, &s->idx64, (size_t)n));
+        s->idx64_cap = n;
+    }
+    if (probs_out) {
+        // probabilities need every distance exactly as Java computes it: exact engine, in slabs
+        const int64_t slab = std::max<int64_t>(1, std::min<int64_t>(n, ((int64_t)256 << 20) / ((int64_t)k * 8)));
+        if (s->dist_all_count < (size_t)slab * k) {
+            dev_free(s->dist_all); dev_free(s->probs);
+            AKM_TRY(dev_alloc(h, &s->dist_all, (size_t)slab * k));
+            AKM_TRY(dev_alloc(h, &s->probs, (size_t)slab * k));
+            s->dist_all_count = s->probs_count = (size_t)slab * k;
+        }
+        for (int64_t off = 0; off < n; off += slab) {
+            const int64_t m = std::min<int64_t>(slab, n - off);
+            RowStore view = rs;
+            if (rs.store == 4) view.x32 = rs.x32 + off * h->d; else view.x64 = rs.x64 + off * h->d;
+            view.xlabel = rs.xlabel + off;
+            view.n = m;
+            AKM_TRY(launch_assign_exact(h, view, nullptr, m, dC, dl, k, k, h->labels + off, h->mind + off, s->dist_all));
+            AKM_TRY(launch_probs(h, s->dist_all, m, k, s->probs));
+            AKM_CUDA(h, cudaMemcpyAsync(probs_out + (size_t)off * k, s->probs, sizeof(double) * (size_t)m * k,
+                                        cudaMemcpyDeviceToHost, h->stream));
+            AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+        }
+    } else {
+        AKM_TRY(run_assign(h, rs, dC, dl, k, k, h->labels, dist_out ? h->mind : nullptr));
+    }
+    AKM_TRY(launch_labels_to_i64(h, h->labels, n, s->idx64));
+    AKM_CUDA(h, cudaMemcpyAsync(idx_out, s->idx64, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    if (dist_out) AKM_CUDA(h, cudaMemcpyAsync(dist_out, h->mind, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (h->h_iscal[2] != 0) {
+        cudaMemsetAsync(h->iscal + 2, 0, sizeof(int), h->stream);
+        // Java: (long) -1 is emitted; reading clusterDistances[-1] throws only when a distance/detail column is asked for
+        if (dist_out || probs_out)
+            return akm_fail(h, AKM_ERR_NOFINITE, "a row has no distance < Double.MAX_VALUE (index -1)");
+    }
+    return AKM_OK;
+}
+
+int akm_predict(akm_handle h, const double *x_host, int64_t n, const double *centroids, int k, int64_t *idx_out,
+                double *dist_out, double *probs_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, n >= 0, "negative row count");
+    REQUIRE(h, centroids && k > 0, "model centroids missing");
+    REQUIRE(h, n == 0 || (x_host && idx_out), "rows / idx_out is null");
+    if (n == 0) return AKM_OK;
+    AKM_TRY(ensure_scratch(h, k));
+    Scratch *s = scratch_of(h);
+    const int d = h->d;
+    AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centroids, sizeof(double) * (size_t)k * d, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k, /*cos_normalise=*/true));   // loadModel -> updateLabel
+    const int64_t macro = std::max<int64_t>(1, std::min<int64_t>(n, ((int64_t)2 << 30) / ((int64_t)d * 8)));
+    for (int64_t off = 0; off < n; off += macro) {
+        const int64_t m = std::min<int64_t>(macro, n - off);
+        h->batch.n = 0;
+        h->batch.x16_valid = false;
+        AKM_TRY(upload_rows(h, h->batch, x_host + (size_t)off * d, SRC_HOST_F64, m));
+        AKM_TRY(predict_store(h, h->batch, s->c[0], s->l[0], k, idx_out + off, dist_out ? dist_out + off : nullptr,
+                              probs_out ? probs_out + (size_t)off * k : nullptr));
+    }
+    return AKM_OK;
+}
+
+int akm_predict_cached(akm_handle h, const double *centroids, int k, int64_t *idx_out, double *dist_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, centroids && k > 0, "model centroids missing");
+    REQUIRE(h, h->rows.n == 0 || idx_out, "idx_out is null");
+    AKM_TRY(ensure_scratch(h, k));
+    Scratch *s = scratch_of(h);
+    AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centroids, sizeof(double) * (size_t)k * h->d, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k, true));
+    return predict_store(h, h->rows, s->c[0], s->l[0], k, idx_out, dist_out, nullptr);
+}
+
+int akm_get_stats(akm_handle h, akm_stats *out) {
+    if (!h || !out) return akm_fail(h, AKM_ERR_BADARG, "null argument");
+    *out = h->stats;
+    return AKM_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------- kernel timing for the roofline object
+extern "C" int akm_time_kernel(akm_handle h, const char *name, int reps, double *ms_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, name && ms_out && reps > 0, "bad argument");
+    if (h->k0 <= 0 || h->rows.n == 0) return akm_fail(h, AKM_ERR_STATE, "needs cached rows and centroids");
+    const int rd = ((h->step + 1) % 2 == 0) ? 0 : 1;
+    const size_t L = (size_t)h->k0 * (size_t)(h->d + 1);
+    AKM_TRY(ensure_labels(h, h->rows.n));
+    Scratch *s = scratch_of(h);
+    AKM_TRY(ensure_scratch(h, h->k0));
+    cudaEvent_t e0, e1;
+    AKM_CUDA(h, cudaEventCreate(&e0));
+    AKM_CUDA(h, cudaEventCreate(&e1));
+    const bool is_assign = strcmp(name, "assign") == 0;
+    const bool is_acc = strcmp(name, "accumulate") == 0;
+    if (!is_assign && !is_acc) return akm_fail(h, AKM_ERR_BADARG, "name must be assign | accumulate");
+    int rc = AKM_OK;
+    // one untimed launch, then `reps` timed ones (labels must exist before timing accumulate)
+    rc = run_assign(h, h->rows, h->cent[rd], h->clabel[rd], h->k0, h->k, h->labels, nullptr);
+    if (rc == AKM_OK && is_acc) rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->k0, s->sum, s->sum + L);
+    if (rc == AKM_OK) {
+        cudaEventRecord(e0, h->stream);
+        for (int i = 0; i < reps && rc == AKM_OK; ++i) {
+            if (is_assign) rc = run_assign(h, h->rows, h->cent[rd], h->clabel[rd], h->k0, h->k, h->labels, nullptr);
+            else rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->k0, s->sum, s->sum + L);
+        }
+        cudaEventRecord(e1, h->stream);
+        if (cudaEventSynchronize(e1) != cudaSuccess) rc = akm_fail(h, AKM_ERR_CUDA, "event sync failed");
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        *ms_out = (double)ms / reps;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
+}
+
+extern "C" int akm_set_profiling(akm_handle h, int on) {
+    AKM_TRY(bind_device(h));
+    if (on && !h->pev[0]) {
+        for (int i = 0; i < 5; ++i) AKM_CUDA(h, cudaEventCreate(&h->pev[i]));
+        AKM_CUDA(h, cudaEventCreate(&h->mid_event));
+    }
+    h->profiling = on != 0;
+    return AKM_OK;
+}
+
+extern "C" int akm_get_profile(akm_handle h, double *out5, int reset) {
+    if (!h || !out5) return akm_fail(h, AKM_ERR_BADARG, "null argument");
+    for (int i = 0; i < 4; ++i) out5[i] = h->prof_ms[i];
+    out5[4] = (double)h->prof_steps;
+    if (reset) { for (int i = 0; i < 4; ++i) h->prof_ms[i] = 0; h->prof_steps = 0; }
+    return AKM_OK;
+}
+
+// ---------------------------------------------------------------- synthetic blobs (benchmark data)
+extern "C" int akm_blobs_append(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, int64_t row0,
+                                int64_t n) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, k_true > 0 && n >= 0 && row0 >= 0, "bad blob parameters");
+    if (n == 0) return AKM_OK;
+    AKM_TRY(rowstore_reserve(h, h->rows, h->rows.n + n));
+    const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n, ((int64_t)512 << 20) / ((int64_t)h->d * 4)));
+    AKM_TRY(ensure_stage(h, (size_t)chunk * h->d * 4));
+    for (int64_t off = 0; off < n; off += chunk) {
+        const int64_t m = std::min<int64_t>(chunk, n - off);
+        AKM_TRY(launch_blobs(h, seed, k_true, spread, sigma, nullptr, row0 + off, m, (float *)h->stage));
+        AKM_TRY(upload_rows(h, h->rows, h->stage, SRC_DEV_F32, m));
+    }
+    return AKM_OK;
+}
+
+extern "C" int akm_blobs_rows(akm_handle h, uint64_t seed, int k_true, double spread, double sigma,
+                              const int64_t *rows, int64_t m, float *out_host) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, k_true > 0 && m >= 0 && (m == 0 || (rows && out_host)), "bad blob parameters");
+    if (m == 0) return AKM_OK;
+    int64_t *drows = nullptr;
+    float *dout = nullptr;
+    AKM_CUDA(h, cudaMalloc((void **)&drows, sizeof(int64_t) * (size_t)m));
+    cudaError_t e = cudaMalloc((void **)&dout, sizeof(float) * (size_t)m * h->d);
+    if (e != cudaSuccess) { cudaFree(drows); return akm_fail(h, AKM_ERR_OOM, cudaGetErrorString(e)); }
+    int rc = AKM_OK;
+    do {
+        if (cudaMemcpyAsync(drows, rows, sizeof(int64_t) * (size_t)m, cudaMemcpyHostToDevice, h->stream) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "H2D failed"); break; }
+        if ((rc = launch_blobs(h, seed, k_true, spread, sigma, drows, 0, m, dout))) break;
+        if (cudaMemcpyAsync(out_host, dout, sizeof(float) * (size_t)m * h->d, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "D2H failed"); break; }
+        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "sync failed"); break; }
+    } while (0);
+    cudaFree(drows); cudaFree(dout);
+    return rc;
+}

@@ -1,0 +1,138 @@
+// Internal declarations of libakm (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/akm.h"
+
+// ---------------------------------------------------------------- row storage
+// A block of samples resident in HBM after FastDistance.prepareVectorData.
+//   x32 / x64 : n x d row-major, exactly the values Java holds (fp32 only when every
+//               value is fp32-representable, so widening back to double is lossless)
+//   xlabel    : EUCLIDEAN ||x||^2 summed in index order (EuclideanDistance.java:59-65)
+//   x16       : n x d16 fp16 copy scaled by 2^x16_shift, operand of the tcgen05 search
+//   xerr      : per row float2 {||x||_2 rounded up, ||x - x16/scale||_2 rounded up}
+struct RowStore {
+    int64_t n = 0, cap = 0;
+    int store = 4;            // bytes per value of the exact copy (4 or 8)
+    float *x32 = nullptr;
+    double *x64 = nullptr;
+    double *xlabel = nullptr;
+    __half *x16 = nullptr;
+    float2 *xerr = nullptr;
+    int d16 = 0;              // row stride of x16 in elements (multiple of 8)
+    bool want16 = false;
+    int x16_shift = 0;        // x16 = fp16(x * 2^x16_shift)
+    bool x16_valid = false;
+};
+
+struct Scratch;   // akm_api.cu
+
+struct akm_handle_s {
+    int device = 0, d = 0, metric = 0, engine = AKM_ENGINE_AUTO;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    int num_sms = 148;
+    size_t smem_optin = 0;
+
+    RowStore rows;            // cached training partition
+    RowStore batch;           // scratch store for akm_predict micro-batches
+    int32_t *labels = nullptr; int64_t labels_cap = 0;
+    double *mind = nullptr; int64_t mind_cap = 0;   // per-row min distance (predict)
+
+    // centroids: ping-pong (KMeansAssignCluster.java:38-42)
+    int k0 = 0, k = 0, step = 0, cur = 0;
+    double *cent[2] = {nullptr, nullptr};
+    double *clabel[2] = {nullptr, nullptr};
+    int cent_cap = 0;
+    double *sum = nullptr;    // k0*(d+1) + 2 : [L] = sum of xlabel / row count of this rank
+    int *cmap = nullptr;      // k0 compaction map
+    double *shift = nullptr;  // k0
+    int kvec_cap = 0;
+    Scratch *sc = nullptr;    // buffers of the host-buffer entry points
+    double *dscal = nullptr;  // device scalars: [0] objective, [1] sum xlabel (local)
+    int *iscal = nullptr;     // device ints: [0] new k, [1] converged, [2] error flag, [3] inexact flag, [4] worklist count
+    double *h_dscal = nullptr; int *h_iscal = nullptr;   // pinned mirrors
+
+    // staging for uploads
+    void *stage = nullptr; size_t stage_bytes = 0;
+    void *hstage = nullptr; size_t hstage_bytes = 0;     // pinned
+
+    // tensor path scratch (kernels_tensor.cu)
+    void *tc = nullptr;
+
+    // NCCL
+    void *comm = nullptr; int rank = 0, world = 1;
+
+    // optional per-phase profiling of akm_step
+    bool profiling = false;
+    cudaEvent_t pev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    double prof_ms[4] = {0, 0, 0, 0};
+    int64_t prof_steps = 0;
+    cudaEvent_t mid_event = nullptr;   // recorded by tensor_assign between search and refinement
+    bool mid_recorded = false;
+
+    akm_stats stats{};
+    std::string err;
+};
+
+// ---------------------------------------------------------------- error helpers
+void akm_set_tls_error(const std::string &s);
+int akm_fail(akm_handle h, int code, const std::string &msg);
+
+#define AKM_CUDA(h, call)                                                                  \
+    do {                                                                                   \
+        cudaError_t e__ = (call);                                                          \
+        if (e__ != cudaSuccess)                                                            \
+            return akm_fail((h), e__ == cudaErrorMemoryAllocation ? AKM_ERR_OOM : AKM_ERR_CUDA, \
+                            std::string(#call) + ": " + cudaGetErrorString(e__));          \
+    } while (0)
+
+#define AKM_TRY(expr)                  \
+    do {                               \
+        int rc__ = (expr);             \
+        if (rc__ != AKM_OK) return rc__; \
+    } while (0)
+
+// ---------------------------------------------------------------- kernels_exact.cu
+// prepareVectorData over `n` staged rows (src: double or float, row-major) appended at row `row0`.
+int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n);
+// widen rows [0,n) of x32 into x64 (storage migration)
+int launch_widen_rows(akm_handle h, const float *x32, double *x64, int64_t count);
+// updateLabel on k0 centroids in place (EUCL: labels; COS: normalise rows unless cos_normalise == false,
+// which is what KMeansAssignCluster sees: a matrix that was label-updated already)
+int launch_prepare_centroids(akm_handle h, double *C, double *clabel, int k0, bool cos_normalise);
+// exact (Java order) assignment of rows [0,n) or of the rows in `rowlist`
+int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist, int64_t nrows,
+                        const double *C, const double *clabel, int k0, int k, int32_t *labels,
+                        double *mind, double *dist_all);
+// per-cluster sums/counts (+ objective) from labels
+int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C,
+                      int k0, double *sum, double *objective);
+// KMeansUpdateCentroids + KMeansIterTermination diag
+int launch_update(akm_handle h, const double *sum, int k, int k0, double *Cnew, double *clnew,
+                  const double *Cprev, const double *clprev, bool new_is_c1, double tol,
+                  double *shift, int *iscal);
+// probs from all distances (getProbArrayFromDistanceArray)
+int launch_probs(akm_handle h, const double *dist_all, int64_t n, int k, double *probs);
+int launch_labels_to_i64(akm_handle h, const int32_t *labels, int64_t n, int64_t *out);
+
+// ---------------------------------------------------------------- kernels_tensor.cu
+bool tensor_supported(akm_handle h, int k0);
+// approximate search on tensor cores + certification + exact refinement; fills labels (and mind when non-null)
+int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *clabel, int k0, int k,
+                  int32_t *labels, double *mind);
+int tensor_prepare_x16(akm_handle h, RowStore &rs);
+void tensor_free(akm_handle h);
+
+// ---------------------------------------------------------------- akm_nccl.cu
+int nccl_allreduce_device(akm_handle h, double *dbuf, int64_t count);
+void nccl_destroy(akm_handle h);
+
+// ---------------------------------------------------------------- blobs.cu
+int launch_blobs(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, const int64_t *rows_dev,
+                 int64_t row0, int64_t m, float *out_dev);
+
+static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

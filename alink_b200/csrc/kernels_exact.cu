@@ -1,0 +1,670 @@
+// Exact (fp64, Java operation order) kernels of the KMeans hot path.
+//
+// "Java order" means: every product and every sum is rounded separately (no FMA:
+// __dmul_rn / __dadd_rn are never contracted by nvcc) and dot products run in
+// index order, exactly like the F2J reference BLAS loops the Alink code reaches
+// (dgemv 'T': BLAS.java:204-212; daxpy: BLAS.java:96-98; own dot: BLAS.java:103-110).
+// These kernels are the ground truth on the device: the tensor-core search
+// (kernels_tensor.cu) only proposes candidates and falls back to them.
+#include <cfloat>
+#include <climits>
+
+#include "akm_internal.cuh"
+
+#define DMUL(a, b) __dmul_rn((a), (b))
+#define DADD(a, b) __dadd_rn((a), (b))
+
+// =====================================================================================
+// prepareVectorData  (FastDistance.java:136-140 -> Euclidean/CosineDistance.updateLabel)
+// =====================================================================================
+constexpr int PREP_ROWS = 128;   // rows per CTA == threads per CTA
+constexpr int PREP_COLS = 32;
+
+template <typename SrcT, int METRIC, int STORE>
+__global__ void __launch_bounds__(PREP_ROWS)
+prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, float *__restrict__ x32,
+                 double *__restrict__ x64, double *__restrict__ xlabel, double *__restrict__ sum_xlabel,
+                 int *__restrict__ inexact_flag) {
+    __shared__ double tile[PREP_ROWS][PREP_COLS + 1];
+    __shared__ double inv_s[PREP_ROWS];
+    __shared__ double red[PREP_ROWS / 32];
+    const int tid = threadIdx.x;
+    const int64_t base = (int64_t)blockIdx.x * PREP_ROWS;
+    const int lc = tid % PREP_COLS, lr0 = tid / PREP_COLS;
+    bool inexact = false;
+    double s = 0.0;   // sequential sum of squares of row `tid`
+
+    for (int c0 = 0; c0 < d; c0 += PREP_COLS) {
+        __syncthreads();
+#pragma unroll 8
+        for (int it = 0; it < PREP_ROWS / (PREP_ROWS / PREP_COLS); ++it) {
+            const int r = lr0 + it * (PREP_ROWS / PREP_COLS);
+            const int64_t row = base + r;
+            const int col = c0 + lc;
+            double v = 0.0;
+            if (row < n && col < d) {
+                v = (double)src[row * d + col];
+                if (METRIC == AKM_EUCLIDEAN) {
+                    if (STORE == 4) {
+                        const float f = (float)v;
+                        if (!((double)f == v)) inexact = true;   // NaN/overflow also land here
+                        x32[(row0 + row) * d + col] = f;
+                    } else {
+                        x64[(row0 + row) * d + col] = v;
+                    }
+                }
+            }
+            tile[r][lc] = v;
+        }
+        __syncthreads();
+        const int lim = min(PREP_COLS, d - c0);
+        for (int i = 0; i < lim; ++i) {
+            const double v = tile[tid][i];
+            s = DADD(s, DMUL(v, v));
+        }
+    }
+    const int64_t myrow = base + tid;
+    if (METRIC == AKM_EUCLIDEAN) {
+        if (myrow < n) xlabel[row0 + myrow] = s;
+        // block sum of labels (only used for diagnostics)
+        double t = (myrow < n) ? s : 0.0;
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if ((tid & 31) == 0) red[tid >> 5] = t;
+        __syncthreads();
+        if (tid == 0) {
+            double a = 0.0;
+            for (int w = 0; w < PREP_ROWS / 32; ++w) a += red[w];
+            atomicAdd(sum_xlabel, a);
+        }
+    } else {
+        // CosineDistance.updateLabel :60-65: norm = sqrt(dot); if (norm > 0) x *= 1.0 / norm
+        const double nrm = sqrt(s);
+        inv_s[tid] = (nrm > 0.0) ? (1.0 / nrm) : -1.0;   // -1 == leave untouched
+        if (myrow < n) xlabel[row0 + myrow] = 0.0;
+        __syncthreads();
+        for (int c0 = 0; c0 < d; c0 += PREP_COLS) {
+#pragma unroll 8
+            for (int it = 0; it < PREP_ROWS / (PREP_ROWS / PREP_COLS); ++it) {
+                const int r = lr0 + it * (PREP_ROWS / PREP_COLS);
+                const int64_t row = base + r;
+                const int col = c0 + lc;
+                if (row < n && col < d) {
+                    double v = (double)src[row * d + col];
+                    const double inv = inv_s[r];
+                    if (inv >= 0.0) v = DMUL(inv, v);
+                    x64[(row0 + row) * d + col] = v;   // normalised values are never fp32-exact
+                }
+            }
+        }
+    }
+    if (STORE == 4 && inexact) atomicExch(inexact_flag, 1);
+}
+
+int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n) {
+    if (n <= 0) return AKM_OK;
+    const unsigned grid = (unsigned)ceil_div64(n, PREP_ROWS);
+    double *sx = h->dscal + 1;
+    int *flag = h->iscal + 3;
+#define PREP_LAUNCH(SRC, M, ST)                                                              \
+    prep_rows_kernel<SRC, M, ST><<<grid, PREP_ROWS, 0, h->stream>>>((const SRC *)src, n, h->d, row0, rs.x32, \
+                                                                    rs.x64, rs.xlabel, sx, flag)
+    if (h->metric == AKM_EUCLIDEAN) {
+        if (rs.store == 4) { if (src_is_f32) PREP_LAUNCH(float, AKM_EUCLIDEAN, 4); else PREP_LAUNCH(double, AKM_EUCLIDEAN, 4); }
+        else               { if (src_is_f32) PREP_LAUNCH(float, AKM_EUCLIDEAN, 8); else PREP_LAUNCH(double, AKM_EUCLIDEAN, 8); }
+    } else {
+        if (src_is_f32) PREP_LAUNCH(float, AKM_COSINE, 8); else PREP_LAUNCH(double, AKM_COSINE, 8);
+    }
+#undef PREP_LAUNCH
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+__global__ void widen_rows_kernel(const float *__restrict__ a, double *__restrict__ b, int64_t count) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < count; i += stride) b[i] = (double)a[i];
+}
+
+int launch_widen_rows(akm_handle h, const float *x32, double *x64, int64_t count) {
+    if (count <= 0) return AKM_OK;
+    widen_rows_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(x32, x64, count);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+// =====================================================================================
+// updateLabel on a centroid matrix (EuclideanDistance.java:66-86, CosineDistance.java:66-84)
+// =====================================================================================
+__device__ __forceinline__ void centroid_label_row(int metric, double *c, int d, double *label_out,
+                                                   bool cos_normalise = true) {
+    double s = 0.0;
+    for (int i = 0; i < d; ++i) s = DADD(s, DMUL(c[i], c[i]));
+    if (metric == AKM_EUCLIDEAN) {
+        *label_out = s;
+    } else if (!cos_normalise) {
+        *label_out = 0.0;
+    } else {
+        const double nrm = sqrt(s);
+        if (nrm > 0.0) {
+            const double inv = 1.0 / nrm;
+            for (int i = 0; i < d; ++i) c[i] = DMUL(inv, c[i]);   // BLAS.scal
+        }
+        *label_out = 0.0;
+    }
+}
+
+__global__ void prepare_centroids_kernel(int metric, double *C, double *clabel, int k0, int d, int cos_normalise) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < k0) centroid_label_row(metric, C + (size_t)j * d, d, clabel + j, cos_normalise != 0);
+}
+
+int launch_prepare_centroids(akm_handle h, double *C, double *clabel, int k0, bool cos_normalise) {
+    if (k0 <= 0) return AKM_OK;
+    prepare_centroids_kernel<<<(k0 + 127) / 128, 128, 0, h->stream>>>(h->metric, C, clabel, k0, h->d,
+                                                                       cos_normalise ? 1 : 0);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+// =====================================================================================
+// Exact assignment: KMeansUtil.updateSumMatrix's distance + argmin part
+//   t_j = sum_i C[j][i]*x[i]  (index order, separate roundings)
+//   EUCL: D_j = sqrt(|((0 + -2*t_j) + xlabel) + clabel_j|)      EuclideanDistance.java:109-116
+//   COS : D_j = 1 + (-1)*t_j                                    CosineDistance.java:107-110
+//   a   = first j < k with D_j < running min (start Double.MAX_VALUE)   KMeansUtil.java:162-173
+// One CTA = 64 rows; loops over 64-centroid tiles; each thread owns a 4x4 (row, centroid) patch.
+// =====================================================================================
+constexpr int AE_TR = 64, AE_TC = 64, AE_KC = 32, AE_LD = 66;
+
+template <typename T, int METRIC, bool INDIRECT>
+__global__ void __launch_bounds__(256)
+assign_exact_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, const int32_t *__restrict__ rowlist,
+                    int64_t nrows, int d, const double *__restrict__ C, const double *__restrict__ clabel, int k,
+                    int32_t *__restrict__ labels, double *__restrict__ mind, double *__restrict__ dist_all, int kd,
+                    int *__restrict__ err_flag) {
+    __shared__ __align__(16) double xs[AE_KC][AE_LD];
+    __shared__ __align__(16) double cs[AE_KC][AE_LD];
+    __shared__ int64_t srow[AE_TR];
+    const int tid = threadIdx.x;
+    const int tr = tid >> 4, tc = tid & 15;
+    const int64_t base = (int64_t)blockIdx.x * AE_TR;
+    if (tid < AE_TR) {
+        const int64_t p = base + tid;
+        int64_t r = -1;
+        if (p < nrows) r = INDIRECT ? (int64_t)rowlist[p] : p;
+        srow[tid] = r;
+    }
+    __syncthreads();
+
+    double bestv[4];
+    int besti[4];
+    double xl[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        bestv[a] = DBL_MAX;
+        besti[a] = INT_MAX;
+        const int64_t r = srow[4 * tr + a];
+        xl[a] = (METRIC == AKM_EUCLIDEAN && r >= 0) ? xlabel[r] : 0.0;
+    }
+    const int lcol = tid & 31, lrow0 = tid >> 5;   // loader mapping: warp = one row, 32 consecutive columns
+
+    for (int c0 = 0; c0 < k; c0 += AE_TC) {
+        double t[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) t[a][b] = 0.0;
+
+        for (int i0 = 0; i0 < d; i0 += AE_KC) {
+            __syncthreads();
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int r = lrow0 + 8 * it;
+                const int col = i0 + lcol;
+                const int64_t row = srow[r];
+                double xv = 0.0, cv = 0.0;
+                if (row >= 0 && col < d) xv = (double)X[row * d + col];
+                const int cj = c0 + r;
+                if (cj < k && col < d) cv = C[(size_t)cj * d + col];
+                xs[lcol][r] = xv;
+                cs[lcol][r] = cv;
+            }
+            __syncthreads();
+            const int lim = min(AE_KC, d - i0);
+            for (int i = 0; i < lim; ++i) {
+                const double2 xa = *reinterpret_cast<const double2 *>(&xs[i][4 * tr]);
+                const double2 xb = *reinterpret_cast<const double2 *>(&xs[i][4 * tr + 2]);
+                const double2 ca = *reinterpret_cast<const double2 *>(&cs[i][4 * tc]);
+                const double2 cb = *reinterpret_cast<const double2 *>(&cs[i][4 * tc + 2]);
+                const double xv[4] = {xa.x, xa.y, xb.x, xb.y};
+                const double cv[4] = {ca.x, ca.y, cb.x, cb.y};
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) t[a][b] = DADD(t[a][b], DMUL(cv[b], xv[a]));
+            }
+        }
+        // distances + running first-minimum
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int j = c0 + 4 * tc + b;
+            if (j < k) {
+                const double cl = (METRIC == AKM_EUCLIDEAN) ? clabel[j] : 0.0;
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    double D;
+                    if (METRIC == AKM_EUCLIDEAN) {
+                        const double y = DADD(0.0, DMUL(-2.0, t[a][b]));     // y = 0 (beta == 0); y += alpha*temp
+                        D = sqrt(fabs(DADD(DADD(y, xl[a]), cl)));
+                    } else {
+                        D = DADD(1.0, DMUL(-1.0, t[a][b]));                  // y = 1 (beta == 1); y += alpha*temp
+                    }
+                    if (dist_all != nullptr) {
+                        const int64_t p = base + 4 * tr + a;
+                        if (p < nrows) dist_all[p * kd + j] = D;
+                    }
+                    if (D < DBL_MAX && (D < bestv[a] || (D == bestv[a] && j < besti[a]))) {
+                        bestv[a] = D;
+                        besti[a] = j;
+                    }
+                }
+            }
+        }
+    }
+    // merge the 16 centroid lanes of each row: lowest distance, then lowest index (== first minimum)
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, bestv[a], o);
+            const int oi = __shfl_xor_sync(0xffffffffu, besti[a], o);
+            if (oi != INT_MAX && (ov < bestv[a] || (ov == bestv[a] && oi < besti[a]))) {
+                bestv[a] = ov;
+                besti[a] = oi;
+            }
+        }
+        if (tc == 0) {
+            const int64_t p = base + 4 * tr + a;
+            const int64_t r = srow[4 * tr + a];
+            if (r >= 0) {
+                const int64_t o = INDIRECT ? r : p;
+                const int lab = (besti[a] == INT_MAX) ? -1 : besti[a];
+                labels[o] = lab;
+                if (mind != nullptr) mind[o] = (lab < 0) ? nan("") : bestv[a];
+                if (lab < 0) atomicExch(err_flag, 1);
+            }
+        }
+    }
+}
+
+int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist, int64_t nrows, const double *C,
+                        const double *clabel, int k0, int k, int32_t *labels, double *mind, double *dist_all) {
+    (void)k0;
+    if (nrows <= 0) return AKM_OK;
+    const unsigned grid = (unsigned)ceil_div64(nrows, AE_TR);
+    int *err = h->iscal + 2;
+#define AE_LAUNCH(T, PTR, M, IND)                                                                        \
+    assign_exact_kernel<T, M, IND><<<grid, 256, 0, h->stream>>>(PTR, rs.xlabel, rowlist, nrows, h->d, C, clabel, k, \
+                                                                labels, mind, dist_all, k, err)
+    const bool ind = rowlist != nullptr;
+    if (h->metric == AKM_EUCLIDEAN) {
+        if (rs.store == 4) { if (ind) AE_LAUNCH(float, rs.x32, AKM_EUCLIDEAN, true); else AE_LAUNCH(float, rs.x32, AKM_EUCLIDEAN, false); }
+        else               { if (ind) AE_LAUNCH(double, rs.x64, AKM_EUCLIDEAN, true); else AE_LAUNCH(double, rs.x64, AKM_EUCLIDEAN, false); }
+    } else {
+        if (ind) AE_LAUNCH(double, rs.x64, AKM_COSINE, true); else AE_LAUNCH(double, rs.x64, AKM_COSINE, false);
+    }
+#undef AE_LAUNCH
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+// =====================================================================================
+// Per-cluster sums and counts: the daxpy/count half of KMeansUtil.updateSumMatrix (:76-83)
+// as a segmented reduction.  One CTA owns a chunk of rows: it counting-sorts the chunk's
+// row offsets by label in shared memory, then each warp reduces whole (cluster, chunk)
+// segments in registers (lane <-> columns lane + 32*m, coalesced 128-byte row reads, fp64
+// accumulation) and flushes one fp64 atomic per (segment, column).
+// The objective is accumulated on the way: EUCL sum (x-c)^2 (robust form of D^2),
+// COS count - c.S.
+// =====================================================================================
+constexpr int ACC_THREADS = 512;
+constexpr int ACC_MAX_CHUNK = 65536;   // row offsets are uint16
+
+template <typename T, int DC, int METRIC>
+__global__ void __launch_bounds__(ACC_THREADS)
+accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, int64_t n, int d, int k0,
+                  int chunk_rows, const double *__restrict__ C, double *__restrict__ sum,
+                  double *__restrict__ objective) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    int *off = reinterpret_cast<int *>(smem_raw);           // k0 + 1
+    int *cursor = off + (k0 + 1);                           // k0
+    unsigned short *sorted = reinterpret_cast<unsigned short *>(cursor + k0 + ((k0 & 1) ? 1 : 0));
+    __shared__ int scan_tmp[ACC_THREADS];
+    __shared__ double obj_red[ACC_THREADS / 32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = (int64_t)blockIdx.x * chunk_rows;
+    const int rows = (int)min((int64_t)chunk_rows, n - base);
+    const int cb0 = blockIdx.y * (DC * 32);
+
+    for (int j = tid; j <= k0; j += ACC_THREADS) off[j] = 0;
+    __syncthreads();
+    for (int r = tid; r < rows; r += ACC_THREADS) {
+        const int lab = labels[base + r];
+        if (lab >= 0 && lab < k0) atomicAdd(&off[lab + 1], 1);
+    }
+    __syncthreads();
+    // inclusive scan of off[1..k0] -> off[j] = start of cluster j
+    {
+        const int per = (k0 + ACC_THREADS - 1) / ACC_THREADS;
+        const int lo = tid * per, hi = min(k0, lo + per);
+        int s = 0;
+        for (int j = lo; j < hi; ++j) s += off[j + 1];
+        scan_tmp[tid] = s;
+        __syncthreads();
+        for (int o = 1; o < ACC_THREADS; o <<= 1) {
+            int v = (tid >= o) ? scan_tmp[tid - o] : 0;
+            __syncthreads();
+            scan_tmp[tid] += v;
+            __syncthreads();
+        }
+        int run = (tid > 0) ? scan_tmp[tid - 1] : 0;
+        for (int j = lo; j < hi; ++j) {
+            const int c = off[j + 1];
+            cursor[j] = run;
+            run += c;
+            off[j + 1] = run;   // safe: off[j+1] of this range is only read by this thread
+        }
+    }
+    __syncthreads();
+    for (int r = tid; r < rows; r += ACC_THREADS) {
+        const int lab = labels[base + r];
+        if (lab >= 0 && lab < k0) {
+            const int p = atomicAdd(&cursor[lab], 1);
+            sorted[p] = (unsigned short)r;
+        }
+    }
+    __syncthreads();
+
+    double obj = 0.0;
+    for (int j = warp; j < k0; j += ACC_THREADS / 32) {
+        const int s = off[j], e = off[j + 1];
+        if (s == e) continue;
+        double acc[DC], cen[DC], sq[DC];
+#pragma unroll
+        for (int m = 0; m < DC; ++m) {
+            acc[m] = 0.0;
+            sq[m] = 0.0;
+            const int col = cb0 + lane + 32 * m;
+            cen[m] = (col < d) ? C[(size_t)j * d + col] : 0.0;
+        }
+        int p = s;
+        constexpr int U = (DC <= 2) ? 8 : ((DC <= 4) ? 4 : 2);   // rows in flight per warp (register budget)
+        for (; p + U <= e; p += U) {
+            double v[U][DC];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const T *row = X + (base + sorted[p + u]) * (int64_t)d + cb0 + lane;
+#pragma unroll
+                for (int m = 0; m < DC; ++m) v[u][m] = (cb0 + lane + 32 * m < d) ? (double)row[32 * m] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int m = 0; m < DC; ++m) {
+                    acc[m] += v[u][m];
+                    if (METRIC == AKM_EUCLIDEAN) {
+                        const double df = v[u][m] - cen[m];
+                        sq[m] = fma(df, df, sq[m]);
+                    }
+                }
+        }
+        for (; p < e; ++p) {
+            const T *row = X + (base + sorted[p]) * (int64_t)d + cb0 + lane;
+#pragma unroll
+            for (int m = 0; m < DC; ++m) {
+                const double v = (cb0 + lane + 32 * m < d) ? (double)row[32 * m] : 0.0;
+                acc[m] += v;
+                if (METRIC == AKM_EUCLIDEAN) {
+                    const double df = v - cen[m];
+                    sq[m] = fma(df, df, sq[m]);
+                }
+            }
+        }
+        double *out = sum + (size_t)j * (d + 1);
+#pragma unroll
+        for (int m = 0; m < DC; ++m) {
+            const int col = cb0 + lane + 32 * m;
+            if (col < d) {
+                atomicAdd(out + col, acc[m]);
+                if (METRIC == AKM_EUCLIDEAN) obj += sq[m];
+                else obj -= cen[m] * acc[m];
+            }
+        }
+        if (lane == 0 && blockIdx.y == 0) {
+            atomicAdd(out + d, (double)(e - s));
+            if (METRIC == AKM_COSINE) obj += (double)(e - s);
+        }
+    }
+    if (objective != nullptr) {
+        for (int o = 16; o > 0; o >>= 1) obj += __shfl_xor_sync(0xffffffffu, obj, o);
+        if (lane == 0) obj_red[warp] = obj;
+        __syncthreads();
+        if (tid == 0) {
+            double a = 0.0;
+            for (int w = 0; w < ACC_THREADS / 32; ++w) a += obj_red[w];
+            atomicAdd(objective, a);
+        }
+    }
+}
+
+// General fallback (k0 too large for the shared-memory sort): one warp per row, fp64 atomics.
+template <typename T, int METRIC>
+__global__ void accumulate_atomic_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, int64_t n, int d,
+                                         int k0, const double *__restrict__ C, double *__restrict__ sum,
+                                         double *__restrict__ objective) {
+    const int lane = threadIdx.x & 31;
+    int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    double obj = 0.0;
+    for (; row < n; row += stride) {
+        const int lab = labels[row];
+        if (lab < 0 || lab >= k0) continue;
+        double *out = sum + (size_t)lab * (d + 1);
+        const double *c = C + (size_t)lab * d;
+        for (int col = lane; col < d; col += 32) {
+            const double v = (double)X[row * d + col];
+            atomicAdd(out + col, v);
+            if (METRIC == AKM_EUCLIDEAN) { const double df = v - c[col]; obj = fma(df, df, obj); }
+            else obj -= c[col] * v;
+        }
+        if (lane == 0) { atomicAdd(out + d, 1.0); if (METRIC == AKM_COSINE) obj += 1.0; }
+    }
+    if (objective != nullptr) {
+        for (int o = 16; o > 0; o >>= 1) obj += __shfl_xor_sync(0xffffffffu, obj, o);
+        if (lane == 0 && obj != 0.0) atomicAdd(objective, obj);
+    }
+}
+
+template <typename T, int METRIC>
+static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_t *labels, const double *C, int k0,
+                               double *sum, double *objective) {
+    const int d = h->d;
+    // chunk size: <= 65536 rows, aim for >= 4 CTAs per SM, bounded by shared memory
+    const size_t fixed = (size_t)(2 * k0 + 2) * sizeof(int);
+    const size_t budget = h->smem_optin > 8192 ? h->smem_optin - 8192 : 0;
+    if (fixed + 2048 * 2 > budget) {
+        const int blocks = h->num_sms * 8;
+        accumulate_atomic_kernel<T, METRIC><<<blocks, 256, 0, h->stream>>>(X, labels, n, d, k0, C, sum, objective);
+        h->stats.kernel_launches++;
+        AKM_CUDA(h, cudaGetLastError());
+        return AKM_OK;
+    }
+    int64_t chunk = ceil_div64(n, (int64_t)h->num_sms * 4);
+    chunk = ((chunk + 1023) / 1024) * 1024;
+    if (chunk > ACC_MAX_CHUNK) chunk = ACC_MAX_CHUNK;
+    const int64_t max_by_smem = (int64_t)((budget - fixed) / 2);
+    if (chunk > max_by_smem) chunk = (max_by_smem / 1024) * 1024;
+    if (chunk < 1024) chunk = 1024;
+    const size_t smem = fixed + (size_t)chunk * 2;
+    const int dc_need = (d + 31) / 32;
+    const int DCsel = dc_need >= 8 ? 8 : dc_need;
+    const dim3 grid((unsigned)ceil_div64(n, chunk), (unsigned)((d + DCsel * 32 - 1) / (DCsel * 32)));
+#define ACC_CASE(DCV)                                                                                          \
+    case DCV: {                                                                                                \
+        auto kern = accumulate_kernel<T, DCV, METRIC>;                                                         \
+        AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
+        kern<<<grid, ACC_THREADS, smem, h->stream>>>(X, labels, n, d, k0, (int)chunk, C, sum, objective);      \
+    } break
+    switch (DCsel) {
+        ACC_CASE(1); ACC_CASE(2); ACC_CASE(3); ACC_CASE(4); ACC_CASE(5); ACC_CASE(6); ACC_CASE(7); ACC_CASE(8);
+    }
+#undef ACC_CASE
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C, int k0, double *sum,
+                      double *objective) {
+    AKM_CUDA(h, cudaMemsetAsync(sum, 0, sizeof(double) * (size_t)k0 * (h->d + 1), h->stream));   // Arrays.fill :59
+    if (objective) AKM_CUDA(h, cudaMemsetAsync(objective, 0, sizeof(double), h->stream));
+    if (rs.n <= 0) return AKM_OK;
+    if (h->metric == AKM_EUCLIDEAN) {
+        if (rs.store == 4) return accumulate_dispatch<float, AKM_EUCLIDEAN>(h, rs.x32, rs.n, labels, C, k0, sum, objective);
+        return accumulate_dispatch<double, AKM_EUCLIDEAN>(h, rs.x64, rs.n, labels, C, k0, sum, objective);
+    }
+    return accumulate_dispatch<double, AKM_COSINE>(h, rs.x64, rs.n, labels, C, k0, sum, objective);
+}
+
+// =====================================================================================
+// KMeansUpdateCentroids.updateCentroids (:52-69) + KMeansIterTermination diagonal (:28-44)
+// Single CTA: k0*d is at most a few hundred thousand values.
+//   iscal[0] = new k, iscal[1] = converged
+// =====================================================================================
+constexpr int UPD_THREADS = 1024;
+
+__global__ void __launch_bounds__(UPD_THREADS)
+update_kernel(int metric, const double *__restrict__ sum, int k, int k0, int d, double *__restrict__ Cnew,
+              double *__restrict__ clnew, const double *__restrict__ Cprev, const double *__restrict__ clprev,
+              int new_is_c1, double tol, double *__restrict__ shift, int *__restrict__ cmap, int *__restrict__ iscal) {
+    __shared__ int scan_tmp[UPD_THREADS];
+    __shared__ int s_newk, s_notconv;
+    const int tid = threadIdx.x;
+    const int per = (k + UPD_THREADS - 1) / UPD_THREADS;
+    const int lo = min(k, tid * per), hi = min(k, lo + per);
+    int cnt = 0;
+    for (int j = lo; j < hi; ++j) cnt += (sum[(size_t)j * (d + 1) + d] != 0.0) ? 1 : 0;   // "if (weight == 0) continue"
+    scan_tmp[tid] = cnt;
+    if (tid == 0) s_notconv = 0;
+    __syncthreads();
+    for (int o = 1; o < UPD_THREADS; o <<= 1) {
+        const int v = (tid >= o) ? scan_tmp[tid - o] : 0;
+        __syncthreads();
+        scan_tmp[tid] += v;
+        __syncthreads();
+    }
+    int run = (tid > 0) ? scan_tmp[tid - 1] : 0;
+    for (int j = lo; j < hi; ++j) {
+        const bool ne = sum[(size_t)j * (d + 1) + d] != 0.0;
+        cmap[j] = ne ? run : -1;
+        run += ne ? 1 : 0;
+    }
+    if (tid == UPD_THREADS - 1) s_newk = scan_tmp[UPD_THREADS - 1];
+    // Arrays.fill(data, 0.0)
+    for (size_t i = tid; i < (size_t)k0 * d; i += UPD_THREADS) Cnew[i] = 0.0;
+    __syncthreads();
+    // daxpy(d, 1.0/weight, buffer, start, data, index*d):  y = 0 + (1/w)*x
+    for (size_t e = tid; e < (size_t)k * d; e += UPD_THREADS) {
+        const int j = (int)(e / d), i = (int)(e % d);
+        const int m = cmap[j];
+        if (m >= 0) {
+            const double w = sum[(size_t)j * (d + 1) + d];
+            const double a = 1.0 / w;
+            Cnew[(size_t)m * d + i] = DADD(0.0, DMUL(a, sum[(size_t)j * (d + 1) + i]));
+        }
+    }
+    __syncthreads();
+    // distance.updateLabel over ALL k0 columns
+    for (int j = tid; j < k0; j += UPD_THREADS) centroid_label_row(metric, Cnew + (size_t)j * d, d, clnew + j);
+    __syncthreads();
+    const int newk = s_newk;
+    if (Cprev != nullptr) {
+        // left = CENTROID1, right = CENTROID2 (KMeansIterTermination.java:33):
+        // EUCL sqrt(|(-2*dot(right,left) + label_right) + label_left|), COS (-1*dot) + 1*1
+        const double *c1 = new_is_c1 ? Cnew : Cprev, *l1 = new_is_c1 ? clnew : clprev;
+        const double *c2 = new_is_c1 ? Cprev : Cnew, *l2 = new_is_c1 ? clprev : clnew;
+        int notconv = 0;
+        for (int j = tid; j < newk; j += UPD_THREADS) {
+            const double *a = c2 + (size_t)j * d, *b = c1 + (size_t)j * d;
+            double t = 0.0;
+            for (int l = 0; l < d; ++l) t = DADD(t, DMUL(a[l], b[l]));
+            double v;
+            if (metric == AKM_EUCLIDEAN) {
+                v = DMUL(-2.0, t);
+                v = sqrt(fabs(DADD(DADD(v, l2[j]), l1[j])));
+            } else {
+                v = DADD(DMUL(-1.0, t), DMUL(1.0, 1.0));
+            }
+            if (shift) shift[j] = v;
+            if (v >= tol) notconv = 1;
+        }
+        if (notconv) atomicExch(&s_notconv, 1);
+        __syncthreads();
+    }
+    if (tid == 0) {
+        iscal[0] = newk;
+        iscal[1] = (Cprev != nullptr && s_notconv == 0) ? 1 : 0;
+    }
+}
+
+int launch_update(akm_handle h, const double *sum, int k, int k0, double *Cnew, double *clnew, const double *Cprev,
+                  const double *clprev, bool new_is_c1, double tol, double *shift, int *iscal) {
+    update_kernel<<<1, UPD_THREADS, 0, h->stream>>>(h->metric, sum, k, k0, h->d, Cnew, clnew, Cprev, clprev,
+                                                    new_is_c1 ? 1 : 0, tol, shift, h->cmap, iscal);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+// =====================================================================================
+// KMeansUtil.getProbArrayFromDistanceArray (:262-269): sequential sum (StatUtils.sum),
+// ratio = 1.0 / sum / (k-1), probs = 1/(k-1) + (-ratio)*d_i
+// =====================================================================================
+__global__ void probs_kernel(const double *__restrict__ dist_all, int64_t n, int k, double *__restrict__ probs) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const double *dr = dist_all + r * k;
+    double s = 0.0;
+    for (int i = 0; i < k; ++i) s = DADD(s, dr[i]);
+    const double ratio = (1.0 / s) / (double)(k - 1);
+    const double base = 1.0 / (double)(k - 1);
+    double *pr = probs + r * k;
+    for (int i = 0; i < k; ++i) pr[i] = DADD(base, DMUL(-ratio, dr[i]));
+}
+
+int launch_probs(akm_handle h, const double *dist_all, int64_t n, int k, double *probs) {
+    if (n <= 0) return AKM_OK;
+    probs_kernel<<<(unsigned)ceil_div64(n, 128), 128, 0, h->stream>>>(dist_all, n, k, probs);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+__global__ void labels_to_i64_kernel(const int32_t *__restrict__ a, int64_t n, int64_t *__restrict__ b) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) b[i] = (int64_t)a[i];
+}
+
+int launch_labels_to_i64(akm_handle h, const int32_t *labels, int64_t n, int64_t *out) {
+    if (n <= 0) return AKM_OK;
+    labels_to_i64_kernel<<<h->num_sms * 4, 256, 0, h->stream>>>(labels, n, out);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}

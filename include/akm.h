@@ -1,0 +1,235 @@
+/*
+ * akm.h -- C ABI of the B200-native KMeans hot path for Alink ("akm" = Alink KMeans).
+ *
+ * One shared library (alink_b200/csrc/libakm.so), plain C types only, no C++
+ * exceptions or abort() across the boundary.  Every function returns an int:
+ * AKM_OK (0) or a negative AKM_ERR_* class; akm_last_error() gives the message.
+ * A Java shim maps non-zero to RuntimeException (the reference fails the Flink
+ * job through unchecked exceptions, e.g. KMeansUtil.java:68-71,
+ * KMeansTrainBatchOp.java:106).
+ *
+ * Reference paths:  CORE = core/src/main/java/com/alibaba/alink
+ *
+ * Layout conventions (same bytes Alink already holds):
+ *   - a block of n samples is n x d row-major doubles == the d x n column-major
+ *     DenseMatrix Alink uses (CORE/common/linalg/DenseMatrix.java:26-33,202-204);
+ *   - centroids are k0 x d row-major == FastDistanceMatrixData.vectors (d x k0
+ *     column-major, CORE/operator/common/distance/FastDistanceMatrixData.java:18-26);
+ *   - the accumulator is double[k0*(d+1)], row j = [sum of samples (d), count]
+ *     == "centroidAllReduce" (CORE/operator/batch/clustering/KMeansTrainBatchOp.java:34-41).
+ *
+ * Threading: a handle belongs to one thread at a time (one Flink
+ * subtask <-> one handle <-> one GPU + one CUDA stream); distinct handles may be
+ * used concurrently.  The caller owns every host pointer; the library copies in
+ * and out during the call and never retains host pointers.
+ */
+#ifndef AKM_H_
+#define AKM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct akm_handle_s *akm_handle;
+
+/* HasKMeansDistanceType (CORE/params/shared/clustering/HasKMeansDistanceType.java:37-45) */
+#define AKM_EUCLIDEAN 0
+#define AKM_COSINE 1
+
+#define AKM_OK 0
+#define AKM_ERR_BADARG (-1)      /* IllegalArgumentException / NullPointerException analogue */
+#define AKM_ERR_CUDA (-2)
+#define AKM_ERR_NCCL (-3)
+#define AKM_ERR_OOM (-4)
+#define AKM_ERR_NOFINITE (-5)    /* some row has no distance < Double.MAX_VALUE: Java's
+                                    getMinPointIndex returns -1 and updateSumMatrix then throws
+                                    ArrayIndexOutOfBounds (KMeansUtil.java:162-173,75) */
+#define AKM_ERR_STATE (-6)       /* IllegalStateException analogue (call order) */
+#define AKM_ERR_UNSUPPORTED (-7)
+
+/* assignment engines (akm_set_engine) */
+#define AKM_ENGINE_AUTO 0        /* tensor-core search + exact certification when the shape allows */
+#define AKM_ENGINE_EXACT 1       /* every distance evaluated in fp64 in the Java operation order */
+#define AKM_ENGINE_TENSOR 2      /* force the tcgen05 path (error if the shape is unsupported) */
+
+/* ------------------------------------------------------------------ lifecycle */
+
+/* One handle per (sessionId, taskId): replaces the per-task objects the ComQueue keeps in
+ * SessionSharedObjs (CORE/common/comqueue/SessionSharedObjs.java:50-73) for this path.
+ * `d` = vectorSize (KMeansTrainBatchOp.VECTOR_SIZE), metric = AKM_EUCLIDEAN | AKM_COSINE. */
+int akm_create(int device, int d, int metric, akm_handle *out);
+
+/* Frees every device buffer; called from the ComQueue's clearObjs stage
+ * (CORE/common/comqueue/BaseComQueue.java:420-442). */
+int akm_destroy(akm_handle h);
+
+/* Message of the last error on this handle (or of the calling thread when h == NULL). */
+const char *akm_last_error(akm_handle h);
+
+/* Version / build info string. */
+const char *akm_version(void);
+
+/* Use an existing CUDA stream (e.g. torch's current stream) for all work of this handle.
+ * stream == NULL restores the handle's own stream.  No reference counterpart. */
+int akm_set_stream(akm_handle h, void *cuda_stream);
+
+/* Select the assignment engine (default AKM_ENGINE_AUTO).  Results are identical by
+ * construction; EXACT exists for verification.  No reference counterpart. */
+int akm_set_engine(akm_handle h, int engine);
+
+/* ------------------------------------------------------------------ training data (superstep 1) */
+
+/* Optional: pre-size device storage for n_total rows (avoids regrowth while appending). */
+int akm_reserve_rows(akm_handle h, int64_t n_total);
+
+/* Appends n samples (host, n x d doubles) to the partition cached on the GPU and performs
+ * FastDistance.prepareVectorData on them (CORE/operator/common/distance/FastDistance.java:136-140,
+ * called from KMeansTrainBatchOp.java:95-101): EUCLIDEAN label = sum x_i^2 in index order
+ * (EuclideanDistance.java:59-65), COSINE x <- x * (1/||x||) when ||x|| > 0 (CosineDistance.java:60-65).
+ * Replaces the List<FastDistanceVectorData> "trainData" cached by the ComQueue
+ * (BaseComQueue.java:497-527).  Rows whose values are all exactly representable in fp32 are kept
+ * as fp32 (4 B/value); the first value that is not switches the partition to fp64 losslessly. */
+int akm_upload_rows(akm_handle h, const double *x_host, int64_t n);
+
+/* Same for fp32 host rows (values widened exactly). */
+int akm_upload_rows_f32(akm_handle h, const float *x_host, int64_t n);
+
+/* Same, but the source already lives in device memory on the handle's device (used to measure
+ * the resident-data throughput and to feed data produced on the GPU). */
+int akm_upload_rows_device_f32(akm_handle h, const float *x_dev, int64_t n);
+
+/* Drops the cached partition (keeps the handle). */
+int akm_clear_rows(akm_handle h);
+
+/* Number of cached rows; storage kind: 4 = fp32, 8 = fp64. */
+int akm_num_rows(akm_handle h, int64_t *n_out, int *bytes_per_value_out);
+
+/* ------------------------------------------------------------------ per-superstep work, host buffers */
+
+/* Replaces KMeansAssignCluster.calc (CORE/operator/common/clustering/kmeans/KMeansAssignCluster.java:30-67)
+ * = KMeansUtil.updateSumMatrix for every cached sample (KMeansUtil.java:60-85) with
+ * FastDistance.calc(vector, matrix) (EuclideanDistance.java:109-116, CosineDistance.java:107-110)
+ * and getMinPointIndex (KMeansUtil.java:162-173).
+ *   centroids  k0 x d, as stored in FastDistanceMatrixData.vectors (already label-updated:
+ *              for COSINE the rows are unit vectors; stale rows >= k are zero)
+ *   k0         number of rows of the buffer (= the init matrix's numCols, KMeansPreallocateCentroid.java:22-39)
+ *   k          current cluster count (context "k"), only the first k centroids are candidates
+ *   sum_out    double[k0*(d+1)], fully overwritten ("Arrays.fill(sumMatrixData, 0.0)" then accumulate)
+ *   objective_out  nullable; sum over samples of min distance^2 (EUCLIDEAN) / min distance (COSINE)
+ *              against `centroids` (the reference train loop has no objective)
+ *   labels_out nullable int32[n]: closest cluster index per cached sample (updateSumMatrix's return) */
+int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k,
+                          double *sum_out, double *objective_out, int32_t *labels_out);
+
+/* Replaces KMeansUpdateCentroids.updateCentroids (KMeansUpdateCentroids.java:52-69) followed by the
+ * diagonal of KMeansIterTermination.calc (KMeansIterTermination.java:28-44).
+ *   sum        double[k0*(d+1)] after the all-reduce
+ *   step_no    ComContext.getStepNo(): the buffer written at an odd step is CENTROID1 (:38-42), which
+ *              fixes the order of the two label additions in the shift distance
+ *   prev       nullable k0 x d: the centroid buffer the assignment used (other ping-pong buffer);
+ *              when given, shift_out[j] = distance(prev_j, new_j) as the matrix x matrix path computes it
+ *   c_out      k0 x d, fully rewritten (zero fill, 1.0/weight scaling, empty clusters compacted away,
+ *              updateLabel over all k0 rows: COSINE renormalises)
+ *   k_out      new cluster count
+ *   shift_out  nullable double[k0] (first *k_out entries valid) */
+int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int step_no, const double *prev,
+                         double *c_out, int *k_out, double *shift_out);
+
+/* ------------------------------------------------------------------ device-resident iteration */
+
+/* KMeansPreallocateCentroid.calc (KMeansPreallocateCentroid.java:22-39) + KMeansUtil.buildCentroidsMatrix's
+ * updateLabel (KMeansUtil.java:35-45): publishes CENTROID1 = init, CENTROID2 = copy, K = k0, step = 0.
+ * c0 = k0 x d raw initial centroids (for COSINE they are normalised here, like updateLabel does). */
+int akm_set_centroids(akm_handle h, const double *c0, int k0);
+
+/* One superstep of KMeansTrainBatchOp.iterateICQ (KMeansTrainBatchOp.java:58-81) entirely on the
+ * device stream: KMeansAssignCluster -> AllReduce (NCCL when a communicator is attached, identity
+ * otherwise) -> KMeansUpdateCentroids -> KMeansIterTermination.  Only three scalars come back.
+ *   tol            epsilon (HasEpsilonDv00001.java:12-18)
+ *   converged_out  1 when every centroid moved < tol (the ComQueue criterion)
+ *   k_out          cluster count after the update
+ *   objective_out  nullable, objective of this assignment pass over ALL ranks */
+int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *objective_out);
+
+/* KMeansOutputModel.calc (KMeansOutputModel.java:37-80): newest centroid buffer (k0 x d, first *k_out
+ * rows are the model), weights[j] = count of cluster j in the LAST assignment pass read at the
+ * uncompacted index j (as the reference does), step counter. Any output may be NULL. */
+int akm_get_model(akm_handle h, double *c_out, int *k_out, double *weights_out, int *steps_out);
+
+/* Labels of the last assignment pass for the cached rows (int32[n]). */
+int akm_get_labels(akm_handle h, int32_t *labels_out);
+
+/* ------------------------------------------------------------------ AllReduce over NVLink (NCCL) */
+
+/* Replaces AllReduce(CENTROID_ALL_REDUCE) (CORE/common/comqueue/communication/AllReduce.java:85-120,
+ * SUM :125-133) inside akm_step.  id_out receives an ncclUniqueId (128 bytes) created on rank 0;
+ * the host side broadcasts it (Flink broadcast set / torch.distributed) and every rank calls
+ * akm_comm_init with it. */
+#define AKM_UNIQUE_ID_BYTES 128
+int akm_comm_unique_id(void *id_out);
+int akm_comm_init(akm_handle h, const void *id, int rank, int world);
+/* Stand-alone all-reduce (SUM, fp64) of a host buffer through the handle's communicator. */
+int akm_allreduce_sum(akm_handle h, double *buf, int64_t count);
+
+/* ------------------------------------------------------------------ prediction */
+
+/* Replaces KMeansModelMapper.map (CORE/operator/common/clustering/kmeans/KMeansModelMapper.java:62-97)
+ * for a micro-batch of n rows (the Java side batches inside mapPartition):
+ * prepareVectorData -> getClusterDistances -> getMinPointIndex.
+ *   x_host     n x d raw vectors; centroids = model matrix k x d as stored in the model rows
+ *              (updateLabel is applied here like transformTrainDataToPredictData does, KMeansUtil.java:246-260)
+ *   idx_out    int64[n]  = (long) index (:82); -1 when no distance is < Double.MAX_VALUE
+ *   dist_out   nullable double[n]   = clusterDistances[index]   (predictionDistanceCol, :91-93)
+ *   probs_out  nullable double[n*k] = getProbArrayFromDistanceArray (KMeansUtil.java:262-269), row-major,
+ *              indexed by centroid position (the caller scatters by clusterId, :85-88) */
+int akm_predict(akm_handle h, const double *x_host, int64_t n, const double *centroids, int k,
+                int64_t *idx_out, double *dist_out, double *probs_out);
+
+/* Prediction over the rows already cached on the device (KMeansPredictBatchOp over the training
+ * table); outputs as above. */
+int akm_predict_cached(akm_handle h, const double *centroids, int k,
+                       int64_t *idx_out, double *dist_out);
+
+/* ------------------------------------------------------------------ introspection (no reference counterpart) */
+
+/* Counters of the last assignment pass: rows decided by the tensor-core search alone, rows that
+ * were re-evaluated exactly, number of kernel launches issued by this handle so far. */
+typedef struct {
+    int64_t rows;
+    int64_t rows_certified;
+    int64_t rows_refined;
+    int64_t kernel_launches;
+    int32_t engine_used;      /* AKM_ENGINE_EXACT or AKM_ENGINE_TENSOR */
+    int32_t storage_bytes;    /* 4 or 8 */
+} akm_stats;
+int akm_get_stats(akm_handle h, akm_stats *out);
+
+/* Times `reps` back-to-back launches of one named kernel of the last configuration with CUDA events
+ * on the handle's stream; returns the average milliseconds per launch.  Used by bench.py for the
+ * roofline object. name: "assign" | "accumulate". */
+int akm_time_kernel(akm_handle h, const char *name, int reps, double *ms_out);
+
+/* Per-phase device timing of akm_step with CUDA events on the handle's stream (off by default).
+ * akm_get_profile fills out[0..4] = cumulative milliseconds of {nearest-centroid search, exact
+ * refinement, per-cluster accumulation, all-reduce + centroid update} and the number of steps
+ * counted; reset != 0 clears the counters.  No reference counterpart. */
+int akm_set_profiling(akm_handle h, int on);
+int akm_get_profile(akm_handle h, double *out5, int reset);
+
+/* Synthetic Gaussian-blob rows of SURVEY 8(d), generated on the device by a counter-based hash RNG
+ * (a pure function of seed and the global row index, so any shard can be produced independently):
+ *   centre[j] ~ U(-spread, spread)^d,  row r = fp32( centre[blob(r)] + sigma * N(0,1)^d ),
+ *   blob(r) = hash(seed, r) mod k_true.
+ * akm_blobs_append appends rows [row0, row0+n) to the cached partition (prepareVectorData included);
+ * akm_blobs_rows writes the m x d fp32 values of arbitrary global rows to host memory (used for the
+ * initial centroids "rows floor(i*N/k)" and for the CPU baseline's sample).  No reference counterpart. */
+int akm_blobs_append(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, int64_t row0, int64_t n);
+int akm_blobs_rows(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, const int64_t *rows,
+                   int64_t m, float *out_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AKM_H_ */

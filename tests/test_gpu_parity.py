@@ -1,0 +1,267 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle and the reference's golden vectors.
+
+Bars (BASELINE.json north_star): assignments bit-exact (documented ties aside -- none are needed
+here: both engines reproduce Java's first-minimum rule exactly), centroids and objective within
+1e-6 relative (the tests use 1e-9 or tighter; the update step is bit-exact)."""
+import numpy as np
+import pytest
+
+import oracle as orc
+from alink_b200 import native
+
+pytestmark = pytest.mark.gpu
+
+ENGINES = [native.ENGINE_EXACT, native.ENGINE_AUTO]
+
+
+def blobs(n, d, k, seed, fp32=True, spread=10.0):
+    rng = np.random.default_rng(seed)
+    centers = rng.uniform(-spread, spread, size=(k, d))
+    X = centers[rng.integers(0, k, size=n)] + rng.normal(size=(n, d))
+    if fp32:
+        X = X.astype(np.float32).astype(np.float64)
+    return X
+
+
+def oracle_pass(metric, X, C, k=None):
+    Xp, xl = orc.prepare_rows(metric, X)
+    Cp, cl = orc.prepare_centroids(metric, C)
+    s, labels, mind = orc.assign_accumulate(metric, Xp, xl, Cp, cl, k=k)
+    obj = float((mind ** 2).sum()) if metric == orc.EUCLIDEAN else float(mind.sum())
+    return Cp, s, labels, mind, obj
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+@pytest.mark.parametrize("n,d,k", [(1, 3, 1), (63, 5, 2), (64, 64, 37), (65, 130, 100), (5000, 128, 257),
+                                   (3000, 784, 10), (4097, 16, 1000)])
+def test_assign_accumulate_matches_oracle(engine, metric, n, d, k):
+    X = blobs(n, d, max(k, 2), seed=n + d + k)
+    C = X[np.linspace(0, n - 1, k).astype(int)].copy() if n >= k else blobs(k, d, k, seed=1)
+    Cp, s_ref, l_ref, _, obj_ref = oracle_pass(metric, X, C)
+    with native.Handle(d, metric) as h:
+        h.set_engine(engine)
+        h.upload_rows(X)
+        s, obj, labels = h.assign_accumulate(Cp, want_labels=True)
+    assert (labels == l_ref).all()
+    L = s.reshape(k, d + 1)
+    R = s_ref.reshape(k, d + 1)
+    assert (L[:, d] == R[:, d]).all()                       # counts are exact
+    np.testing.assert_allclose(L, R, rtol=1e-12, atol=1e-9)
+    assert abs(obj - obj_ref) <= 1e-9 * max(1.0, abs(obj_ref))
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_storage_fp32_exact_vs_fp64_and_lossless_migration(engine):
+    d, k = 24, 9
+    Xa = blobs(700, d, k, seed=3, fp32=True)
+    Xb = blobs(900, d, k, seed=4, fp32=False)                # not fp32-representable
+    C = Xa[:k].copy()
+    with native.Handle(d, native.EUCLIDEAN) as h:
+        h.set_engine(engine)
+        h.upload_rows(Xa)
+        assert h.num_rows() == (700, 4)
+        h.upload_rows(Xb)                                    # switches the partition to fp64, losslessly
+        assert h.num_rows() == (1600, 8)
+        s, obj, labels = h.assign_accumulate(C, want_labels=True)
+    X = np.vstack([Xa, Xb])
+    _, s_ref, l_ref, _, obj_ref = oracle_pass(orc.EUCLIDEAN, X, C)
+    assert (labels == l_ref).all()
+    np.testing.assert_allclose(s, s_ref, rtol=1e-12, atol=1e-9)
+    assert abs(obj - obj_ref) <= 1e-9 * abs(obj_ref)
+
+
+def test_float32_upload_equals_double_upload():
+    d, k = 20, 6
+    X = blobs(1000, d, k, seed=5)
+    C = X[:k].copy()
+    with native.Handle(d, native.EUCLIDEAN) as h1, native.Handle(d, native.EUCLIDEAN) as h2:
+        h1.upload_rows(X)
+        h2.upload_rows(X.astype(np.float32))
+        s1, o1, l1 = h1.assign_accumulate(C, want_labels=True)
+        s2, o2, l2 = h2.assign_accumulate(C, want_labels=True)
+    assert (l1 == l2).all() and (s1 == s2).all()
+
+
+def test_update_centroids_golden_and_bit_exact(golden):
+    g = golden["update_centroids"]
+    with native.Handle(g["d"], native.EUCLIDEAN) as h:
+        C, nk, _ = h.update_centroids(g["buffer"], g["k"], g["k"])
+    assert nk == g["new_k"]
+    np.testing.assert_allclose(C.ravel(), g["centroids"], atol=g["tol"])
+    # random buffers with empty clusters: bit-exact against the oracle, both metrics, incl. shift
+    rng = np.random.default_rng(11)
+    for metric in (native.EUCLIDEAN, native.COSINE):
+        k0, d = 57, 19
+        buf = rng.normal(size=(k0, d + 1))
+        buf[:, d] = rng.integers(0, 5, size=k0)
+        prev = rng.normal(size=(k0, d))
+        prev_p, prev_l = orc.prepare_centroids(metric, prev)
+        C_ref, cl_ref, nk_ref = orc.update_centroids(metric, buf.ravel(), k0, k0, d)
+        for step_no in (1, 2):
+            with native.Handle(d, metric) as h:
+                C, nk, shift = h.update_centroids(buf.ravel(), k0, k0, step_no=step_no, prev=prev_p)
+            assert nk == nk_ref
+            assert (C == C_ref).all()
+            if step_no % 2 == 1:   # new buffer is CENTROID1
+                _, diag = orc.converged(metric, C_ref, cl_ref, prev_p, prev_l, nk_ref, 1e-4)
+            else:
+                _, diag = orc.converged(metric, prev_p, prev_l, C_ref, cl_ref, nk_ref, 1e-4)
+            assert (shift == diag).all()
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_training_loop_matches_oracle(engine, metric):
+    n, d, k = 6000, 48, 40
+    X = blobs(n, d, 25, seed=21)                            # fewer blobs than centroids: splits + near ties
+    C0 = X[np.random.default_rng(2).choice(n, k, replace=False)].copy()
+    ref = orc.train(metric, X, C0, max_iter=12, tol=1e-4)
+    with native.Handle(d, metric) as h:
+        h.set_engine(engine)
+        h.upload_rows(X)
+        m = h.train(C0, max_iter=12, tol=1e-4)
+        labels = h.get_labels()
+    assert m["iters"] == ref["iters"] and m["k"] == ref["k"]
+    assert (labels == ref["labels"]).all()
+    np.testing.assert_allclose(m["C"][: m["k"]], ref["C"][: ref["k"]], rtol=1e-9, atol=1e-12)
+    assert (m["weights"] == ref["weights"]).all()
+    np.testing.assert_allclose(m["objective"], ref["objective"], rtol=1e-9)
+
+
+def test_empty_clusters_are_dropped_like_the_reference():
+    X = np.array([[0.0], [0.1], [10.0], [10.1]])
+    C0 = np.array([[0.0], [100.0], [10.0]])
+    ref = orc.train(orc.EUCLIDEAN, X, C0, max_iter=5, tol=0.0)
+    with native.Handle(1, native.EUCLIDEAN) as h:
+        h.upload_rows(X)
+        m = h.train(C0, max_iter=5, tol=0.0)
+        labels = h.get_labels()
+    assert m["k"] == ref["k"] == 2
+    assert (m["C"] == ref["C"]).all()
+    assert labels.tolist() == [0, 0, 1, 1]
+    assert (m["weights"] == ref["weights"]).all()
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_exact_ties_first_index_wins(engine):
+    d = 32
+    X = blobs(2000, d, 4, seed=8)
+    base = X[:5].copy()
+    C = np.vstack([base, base, base[::-1]])                 # every centroid appears three times
+    _, s_ref, l_ref, _, _ = oracle_pass(orc.EUCLIDEAN, X, C)
+    assert l_ref.max() < 5                                  # duplicates never win
+    with native.Handle(d, native.EUCLIDEAN) as h:
+        h.set_engine(engine)
+        h.upload_rows(X)
+        s, _, labels = h.assign_accumulate(C, want_labels=True)
+    assert (labels == l_ref).all()
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_near_ties_are_resolved_exactly(engine, metric):
+    # centroids that differ by a few ulps / 1e-7 relative: the tensor-core search must hand these rows
+    # to the exact evaluation, and the exact evaluation must reproduce Java's rounding.
+    rng = np.random.default_rng(5)
+    d, kb = 128, 16
+    base = rng.uniform(-10, 10, size=(kb, d))
+    C = np.vstack([base, base * (1 + 1e-7), base + 1e-9, base * (1 - 3e-8), np.nextafter(base, np.inf)])
+    X = (base[rng.integers(0, kb, size=4000)] + 0.5 * rng.normal(size=(4000, d))).astype(np.float32).astype(np.float64)
+    Cp, s_ref, l_ref, _, _ = oracle_pass(metric, X, C)
+    with native.Handle(d, metric) as h:
+        h.set_engine(engine)
+        h.upload_rows(X)
+        s, _, labels = h.assign_accumulate(Cp, want_labels=True)
+        st = h.stats()
+    assert (labels == l_ref).all(), "mismatches: %d" % int((labels != l_ref).sum())
+    if st["engine_used"] == native.ENGINE_TENSOR:
+        assert st["rows_refined"] > 0
+
+
+def test_only_the_first_k_centroids_are_candidates():
+    d = 8
+    X = blobs(500, d, 3, seed=9)
+    C = np.vstack([X[:4], np.zeros((3, d))])                # stale zero rows beyond k, as after a drop
+    Cp, s_ref, l_ref, _, _ = oracle_pass(orc.EUCLIDEAN, X, C, k=4)
+    with native.Handle(d, native.EUCLIDEAN) as h:
+        h.upload_rows(X)
+        s, _, labels = h.assign_accumulate(Cp, k=4, want_labels=True)
+    assert (labels == l_ref).all() and labels.max() < 4
+    np.testing.assert_allclose(s, s_ref, rtol=1e-12, atol=1e-9)
+
+
+def test_nan_rows_fail_like_java():
+    d = 4
+    X = blobs(100, d, 2, seed=1)
+    X[17, 2] = np.nan
+    with native.Handle(d, native.EUCLIDEAN) as h:
+        h.upload_rows(X)
+        with pytest.raises(native.AkmError) as e:
+            h.assign_accumulate(X[:2].copy())
+        assert e.value.code == -5                            # Java: ArrayIndexOutOfBounds on index -1
+
+
+def test_empty_partition_and_argument_errors():
+    with native.Handle(3, native.EUCLIDEAN) as h:
+        s, obj, _ = h.assign_accumulate(np.ones((2, 3)))
+        assert (s == 0).all() and obj == 0.0
+        with pytest.raises(native.AkmError):
+            h.step()                                         # no centroids yet -> STATE
+        with pytest.raises(ValueError):
+            h.upload_rows(np.ones((2, 4)))
+
+
+def test_predict_golden_detail_string_bit_exact(golden):
+    from alink_b200.javafmt import java_vector_to_string
+    g = golden["model_mapper"]
+    C = np.array(golden["kmeans_util"]["centroids"])
+    with native.Handle(3, native.EUCLIDEAN) as h:
+        idx, dist, probs = h.predict(np.array([g["row"]], dtype=np.float64), C, want_dist=True, want_probs=True)
+    assert idx[0] == g["pred"]
+    assert abs(dist[0] - g["distance"]) <= g["distance_tol"]
+    assert java_vector_to_string(probs[0]) == g["detail_exact"]
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_predict_matches_oracle_bitwise(engine, metric):
+    n, d, k = 3000, 40, 23
+    X = blobs(n, d, k, seed=31, fp32=False)
+    C = blobs(k, d, k, seed=32, fp32=False)
+    idx_r, dist_r, probs_r = orc.predict(metric, X, C, want_dist=True, want_probs=True)
+    with native.Handle(d, metric) as h:
+        h.set_engine(engine)
+        idx, dist, probs = h.predict(X, C, want_dist=True, want_probs=True)
+        idx2, dist2, _ = h.predict(X, C, want_dist=True, want_probs=False)
+    assert (idx == idx_r).all() and (idx2 == idx_r).all()
+    assert (dist == dist_r).all() and (dist2 == dist_r).all()   # Math.sqrt / fp64 order reproduced bit for bit
+    assert (probs == probs_r).all()
+
+
+def test_six_point_pipeline_golden(golden):
+    g = golden["pipeline_6_points"]
+    X = np.array(g["rows"], dtype=np.float64)
+    with native.Handle(3, native.EUCLIDEAN) as h:
+        h.upload_rows(X)
+        m = h.train(X[[0, 3]], max_iter=20, tol=1e-4)
+        idx, dist = h.predict_cached(m["C"][: m["k"]])
+    np.testing.assert_allclose(dist, g["pred_distances"], atol=g["tol"])
+    want = np.array(g["pred_up_to_permutation"])
+    assert (idx == want).all() or (idx == 1 - want).all()
+    assert abs(float((dist ** 2).sum()) - g["ssw"]) <= 0.01
+
+
+def test_iris_config1():
+    # BASELINE config 1: iris k=3 (sklearn's bundled copy; the reference fetches it over HTTP)
+    from sklearn.datasets import load_iris
+    X = load_iris().data.astype(np.float64)
+    C0 = X[[0, 50, 100]].copy()
+    ref = orc.train(orc.EUCLIDEAN, X, C0, max_iter=20, tol=1e-4)
+    with native.Handle(4, native.EUCLIDEAN) as h:
+        h.upload_rows(X)
+        assert h.num_rows()[1] == 8                          # 5.1 etc. are not fp32-representable
+        m = h.train(C0, max_iter=20, tol=1e-4)
+        labels = h.get_labels()
+    assert m["iters"] == ref["iters"] and (labels == ref["labels"]).all()
+    np.testing.assert_allclose(m["C"][:3], ref["C"][:3], rtol=1e-12)
