@@ -244,6 +244,14 @@ static int run_assign(akm_handle h, RowStore &rs, const double *C, const double 
     return launch_assign_exact(h, rs, nullptr, rs.n, C, clabel, k0, k, labels, mind, nullptr);
 }
 
+// h_iscal[4] (rows handed to the exact refinement by the tensor search) was copied back by the caller
+static void absorb_tensor_stats(akm_handle h) {
+    if (h->stats.engine_used == AKM_ENGINE_TENSOR) {
+        h->stats.rows_refined = h->h_iscal[4];
+        h->stats.rows_certified = h->stats.rows - h->h_iscal[4];
+    }
+}
+
 static int check_error_flag(akm_handle h) {
     // h_iscal[2] was copied back by the caller
     if (h->h_iscal[2] != 0) {
@@ -404,10 +412,11 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
     AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], k0, s->sum, s->sum + L));
     AKM_CUDA(h, cudaMemcpyAsync(sum_out, s->sum, sizeof(double) * L, cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     if (labels_out)
         AKM_CUDA(h, cudaMemcpyAsync(labels_out, h->labels, sizeof(int32_t) * (size_t)h->rows.n, cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    absorb_tensor_stats(h);
     if (objective_out) *objective_out = h->h_dscal[0];
     return check_error_flag(h);
 }
@@ -477,9 +486,10 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     AKM_TRY(launch_update(h, h->sum, h->k, k0, h->cent[wr], h->clabel[wr], h->cent[rd], h->clabel[rd],
                           /*new_is_c1=*/wr == 0, tol, h->shift, h->iscal));
     if (prof) cudaEventRecord(h->pev[3], h->stream);
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 3 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 6 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    absorb_tensor_stats(h);
     h->k = h->h_iscal[0];
     if (prof) {
         float a = 0.f, b = 0.f, c = 0.f, m1 = 0.f;
@@ -571,8 +581,9 @@ static int predict_store(akm_handle h, RowStore &rs, const double *dC, const dou
     AKM_TRY(launch_labels_to_i64(h, h->labels, n, s->idx64));
     AKM_CUDA(h, cudaMemcpyAsync(idx_out, s->idx64, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
     if (dist_out) AKM_CUDA(h, cudaMemcpyAsync(dist_out, h->mind, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (!probs_out) absorb_tensor_stats(h);
     if (h->h_iscal[2] != 0) {
         cudaMemsetAsync(h->iscal + 2, 0, sizeof(int), h->stream);
         // Java: (long) -1 is emitted; reading clusterDistances[-1] throws only when a distance/detail column is asked for

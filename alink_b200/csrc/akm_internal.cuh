@@ -24,6 +24,7 @@ struct RowStore {
     __half *x16 = nullptr;
     float2 *xerr = nullptr;
     int d16 = 0;              // row stride of x16 in elements (multiple of 8)
+    int64_t x16_cap = 0;      // rows allocated for x16 / xerr
     bool want16 = false;
     int x16_shift = 0;        // x16 = fp16(x * 2^x16_shift)
     bool x16_valid = false;
@@ -108,6 +109,8 @@ int launch_prepare_centroids(akm_handle h, double *C, double *clabel, int k0, bo
 int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist, int64_t nrows,
                         const double *C, const double *clabel, int k0, int k, int32_t *labels,
                         double *mind, double *dist_all);
+int launch_assign_exact_list(akm_handle h, const RowStore &rs, const int32_t *rowlist, const int *count_dev,
+                             const double *C, const double *clabel, int k0, int k, int32_t *labels);
 // per-cluster sums/counts (+ objective) from labels
 int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C,
                       int k0, double *sum, double *objective);

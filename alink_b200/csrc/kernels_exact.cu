@@ -182,15 +182,18 @@ constexpr int AE_TR = 64, AE_TC = 64, AE_KC = 32, AE_LD = 66;
 template <typename T, int METRIC, bool INDIRECT>
 __global__ void __launch_bounds__(256)
 assign_exact_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, const int32_t *__restrict__ rowlist,
-                    int64_t nrows, int d, const double *__restrict__ C, const double *__restrict__ clabel, int k,
-                    int32_t *__restrict__ labels, double *__restrict__ mind, double *__restrict__ dist_all, int kd,
-                    int *__restrict__ err_flag) {
+                    int64_t nrows_arg, const int *__restrict__ nrows_dev, int d, const double *__restrict__ C,
+                    const double *__restrict__ clabel, int k, int32_t *__restrict__ labels, double *__restrict__ mind,
+                    double *__restrict__ dist_all, int kd, int *__restrict__ err_flag) {
     __shared__ __align__(16) double xs[AE_KC][AE_LD];
     __shared__ __align__(16) double cs[AE_KC][AE_LD];
     __shared__ int64_t srow[AE_TR];
     const int tid = threadIdx.x;
     const int tr = tid >> 4, tc = tid & 15;
-    const int64_t base = (int64_t)blockIdx.x * AE_TR;
+    const int64_t nrows = nrows_dev ? (int64_t)(*nrows_dev) : nrows_arg;   // list length may live on the device
+  for (int64_t tile = blockIdx.x; tile * AE_TR < nrows; tile += gridDim.x) {
+    const int64_t base = tile * AE_TR;
+    __syncthreads();
     if (tid < AE_TR) {
         const int64_t p = base + tid;
         int64_t r = -1;
@@ -298,6 +301,7 @@ assign_exact_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, 
             }
         }
     }
+  }
 }
 
 int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist, int64_t nrows, const double *C,
@@ -307,7 +311,7 @@ int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist
     const unsigned grid = (unsigned)ceil_div64(nrows, AE_TR);
     int *err = h->iscal + 2;
 #define AE_LAUNCH(T, PTR, M, IND)                                                                        \
-    assign_exact_kernel<T, M, IND><<<grid, 256, 0, h->stream>>>(PTR, rs.xlabel, rowlist, nrows, h->d, C, clabel, k, \
+    assign_exact_kernel<T, M, IND><<<grid, 256, 0, h->stream>>>(PTR, rs.xlabel, rowlist, nrows, nullptr, h->d, C, clabel, k, \
                                                                 labels, mind, dist_all, k, err)
     const bool ind = rowlist != nullptr;
     if (h->metric == AKM_EUCLIDEAN) {
@@ -317,6 +321,24 @@ int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist
         if (ind) AE_LAUNCH(double, rs.x64, AKM_COSINE, true); else AE_LAUNCH(double, rs.x64, AKM_COSINE, false);
     }
 #undef AE_LAUNCH
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+// Exact assignment of the rows in a device-resident list whose length also lives on the device
+// (no host round trip between the tensor-core search and its exact fallback).
+int launch_assign_exact_list(akm_handle h, const RowStore &rs, const int32_t *rowlist, const int *count_dev,
+                             const double *C, const double *clabel, int k0, int k, int32_t *labels) {
+    (void)k0;
+    const unsigned grid = (unsigned)(h->num_sms * 4);
+    int *err = h->iscal + 2;
+#define AEL_LAUNCH(T, PTR, M)                                                                                  \
+    assign_exact_kernel<T, M, true><<<grid, 256, 0, h->stream>>>(PTR, rs.xlabel, rowlist, 0, count_dev, h->d, C, clabel, k, \
+                                                                 labels, nullptr, nullptr, k, err)
+    if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) AEL_LAUNCH(float, rs.x32, AKM_EUCLIDEAN); else AEL_LAUNCH(double, rs.x64, AKM_EUCLIDEAN); }
+    else AEL_LAUNCH(double, rs.x64, AKM_COSINE);
+#undef AEL_LAUNCH
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     return AKM_OK;

@@ -1,9 +1,843 @@
-// tcgen05 / TMA nearest-centroid search (placeholder until the tensor path lands).
+// Nearest-centroid search on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), with a
+// rigorous per-row certificate and exact re-evaluation of every row the certificate does not cover.
+//
+//   search_kernel        S[n, j] = ||c_j||^2 - 2 x16_n . c16_j   (EUCLIDEAN)   /   - x16_n . c16_j   (COSINE)
+//                        fp16 operands (scaled by powers of two), fp32 accumulation in TMEM, the running
+//                        minimum and the set {j : S[n,j] <= min + W_n} fused in the epilogue.
+//   W_n                  = 2 * (bound on |S - true score|) + 2 * (bound on Java's own fp64 rounding), from
+//                        per-row ||x||, ||x - x16|| and per-pass max ||c||, max ||c - c16|| (Cauchy-Schwarz).
+//                        If exactly one centroid is inside the window, Java's argmin (KMeansUtil.java:162-173)
+//                        is that centroid -- no tie is possible -- and the row is "certified".
+//   refine_candidates    rows with 2..4 candidates: fp64 evaluation of just those centroids; a clear winner
+//                        (gap above the fp64 error bound of both evaluations) decides the row.
+//   assign_exact (list)  everything else (true ties, > 4 candidates, non-finite data) is evaluated against
+//                        all k centroids in the exact Java operation order (kernels_exact.cu).
+// The result is therefore identical to the exact engine by construction; the tensor cores only prune.
+//
+// Data movement: X16 tiles (128 rows x 64 halfs, 128B-swizzled) and centroid tiles arrive by TMA; centroid
+// tiles are multicast across a 2-CTA cluster so each SM pulls half of them from L2.  One CTA keeps
+// MB x 128 rows resident while all centroid tiles stream past; accumulators are double buffered in TMEM
+// so the epilogue of tile t overlaps the MMAs of tile t+1.
+#include <cuda.h>
+#include <cfloat>
+#include <cmath>
+
 #include "akm_internal.cuh"
 
-bool tensor_supported(akm_handle, int) { return false; }
-int tensor_assign(akm_handle h, RowStore &, const double *, const double *, int, int, int32_t *, double *) {
-    return akm_fail(h, AKM_ERR_UNSUPPORTED, "tensor engine not built");
+// ------------------------------------------------------------------------------------------ PTX helpers
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
-int tensor_prepare_x16(akm_handle, RowStore &) { return AKM_OK; }
-void tensor_free(akm_handle) {}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug must end in a trap, never in a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 24)) __trap();
+    }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1,
+                                               uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%4, %5}], [%2], %3;"
+        ::"r"(dst), "l"(map), "r"(bar), "h"(mask), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, M = 128, N = 128, K = 16, fp16 x fp16 -> fp32
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, 128B-swizzled operand tile (rows x 64 halfs, 128 B per row, 8-row atoms of 1024 B):
+// start address >> 4 | LBO = 1 | SBO = 1024 B >> 4 | version 1 (sm_100) | layout SWIZZLE_128B
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16: D = F32 (bit 4), A = B = F16 (0), both K-major, N = 128 (>>3 at bit 17), M = 128 (>>4 at bit 24)
+constexpr uint32_t IDESC_F16_128x128 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------ constants
+constexpr int TILE_M = 128;           // rows per MMA (TMEM lanes)
+constexpr int TILE_N = 128;           // centroids per tile (TMEM columns per accumulator)
+constexpr int KBLK = 64;              // halfs per 128-byte swizzled row
+constexpr int BOX_BYTES = TILE_M * KBLK * 2;   // 16 KB
+constexpr int MAX_CAND = 4;
+constexpr int MAX_BSLOTS = 16;
+constexpr float PAD_SCORE = 1.0e30f;  // score offset of padding centroids (never candidates)
+
+// per-pass constants produced by c16_build_kernel
+struct PassConst {
+    float c16_max;     // max_j ||c16_j / scale||   (rounded up)
+    float dc_max;      // max_j ||c_j - c16_j / scale||
+    float c_max;       // max_j ||c_j||
+    float score_scale; // -2 * 2^-(sx+sc) (EUCLIDEAN) or -2^-(sx+sc) (COSINE)
+    int sc;            // centroid scale exponent
+    int bad;           // non-finite centroid: tensor search disabled for this pass
+};
+
+struct SearchParams {
+    int64_t n;              // rows
+    int groups;             // row groups of MB*128 rows
+    int ntiles;             // centroid tiles of 128
+    int a_stages, b_slots, resident;
+    int d, metric, k;
+    const float *cn;        // ntiles*128 score offsets
+    const PassConst *pc;
+    const float2 *xerr;     // per row {||x||, ||x - x16||}
+    int32_t *labels;
+    int32_t *wl_rows;       // worklist: rows that need exact work
+    int32_t *wl_cand;       // MAX_CAND candidates per entry (-1 = unused, first == -2: all centroids)
+    int *counters;          // [0] worklist length
+    float eta;              // accumulation error factor
+};
+
+// ------------------------------------------------------------------------------------------ search kernel
+template <int MB, int KB, int CL>
+__global__ void __launch_bounds__(64 + 128 * MB, 1)
+search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__ CUtensorMap tmapC,
+              const SearchParams p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // SWIZZLE_128B atoms need 1024-B alignment
+    constexpr int A_STAGE = MB * KB * BOX_BYTES;
+    constexpr int B_STAGE = KB * BOX_BYTES;
+    constexpr int TMEM_COLS = (MB == 2) ? 512 : 256;
+    constexpr int EPI_WARPS = 4 * MB;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = (CL > 1) ? cluster_ctarank() : 0;
+    const int cluster_id = blockIdx.x / CL, nclusters = gridDim.x / CL;
+
+    unsigned char *a_smem = smem;
+    unsigned char *b_smem = smem + (size_t)p.a_stages * A_STAGE;
+    float *cn_s = reinterpret_cast<float *>(b_smem + (size_t)p.b_slots * B_STAGE);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(cn_s + p.ntiles * TILE_N);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *b_full = bars + 4, *b_empty = b_full + MAX_BSLOTS,
+             *t_full = b_empty + MAX_BSLOTS, *t_empty = t_full + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
+    float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);   // 5 floats
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
+        for (int i = 0; i < MAX_BSLOTS; ++i) { mbar_init(smem_u32(b_full + i), 1); mbar_init(smem_u32(b_empty + i), CL); }
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), EPI_WARPS); }
+        fence_barrier_init();
+        pc_s[0] = p.pc->c16_max; pc_s[1] = p.pc->dc_max; pc_s[2] = p.pc->c_max; pc_s[3] = p.pc->score_scale;
+        pc_s[4] = p.pc->bad ? 1.f : 0.f;
+    }
+    for (int i = threadIdx.x; i < p.ntiles * TILE_N; i += blockDim.x) cn_s[i] = p.cn[i];
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    if (CL > 1) cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // super-groups handled by this cluster: sg = cluster_id, cluster_id + nclusters, ...; this CTA's group = sg*CL + rank
+    const int nsuper = (p.groups + CL - 1) / CL;
+
+    if (warp == 0) {
+        // =============================== TMA producer
+        if (lane == 0) {
+            const uint16_t mc_mask = (uint16_t)((1u << CL) - 1);
+            constexpr int SLICE_ROWS = TILE_N / CL;                    // centroid rows this CTA fetches per tile
+            auto load_b = [&](int slot, int tile) {
+                const uint32_t bar = smem_u32(b_full + slot);
+                mbar_expect_tx(bar, B_STAGE);
+                for (int kb = 0; kb < KB; ++kb) {
+                    const uint32_t dst = smem_u32(b_smem + (size_t)slot * B_STAGE + kb * BOX_BYTES) + rank * SLICE_ROWS * 128;
+                    if (CL > 1) tma_load_2d_mc(dst, &tmapC, bar, kb * KBLK, tile * TILE_N + rank * SLICE_ROWS, mc_mask);
+                    else tma_load_2d(dst, &tmapC, bar, kb * KBLK, tile * TILE_N);
+                }
+            };
+            auto load_a = [&](int it, int sg) {
+                const int as = it % p.a_stages;
+                const uint32_t ph = (it / p.a_stages) & 1;
+                mbar_wait(smem_u32(a_empty + as), ph ^ 1);
+                const uint32_t bar = smem_u32(a_full + as);
+                mbar_expect_tx(bar, A_STAGE);
+                const int64_t row0 = ((int64_t)sg * CL + rank) * (MB * TILE_M);
+                for (int rb = 0; rb < MB; ++rb)
+                    for (int kb = 0; kb < KB; ++kb)
+                        tma_load_2d(smem_u32(a_smem + (size_t)as * A_STAGE + (rb * KB + kb) * BOX_BYTES), &tmapX, bar,
+                                    kb * KBLK, (int)(row0 + rb * TILE_M));
+            };
+            if (p.resident)
+                for (int t = 0; t < p.ntiles; ++t) load_b(t, t);
+            int a_it = 0, b_it = 0;
+            if (cluster_id < nsuper) load_a(a_it++, cluster_id);
+            for (int sg = cluster_id; sg < nsuper; sg += nclusters) {
+                const bool more = sg + nclusters < nsuper;
+                if (p.resident) {
+                    if (more) load_a(a_it++, sg + nclusters);                  // prefetch the next group's rows
+                } else {
+                    for (int t = 0; t < p.ntiles; ++t, ++b_it) {
+                        const int slot = b_it % p.b_slots;
+                        const uint32_t ph = (b_it / p.b_slots) & 1;
+                        mbar_wait(smem_u32(b_empty + slot), ph ^ 1);
+                        load_b(slot, t);
+                        // next group's rows go out after this group's first centroid tile, so the tile
+                        // stream never waits behind the (longer) wait for a free row stage
+                        if (more && t == 0) load_a(a_it++, sg + nclusters);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // =============================== MMA issuer (one thread)
+        int a_it = 0, b_it = 0, t_it = 0;
+        for (int sg = cluster_id; sg < nsuper; sg += nclusters, ++a_it) {
+            const int as = a_it % p.a_stages;
+            mbar_wait(smem_u32(a_full + as), (a_it / p.a_stages) & 1);
+            for (int t = 0; t < p.ntiles; ++t, ++b_it, ++t_it) {
+                const int slot = p.resident ? t : (b_it % p.b_slots);
+                mbar_wait(smem_u32(b_full + slot), p.resident ? 0u : (uint32_t)((b_it / p.b_slots) & 1));
+                const int tb = t_it & 1;
+                mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
+                tc_fence_after();
+                if (lane == 0) {
+#pragma unroll
+                    for (int rb = 0; rb < MB; ++rb) {
+                        const uint32_t d_tmem = tmem_base + (uint32_t)(tb * MB * TILE_N + rb * TILE_N);
+#pragma unroll
+                        for (int kb = 0; kb < KB; ++kb) {
+                            const uint64_t ad = make_desc(smem_u32(a_smem + (size_t)as * A_STAGE + (rb * KB + kb) * BOX_BYTES));
+                            const uint64_t bd = make_desc(smem_u32(b_smem + (size_t)slot * B_STAGE + kb * BOX_BYTES));
+#pragma unroll
+                            for (int k4 = 0; k4 < KBLK / 16; ++k4)
+                                umma_f16(d_tmem, ad + 2 * k4, bd + 2 * k4, IDESC_F16_128x128, (kb | k4) != 0);
+                        }
+                    }
+                    if (!p.resident) {
+                        if (CL > 1) umma_commit_mc(smem_u32(b_empty + slot), (uint16_t)((1u << CL) - 1));
+                        else umma_commit(smem_u32(b_empty + slot));
+                    }
+                    umma_commit(smem_u32(t_full + tb));
+                }
+                __syncwarp();
+            }
+            if (lane == 0) umma_commit(smem_u32(a_empty + as));
+            __syncwarp();
+        }
+    } else {
+        // =============================== epilogue: one thread per row
+        const int e = warp - 2;
+        const int rb = e >> 2;
+        const int q = warp & 3;                       // TMEM lane quadrant this warp may read
+        const float c16_max = pc_s[0], dc_max = pc_s[1], c_max = pc_s[2], scale = pc_s[3];
+        int t_it = 0;
+        for (int sg = cluster_id; sg < nsuper; sg += nclusters) {
+            const int64_t row = (((int64_t)sg * CL + rank) * MB + rb) * TILE_M + q * 32 + lane;
+            const bool valid = row < p.n;
+            float W = 0.f;
+            if (valid) {
+                const float2 xe = p.xerr[row];
+                const float r = xe.x, er = xe.y;
+                const float rc = r + c_max;
+                // |S - true| <= 2(|dx||c16| + |x||dc|) + 2 eta |x16||c16| + fp32 epilogue rounding
+                const float B = 2.f * (er * c16_max + r * dc_max) + 2.f * p.eta * (r + er) * c16_max + 4.8e-7f * rc * rc;
+                const float epsJ = (float)(p.d + 16) * 4.5e-16f * rc * rc;    // Java's own fp64 rounding
+                W = 2.004f * B + 2.f * epsJ + 1e-30f;
+                if (pc_s[4] != 0.f) W = NAN;                                  // non-finite centroids: everything goes exact
+            }
+            float m = INFINITY, thr = INFINITY;
+            int best = -1;
+            float cs[MAX_CAND];
+            int ci[MAX_CAND];
+#pragma unroll
+            for (int i = 0; i < MAX_CAND; ++i) { cs[i] = INFINITY; ci[i] = -1; }
+            float dropped = INFINITY;
+
+            for (int t = 0; t < p.ntiles; ++t, ++t_it) {
+                const int tb = t_it & 1;
+                mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * MB * TILE_N + rb * TILE_N);
+#pragma unroll 1
+                for (int c0 = 0; c0 < TILE_N; c0 += 32) {
+                    uint32_t v[32];
+                    __syncwarp();                      // tcgen05.ld is warp-collective: reconverge after the candidate branch
+                    tmem_ld32(taddr + c0, v);
+                    tmem_ld_wait();
+                    const float *cn_t = cn_s + t * TILE_N + c0;
+#pragma unroll
+                    for (int g8 = 0; g8 < 4; ++g8) {
+                        float s[8];
+                        const float4 o0 = *reinterpret_cast<const float4 *>(cn_t + g8 * 8);
+                        const float4 o1 = *reinterpret_cast<const float4 *>(cn_t + g8 * 8 + 4);
+                        s[0] = fmaf(__uint_as_float(v[g8 * 8 + 0]), scale, o0.x);
+                        s[1] = fmaf(__uint_as_float(v[g8 * 8 + 1]), scale, o0.y);
+                        s[2] = fmaf(__uint_as_float(v[g8 * 8 + 2]), scale, o0.z);
+                        s[3] = fmaf(__uint_as_float(v[g8 * 8 + 3]), scale, o0.w);
+                        s[4] = fmaf(__uint_as_float(v[g8 * 8 + 4]), scale, o1.x);
+                        s[5] = fmaf(__uint_as_float(v[g8 * 8 + 5]), scale, o1.y);
+                        s[6] = fmaf(__uint_as_float(v[g8 * 8 + 6]), scale, o1.z);
+                        s[7] = fmaf(__uint_as_float(v[g8 * 8 + 7]), scale, o1.w);
+                        const float cm = fminf(fminf(fminf(s[0], s[1]), fminf(s[2], s[3])),
+                                               fminf(fminf(s[4], s[5]), fminf(s[6], s[7])));
+                        if (cm <= thr) {
+                            const int j0 = t * TILE_N + c0 + g8 * 8;
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                if (s[i] <= thr) {
+                                    dropped = fminf(dropped, cs[MAX_CAND - 1]);
+#pragma unroll
+                                    for (int u = MAX_CAND - 1; u > 0; --u) { cs[u] = cs[u - 1]; ci[u] = ci[u - 1]; }
+                                    cs[0] = s[i];
+                                    ci[0] = j0 + i;
+                                    if (s[i] < m) { m = s[i]; best = j0 + i; thr = m + W; }
+                                }
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(t_empty + tb));
+            }
+            // ---- certificate
+            bool need_exact = false;
+            int cand[MAX_CAND];
+            if (valid) {
+                const float thrF = m + W;
+                int cnt = 0;
+#pragma unroll
+                for (int i = 0; i < MAX_CAND; ++i) {
+                    const bool in = cs[i] <= thrF;
+                    cand[i] = in ? ci[i] : -1;
+                    cnt += in ? 1 : 0;
+                }
+                const bool overflow = !(dropped > thrF);        // also true for NaN
+                need_exact = overflow || cnt != 1 || best < 0 || best >= p.k;
+#pragma unroll
+                for (int i = 0; i < MAX_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
+                if (overflow || best < 0 || best >= p.k) cand[0] = -2;
+                p.labels[row] = best;
+            }
+            const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
+            if (mask) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(p.counters, __popc(mask));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (need_exact) {
+                    const int pos = base + __popc(mask & ((1u << lane) - 1));
+                    p.wl_rows[pos] = (int32_t)row;
+#pragma unroll
+                    for (int i = 0; i < MAX_CAND; ++i) p.wl_cand[(size_t)pos * MAX_CAND + i] = cand[i];
+                }
+            }
+        }
+    }
+    // ---- teardown
+    tc_fence_before();
+    __syncthreads();
+    if (CL > 1) cluster_sync_all();
+    if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------ operand preparation
+__global__ void absmax_kernel_f32(const float *__restrict__ x, int64_t count, unsigned *__restrict__ out_bits) {
+    float m = 0.f;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < count; i += stride) { const float a = fabsf(x[i]); m = (a > m || a != a) ? a : m; }
+    for (int o = 16; o > 0; o >>= 1) { const float t = __shfl_xor_sync(0xffffffffu, m, o); m = (t > m || t != t) ? t : m; }
+    if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));   // NaN bits compare above +inf
+}
+__global__ void absmax_kernel_f64(const double *__restrict__ x, int64_t count, unsigned *__restrict__ out_bits) {
+    float m = 0.f;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < count; i += stride) {
+        const double ad = fabs(x[i]);
+        float a = __double2float_ru(ad);
+        m = (a > m || a != a) ? a : m;
+    }
+    for (int o = 16; o > 0; o >>= 1) { const float t = __shfl_xor_sync(0xffffffffu, m, o); m = (t > m || t != t) ? t : m; }
+    if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));
+}
+
+// one warp per row: x16 = fp16(x * 2^sx), xerr = {||x||, ||x - x16 * 2^-sx||} (rounded up)
+template <typename T>
+__global__ void x16_build_kernel(const T *__restrict__ X, int64_t n, int d, int d16, int sx, __half *__restrict__ x16,
+                                 float2 *__restrict__ xerr) {
+    const int lane = threadIdx.x & 31;
+    int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const double up = ldexp(1.0, sx), down = ldexp(1.0, -sx);
+    for (; row < n; row += stride) {
+        double s2 = 0.0, e2 = 0.0;
+        for (int c = lane; c < d16; c += 32) {
+            __half hv = __float2half_rn(0.f);
+            if (c < d) {
+                const double v = (double)X[row * d + c];
+                hv = __double2half(v * up);
+                const double back = (double)__half2float(hv) * down;
+                const double dl = v - back;
+                s2 = fma(v, v, s2);
+                e2 = fma(dl, dl, e2);
+            }
+            x16[row * d16 + c] = hv;
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            e2 += __shfl_xor_sync(0xffffffffu, e2, o);
+        }
+        if (lane == 0) {
+            float2 o;
+            o.x = __double2float_ru(sqrt(s2) * (1.0 + 1e-9));
+            o.y = __double2float_ru(sqrt(e2) * (1.0 + 1e-9));
+            xerr[row] = o;
+        }
+    }
+}
+
+// single CTA: fp16 centroid operand (scaled), score offsets, per-pass constants
+__global__ void __launch_bounds__(1024)
+c16_build_kernel(const double *__restrict__ C, const double *__restrict__ clabel, int k, int kpad, int d, int d16,
+                 int metric, int sx, __half *__restrict__ c16, float *__restrict__ cn, PassConst *__restrict__ pc) {
+    __shared__ float red[32];
+    __shared__ int s_sc, s_bad;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // 1. max |c| -> scale exponent
+    float m = 0.f;
+    for (size_t i = tid; i < (size_t)k * d; i += blockDim.x) {
+        const float a = __double2float_ru(fabs(C[i]));
+        m = (a > m || a != a) ? a : m;
+    }
+    for (int o = 16; o > 0; o >>= 1) { const float t = __shfl_xor_sync(0xffffffffu, m, o); m = (t > m || t != t) ? t : m; }
+    if (lane == 0) red[warp] = m;
+    __syncthreads();
+    if (tid == 0) {
+        float mm = 0.f;
+        for (int w = 0; w < 32; ++w) mm = (red[w] > mm || red[w] != red[w]) ? red[w] : mm;
+        int bad = !(mm < 3.0e38f);
+        int e = 0;
+        if (!bad && mm > 0.f) { frexpf(mm, &e); }       // mm = f * 2^e, f in [0.5, 1)
+        s_sc = bad ? 0 : (mm > 0.f ? 14 - e : 0);      // max |c| * 2^sc in [2^13, 2^14)
+        s_bad = bad;
+    }
+    __syncthreads();
+    const int sc = s_sc;
+    const double up = ldexp(1.0, sc), down = ldexp(1.0, -sc);
+    // 2. convert rows; per-centroid norms (one warp per centroid)
+    float w_c16 = 0.f, w_dc = 0.f, w_c = 0.f;
+    for (int j = warp; j < kpad; j += 32) {
+        double s2 = 0.0, e2 = 0.0, t2 = 0.0;
+        for (int c = lane; c < d16; c += 32) {
+            __half hv = __float2half_rn(0.f);
+            if (j < k && c < d) {
+                const double v = C[(size_t)j * d + c];
+                hv = __double2half(v * up);
+                const double back = (double)__half2float(hv) * down;
+                const double dl = v - back;
+                s2 = fma(v, v, s2); e2 = fma(dl, dl, e2); t2 = fma(back, back, t2);
+            }
+            c16[(size_t)j * d16 + c] = hv;
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            e2 += __shfl_xor_sync(0xffffffffu, e2, o);
+            t2 += __shfl_xor_sync(0xffffffffu, t2, o);
+        }
+        if (lane == 0) {
+            if (j < k) {
+                cn[j] = (metric == AKM_EUCLIDEAN) ? (float)clabel[j] : 0.f;
+                w_c = fmaxf(w_c, __double2float_ru(sqrt(s2) * (1.0 + 1e-9)));
+                w_dc = fmaxf(w_dc, __double2float_ru(sqrt(e2) * (1.0 + 1e-9)));
+                w_c16 = fmaxf(w_c16, __double2float_ru(sqrt(t2) * (1.0 + 1e-9)));
+            } else {
+                cn[j] = PAD_SCORE;
+            }
+        }
+    }
+    __shared__ float r1[32], r2[32], r3[32];
+    if (lane == 0) { r1[warp] = w_c16; r2[warp] = w_dc; r3[warp] = w_c; }
+    __syncthreads();
+    if (tid == 0) {
+        float a = 0.f, b = 0.f, c = 0.f;
+        for (int w = 0; w < 32; ++w) { a = fmaxf(a, r1[w]); b = fmaxf(b, r2[w]); c = fmaxf(c, r3[w]); }
+        pc->c16_max = a; pc->dc_max = b; pc->c_max = c;
+        const float sgn = (metric == AKM_EUCLIDEAN) ? -2.f : -1.f;
+        pc->score_scale = sgn * ldexpf(1.f, -(sx + sc));
+        pc->sc = sc;
+        pc->bad = s_bad || !(c < 1e18f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ refinement of 2..4 candidates
+// One warp per worklist entry.  fp64 FMA evaluation of the candidate scores; if the best is separated from the
+// runner-up by more than the combined rounding bound of this evaluation and of Java's, it is Java's argmin.
+// Otherwise (or when the entry asks for all centroids) the row goes to the exact list.
+template <typename T, int METRIC>
+__global__ void refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int d,
+                                         const double *__restrict__ C, const double *__restrict__ clabel, int k,
+                                         const int32_t *__restrict__ wl_rows, const int32_t *__restrict__ wl_cand,
+                                         const int *__restrict__ counters, int32_t *__restrict__ labels,
+                                         int32_t *__restrict__ exact_rows, int *__restrict__ exact_count) {
+    const int lane = threadIdx.x & 31;
+    const int nwl = counters[0];
+    int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int stride = (gridDim.x * blockDim.x) >> 5;
+    for (; e < nwl; e += stride) {
+        const int row = wl_rows[e];
+        int cand[MAX_CAND];
+#pragma unroll
+        for (int i = 0; i < MAX_CAND; ++i) cand[i] = wl_cand[(size_t)e * MAX_CAND + i];
+        bool to_exact = cand[0] == -2;
+        int winner = -1;
+        if (!to_exact) {
+            double acc[MAX_CAND];
+#pragma unroll
+            for (int i = 0; i < MAX_CAND; ++i) acc[i] = 0.0;
+            for (int c = lane; c < d; c += 32) {
+                const double xv = (double)X[(int64_t)row * d + c];
+#pragma unroll
+                for (int i = 0; i < MAX_CAND; ++i)
+                    if (cand[i] >= 0) acc[i] = fma(xv, C[(size_t)cand[i] * d + c], acc[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < MAX_CAND; ++i)
+                for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+            const double xl = (METRIC == AKM_EUCLIDEAN) ? xlabel[row] : 1.0;
+            double v1 = DBL_MAX, v2 = DBL_MAX, clmax = 0.0;
+            int i1 = -1;
+#pragma unroll
+            for (int i = 0; i < MAX_CAND; ++i) {
+                if (cand[i] < 0) continue;
+                const double cl = (METRIC == AKM_EUCLIDEAN) ? clabel[cand[i]] : 1.0;
+                clmax = fmax(clmax, cl);
+                const double v = (METRIC == AKM_EUCLIDEAN) ? (xl + cl - 2.0 * acc[i]) : (1.0 - acc[i]);
+                if (v < v1 || (v == v1 && cand[i] < i1)) { v2 = v1; v1 = v; i1 = cand[i]; }
+                else if (v < v2) v2 = v;
+            }
+            const double rc = sqrt(fabs(xl)) + sqrt(clmax);
+            const double tau = 8.0 * (double)(d + 16) * 2.220446049250313e-16 * rc * rc;
+            if (i1 >= 0 && (v2 - v1) > tau) winner = i1;   // false for NaN
+            else to_exact = true;
+        }
+        if (lane == 0) {
+            if (to_exact) exact_rows[atomicAdd(exact_count, 1)] = row;
+            else labels[row] = winner;
+        }
+    }
+}
+
+// distance of each row to its final centroid in the exact Java order (predictionDistanceCol)
+template <typename T, int METRIC>
+__global__ void winner_distance_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int64_t n, int d,
+                                       const double *__restrict__ C, const double *__restrict__ clabel,
+                                       const int32_t *__restrict__ labels, double *__restrict__ mind) {
+    int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; row < n; row += stride) {
+        const int j = labels[row];
+        if (j < 0) { mind[row] = nan(""); continue; }
+        const T *x = X + row * d;
+        const double *c = C + (size_t)j * d;
+        double t = 0.0;
+        for (int i = 0; i < d; ++i) t = __dadd_rn(t, __dmul_rn(c[i], (double)x[i]));
+        double D;
+        if (METRIC == AKM_EUCLIDEAN) {
+            const double y = __dadd_rn(0.0, __dmul_rn(-2.0, t));
+            D = sqrt(fabs(__dadd_rn(__dadd_rn(y, xlabel[row]), clabel[j])));
+        } else {
+            D = __dadd_rn(1.0, __dmul_rn(-1.0, t));
+        }
+        mind[row] = D;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct TensorCtx {
+    EncodeTiledFn encode = nullptr;
+    __half *c16 = nullptr; float *cn = nullptr; int kpad_cap = 0;
+    PassConst *pc = nullptr;
+    int32_t *wl_rows = nullptr, *wl_cand = nullptr, *exact_rows = nullptr; int64_t wl_cap = 0;
+    int *counters = nullptr;     // [0] worklist, [1] exact list
+    unsigned *absmax = nullptr;
+    int fail_count = 0;
+};
+
+static TensorCtx *ctx_of(akm_handle h) {
+    if (!h->tc) h->tc = new TensorCtx();
+    return (TensorCtx *)h->tc;
+}
+
+void tensor_free(akm_handle h) {
+    TensorCtx *c = (TensorCtx *)h->tc;
+    if (!c) return;
+    cudaFree(c->c16); cudaFree(c->cn); cudaFree(c->pc); cudaFree(c->wl_rows); cudaFree(c->wl_cand);
+    cudaFree(c->exact_rows); cudaFree(c->counters); cudaFree(c->absmax);
+    delete c;
+    h->tc = nullptr;
+}
+
+static int round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+bool tensor_supported(akm_handle h, int k0) {
+    const int kb = (h->d + KBLK - 1) / KBLK;
+    if (kb > 2) return false;                 // d <= 128 for now (A tile fully resident per row group)
+    if (k0 > 8064) return false;              // score offsets live in shared memory
+    if (h->smem_optin < 200 * 1024) return false;
+    return true;
+}
+
+static int encode_2d(akm_handle h, TensorCtx *c, CUtensorMap *map, void *base, uint64_t cols, uint64_t rows,
+                     uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows) {
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {row_stride_bytes};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = c->encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return akm_fail(h, AKM_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+    return AKM_OK;
+}
+
+int tensor_prepare_x16(akm_handle h, RowStore &rs) {
+    TensorCtx *c = ctx_of(h);
+    if (rs.x16_valid) return AKM_OK;
+    const int d = h->d, d16 = round_up(d, 8);
+    if (!c->absmax) AKM_CUDA(h, cudaMalloc((void **)&c->absmax, sizeof(unsigned)));
+    AKM_CUDA(h, cudaMemsetAsync(c->absmax, 0, sizeof(unsigned), h->stream));
+    const int64_t count = rs.n * (int64_t)d;
+    if (rs.store == 4) absmax_kernel_f32<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.x32, count, c->absmax);
+    else absmax_kernel_f64<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.x64, count, c->absmax);
+    h->stats.kernel_launches++;
+    unsigned bits = 0;
+    AKM_CUDA(h, cudaMemcpyAsync(&bits, c->absmax, sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    float mx;
+    memcpy(&mx, &bits, sizeof(float));
+    if (!(mx < 3.0e38f)) { rs.x16_shift = INT_MIN; rs.x16_valid = true; return AKM_OK; }   // non-finite data: exact engine only
+    int e = 0;
+    if (mx > 0.f) frexpf(mx, &e);
+    rs.x16_shift = (mx > 0.f) ? 14 - e : 0;
+    if (rs.d16 != d16 || !rs.x16 || rs.x16_cap < rs.n) {
+        if (rs.x16) cudaFree(rs.x16);
+        if (rs.xerr) cudaFree(rs.xerr);
+        rs.x16 = nullptr; rs.xerr = nullptr;
+        const int64_t cap = std::max<int64_t>(rs.cap, 1);
+        AKM_CUDA(h, cudaMalloc((void **)&rs.x16, sizeof(__half) * (size_t)cap * d16));
+        AKM_CUDA(h, cudaMalloc((void **)&rs.xerr, sizeof(float2) * (size_t)cap));
+        rs.d16 = d16;
+        rs.x16_cap = cap;
+        rs.want16 = true;
+    }
+    const int blocks = (int)std::min<int64_t>((rs.n + 7) / 8, (int64_t)h->num_sms * 32);
+    if (rs.store == 4) x16_build_kernel<float><<<blocks, 256, 0, h->stream>>>(rs.x32, rs.n, d, d16, rs.x16_shift, rs.x16, rs.xerr);
+    else x16_build_kernel<double><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.n, d, d16, rs.x16_shift, rs.x16, rs.xerr);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    rs.x16_valid = true;
+    return AKM_OK;
+}
+
+template <int MB, int KB, int CL>
+static int launch_search(akm_handle h, const CUtensorMap &mx, const CUtensorMap &mc, const SearchParams &sp, size_t smem,
+                         int grid) {
+    auto kern = search_kernel<MB, KB, CL>;
+    AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(64 + 128 * MB);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = h->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AKM_CUDA(h, cudaLaunchKernelEx(&cfg, kern, mx, mc, sp));
+    h->stats.kernel_launches++;
+    return AKM_OK;
+}
+
+int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *clabel, int k0, int k, int32_t *labels,
+                  double *mind) {
+    TensorCtx *c = ctx_of(h);
+    const int d = h->d;
+    if (!c->encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || !fn) return akm_fail(h, AKM_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable");
+        c->encode = (EncodeTiledFn)fn;
+    }
+    AKM_TRY(tensor_prepare_x16(h, rs));
+    auto exact_all = [&]() {
+        h->stats.engine_used = AKM_ENGINE_EXACT;
+        h->stats.rows_certified = 0; h->stats.rows_refined = rs.n;
+        return launch_assign_exact(h, rs, nullptr, rs.n, C, clabel, k0, k, labels, mind, nullptr);
+    };
+    if (rs.x16_shift == INT_MIN || k <= 0) return exact_all();
+
+    const int KB = (d + KBLK - 1) / KBLK;
+    const int MB = 2;
+    const int ntiles = (k + TILE_N - 1) / TILE_N, kpad = ntiles * TILE_N;
+    const int d16 = rs.d16;
+    if (c->kpad_cap < kpad) {
+        cudaFree(c->c16); cudaFree(c->cn);
+        c->c16 = nullptr; c->cn = nullptr;
+        AKM_CUDA(h, cudaMalloc((void **)&c->c16, sizeof(__half) * (size_t)kpad * d16));
+        AKM_CUDA(h, cudaMalloc((void **)&c->cn, sizeof(float) * (size_t)kpad));
+        c->kpad_cap = kpad;
+    }
+    if (!c->pc) AKM_CUDA(h, cudaMalloc((void **)&c->pc, sizeof(PassConst)));
+    if (!c->counters) AKM_CUDA(h, cudaMalloc((void **)&c->counters, 4 * sizeof(int)));
+    if (c->wl_cap < rs.n) {
+        cudaFree(c->wl_rows); cudaFree(c->wl_cand); cudaFree(c->exact_rows);
+        c->wl_rows = c->wl_cand = c->exact_rows = nullptr;
+        AKM_CUDA(h, cudaMalloc((void **)&c->wl_rows, sizeof(int32_t) * (size_t)rs.n));
+        AKM_CUDA(h, cudaMalloc((void **)&c->wl_cand, sizeof(int32_t) * (size_t)rs.n * MAX_CAND));
+        AKM_CUDA(h, cudaMalloc((void **)&c->exact_rows, sizeof(int32_t) * (size_t)rs.n));
+        c->wl_cap = rs.n;
+    }
+    if (rs.n >= ((int64_t)1 << 31) - 256) return exact_all();
+
+    AKM_CUDA(h, cudaMemsetAsync(c->counters, 0, 4 * sizeof(int), h->stream));
+    c16_build_kernel<<<1, 1024, 0, h->stream>>>(C, clabel, k, kpad, d, d16, h->metric, rs.x16_shift, c->c16, c->cn, c->pc);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+
+    // shared-memory plan
+    const size_t A_STAGE = (size_t)MB * KB * BOX_BYTES, B_STAGE = (size_t)KB * BOX_BYTES;
+    const size_t fixed = (size_t)kpad * 4 + (4 + 2 * MAX_BSLOTS + 4) * 8 + 64 + 1024;   // offsets, barriers, misc, alignment slack
+    const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
+    const int a_stages = 2;
+    if (a_stages * A_STAGE + 2 * B_STAGE + fixed > budget) return exact_all();
+    int b_slots = (int)((budget - fixed - a_stages * A_STAGE) / B_STAGE);
+    b_slots = std::min(b_slots, MAX_BSLOTS);
+    const int resident = ntiles <= b_slots ? 1 : 0;
+    if (resident) b_slots = ntiles;
+    const size_t smem = a_stages * A_STAGE + (size_t)b_slots * B_STAGE + fixed;
+
+    const int CL = resident ? 1 : 2;          // multicast only pays when centroid tiles stream
+    CUtensorMap mapX, mapC;
+    AKM_TRY(encode_2d(h, c, &mapX, rs.x16, (uint64_t)d, (uint64_t)rs.n, (uint64_t)d16 * 2, KBLK, TILE_M));
+    AKM_TRY(encode_2d(h, c, &mapC, c->c16, (uint64_t)d, (uint64_t)kpad, (uint64_t)d16 * 2, KBLK, TILE_N / CL));
+
+    SearchParams sp{};
+    sp.n = rs.n;
+    sp.groups = (int)ceil_div64(rs.n, (int64_t)MB * TILE_M);
+    sp.ntiles = ntiles; sp.a_stages = a_stages; sp.b_slots = b_slots; sp.resident = resident;
+    sp.d = d; sp.metric = h->metric; sp.k = k;
+    sp.cn = c->cn; sp.pc = c->pc; sp.xerr = rs.xerr; sp.labels = labels;
+    sp.wl_rows = c->wl_rows; sp.wl_cand = c->wl_cand; sp.counters = c->counters;
+    sp.eta = (float)(KB * KBLK + 32) * 2.3841858e-7f;       // (d16 + 32) * 2^-22
+    const int nsuper = (sp.groups + CL - 1) / CL;
+    int grid = std::min(h->num_sms / CL, nsuper) * CL;
+    if (grid < CL) grid = CL;
+    int rc;
+    if (KB == 1) rc = (CL == 2) ? launch_search<2, 1, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 1, 1>(h, mapX, mapC, sp, smem, grid);
+    else rc = (CL == 2) ? launch_search<2, 2, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 2, 1>(h, mapX, mapC, sp, smem, grid);
+    AKM_TRY(rc);
+    if (h->profiling && h->mid_event) { cudaEventRecord(h->mid_event, h->stream); h->mid_recorded = true; }
+
+    // refinement: candidates first, then the exact list (lengths stay on the device)
+    const int rblocks = h->num_sms * 8;
+#define REFINE(T, PTR, M)                                                                                         \
+    refine_candidates_kernel<T, M><<<rblocks, 256, 0, h->stream>>>(PTR, rs.xlabel, d, C, clabel, k, c->wl_rows, \
+                                                                   c->wl_cand, c->counters, labels, c->exact_rows, c->counters + 1)
+    if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) REFINE(float, rs.x32, AKM_EUCLIDEAN); else REFINE(double, rs.x64, AKM_EUCLIDEAN); }
+    else REFINE(double, rs.x64, AKM_COSINE);
+#undef REFINE
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    AKM_TRY(launch_assign_exact_list(h, rs, c->exact_rows, c->counters + 1, C, clabel, k0, k, labels));
+    if (mind) {
+        const int wb = h->num_sms * 8;
+        if (h->metric == AKM_EUCLIDEAN) {
+            if (rs.store == 4) winner_distance_kernel<float, AKM_EUCLIDEAN><<<wb, 256, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+            else winner_distance_kernel<double, AKM_EUCLIDEAN><<<wb, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+        } else {
+            winner_distance_kernel<double, AKM_COSINE><<<wb, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+        }
+        h->stats.kernel_launches++;
+        AKM_CUDA(h, cudaGetLastError());
+    }
+    // counts for akm_get_stats (read back with the other scalars by the caller)
+    AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 4, c->counters, 2 * sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
+    h->stats.engine_used = AKM_ENGINE_TENSOR;
+    return AKM_OK;
+}
