@@ -225,7 +225,7 @@ static int ensure_scratch(akm_handle h, int k0) {
 
 // ------------------------------------------------------------------ assignment dispatch
 static int run_assign(akm_handle h, RowStore &rs, const double *C, const double *clabel, int k0, int k,
-                      int32_t *labels, double *mind) {
+                      int32_t *labels, double *mind, int chain = 0, const int *remap = nullptr) {
     h->stats.rows = rs.n;
     h->stats.storage_bytes = rs.store;
     bool use_tensor = false;
@@ -236,11 +236,13 @@ static int run_assign(akm_handle h, RowStore &rs, const double *C, const double 
     }
     if (use_tensor) {
         h->stats.engine_used = AKM_ENGINE_TENSOR;
-        return tensor_assign(h, rs, C, clabel, k0, k, labels, mind);
+        return tensor_assign(h, rs, C, clabel, k0, k, labels, mind, chain, remap);
     }
+    if (labels == h->labels) tensor_invalidate_seeds(h);
     h->stats.engine_used = AKM_ENGINE_EXACT;
     h->stats.rows_certified = 0;
     h->stats.rows_refined = rs.n;
+    h->stats.rows_exact_all = rs.n;
     return launch_assign_exact(h, rs, nullptr, rs.n, C, clabel, k0, k, labels, mind, nullptr);
 }
 
@@ -249,6 +251,7 @@ static void absorb_tensor_stats(akm_handle h) {
     if (h->stats.engine_used == AKM_ENGINE_TENSOR) {
         h->stats.rows_refined = h->h_iscal[4];
         h->stats.rows_certified = h->stats.rows - h->h_iscal[4];
+        h->stats.rows_exact_all = h->h_iscal[5];
     }
 }
 
@@ -380,6 +383,7 @@ int akm_clear_rows(akm_handle h) {
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     rowstore_free(h->rows);
     h->rows.store = (h->metric == AKM_COSINE) ? 8 : 4;
+    tensor_invalidate_seeds(h);
     return AKM_OK;
 }
 
@@ -408,7 +412,7 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
     AKM_TRY(ensure_labels(h, h->rows.n));
     AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centroids, sizeof(double) * (size_t)k0 * d, cudaMemcpyHostToDevice, h->stream));
     AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, /*cos_normalise=*/false));
-    AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], k0, k, h->labels, nullptr));
+    AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], k0, k, h->labels, nullptr, /*chain=*/2, nullptr));
     AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], k0, s->sum, s->sum + L));
     AKM_CUDA(h, cudaMemcpyAsync(sum_out, s->sum, sizeof(double) * L, cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
@@ -463,6 +467,7 @@ int akm_set_centroids(akm_handle h, const double *c0, int k0) {
     AKM_CUDA(h, cudaMemsetAsync(h->sum, 0, sizeof(double) * ((size_t)k0 * (h->d + 1) + 2), h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     h->k0 = k0; h->k = k0; h->step = 0;
+    tensor_invalidate_seeds(h);
     return AKM_OK;
 }
 
@@ -478,7 +483,8 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     const bool prof = h->profiling;
     h->mid_recorded = false;
     if (prof) cudaEventRecord(h->pev[0], h->stream);
-    AKM_TRY(run_assign(h, h->rows, h->cent[rd], h->clabel[rd], k0, h->k, h->labels, nullptr));
+    AKM_TRY(run_assign(h, h->rows, h->cent[rd], h->clabel[rd], k0, h->k, h->labels, nullptr, /*chain=*/1,
+                       s > 1 ? h->cmap : nullptr));
     if (prof) cudaEventRecord(h->pev[1], h->stream);
     AKM_TRY(launch_accumulate(h, h->rows, h->labels, h->cent[rd], k0, h->sum, h->sum + L));
     if (prof) cudaEventRecord(h->pev[2], h->stream);
@@ -547,6 +553,7 @@ static int predict_store(akm_handle h, RowStore &rs, const double *dC, const dou
     Scratch *s = scratch_of(h);
     const int64_t n = rs.n;
     if (n == 0) return AKM_OK;
+    tensor_invalidate_seeds(h);                      // h->labels is about to hold prediction labels
     AKM_TRY(ensure_labels(h, n));
     AKM_TRY(ensure_mind(h, n));
     if (s->idx64_cap < n) {

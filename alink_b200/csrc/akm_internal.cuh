@@ -126,7 +126,8 @@ int launch_labels_to_i64(akm_handle h, const int32_t *labels, int64_t n, int64_t
 bool tensor_supported(akm_handle h, int k0);
 // approximate search on tensor cores + certification + exact refinement; fills labels (and mind when non-null)
 int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *clabel, int k0, int k,
-                  int32_t *labels, double *mind);
+                  int32_t *labels, double *mind, int chain, const int *remap);
+void tensor_invalidate_seeds(akm_handle h);
 int tensor_prepare_x16(akm_handle h, RowStore &rs);
 void tensor_free(akm_handle h);
 

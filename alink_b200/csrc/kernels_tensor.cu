@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 #include "akm_internal.cuh"
 
@@ -164,11 +165,15 @@ struct SearchParams {
     int32_t *wl_cand;       // MAX_CAND candidates per entry (-1 = unused, first == -2: all centroids)
     int *counters;          // [0] worklist length
     float eta;              // accumulation error factor
+    // seeds: a rigorous upper bound of this pass's minimum score per row, derived from the previous pass
+    float *useed;           // in: previous pass min score + its error bound; out: same for this pass (nullable)
+    const float *sig_old;   // per OLD label: distance its centroid moved (INF if the cluster was dropped)
+    int k_prev;             // 0: no seeds this pass
 };
 
 // ------------------------------------------------------------------------------------------ search kernel
 template <int MB, int KB, int CL>
-__global__ void __launch_bounds__(64 + 128 * MB, 1)
+__global__ void __launch_bounds__(64 + 256 * MB, 1)
 search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__ CUtensorMap tmapC,
               const SearchParams p) {
     extern __shared__ unsigned char smem_raw[];
@@ -176,7 +181,7 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
     constexpr int A_STAGE = MB * KB * BOX_BYTES;
     constexpr int B_STAGE = KB * BOX_BYTES;
     constexpr int TMEM_COLS = (MB == 2) ? 512 : 256;
-    constexpr int EPI_WARPS = 4 * MB;
+    constexpr int EPI_WARPS = 8 * MB;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = (CL > 1) ? cluster_ctarank() : 0;
@@ -189,7 +194,8 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
     uint64_t *a_full = bars, *a_empty = bars + 2, *b_full = bars + 4, *b_empty = b_full + MAX_BSLOTS,
              *t_full = b_empty + MAX_BSLOTS, *t_empty = t_full + 2;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
-    float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);   // 5 floats
+    float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);   // 5 floats (+3 pad)
+    float2 *cand_s = reinterpret_cast<float2 *>(pc_s + 8);     // [2 halves][128*MB rows][MAX_CAND] (index bits, score) + exchange
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
@@ -294,16 +300,25 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
             __syncwarp();
         }
     } else {
-        // =============================== epilogue: one thread per row
+        // =============================== epilogue: 16 warps, one thread per (row, 64-column half)
+        // Warp e = warp - 2: TMEM lane quadrant q = warp & 3 (hardware rule), sub = e >> 2 selects the row
+        // block (sub >> 1) and the column half (sub & 1).  The fast path is branch-light: 32 scores, a min
+        // tree, one compare; only 8-column groups that can hold a candidate take the (predicated) slow path.
         const int e = warp - 2;
-        const int rb = e >> 2;
-        const int q = warp & 3;                       // TMEM lane quadrant this warp may read
+        const int sub = e >> 2;
+        const int rb = sub >> 1, half = sub & 1;
+        const int q = warp & 3;
         const float c16_max = pc_s[0], dc_max = pc_s[1], c_max = pc_s[2], scale = pc_s[3];
+        const int rt = rb * TILE_M + q * 32 + lane;                 // row slot within the CTA's group
+        float2 *my_ring = cand_s + ((size_t)half * (MB * TILE_M) + rt) * MAX_CAND;
+        float2 *peer_ring = cand_s + ((size_t)1 * (MB * TILE_M) + rt) * MAX_CAND;
+        float *xch = reinterpret_cast<float *>(cand_s + (size_t)2 * MB * TILE_M * MAX_CAND) + rt * 4;   // {m, dropped, ncand}
+        const int bar_id = 1 + rb * 4 + q;
         int t_it = 0;
         for (int sg = cluster_id; sg < nsuper; sg += nclusters) {
             const int64_t row = (((int64_t)sg * CL + rank) * MB + rb) * TILE_M + q * 32 + lane;
             const bool valid = row < p.n;
-            float W = 0.f;
+            float W = 0.f, m = INFINITY;
             if (valid) {
                 const float2 xe = p.xerr[row];
                 const float r = xe.x, er = xe.y;
@@ -313,93 +328,139 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
                 const float epsJ = (float)(p.d + 16) * 4.5e-16f * rc * rc;    // Java's own fp64 rounding
                 W = 2.004f * B + 2.f * epsJ + 1e-30f;
                 if (pc_s[4] != 0.f) W = NAN;                                  // non-finite centroids: everything goes exact
+                if (p.k_prev > 0) {
+                    // Seed: the previous winner a had true score <= useed (its approximate minimum + bound); its
+                    // centroid moved by sig_old[a], so this pass's minimum approximate score is at most u.
+                    const int a = p.labels[row];
+                    if (a >= 0 && a < p.k_prev) {
+                        const float sg_a = p.sig_old[a];
+                        const float u0 = p.useed[row];
+                        float u;
+                        if (p.metric == AKM_EUCLIDEAN) {
+                            const float r2 = r * r;
+                            const float t = sqrtf(fmaxf(u0 + r2 * 1.000001f, 0.f)) * 1.000001f + sg_a;
+                            u = t * t * 1.000001f - r2 * 0.999998f + 0.5f * W + 1e-5f * (t * t + r2);
+                        } else {
+                            u = u0 + sg_a * (r + er) * 1.000001f + 0.5f * W + 1e-6f;
+                        }
+                        if (u == u) m = u;                                    // NaN: no seed
+                    }
+                }
             }
-            float m = INFINITY, thr = INFINITY;
-            int best = -1;
-            float cs[MAX_CAND];
-            int ci[MAX_CAND];
-#pragma unroll
-            for (int i = 0; i < MAX_CAND; ++i) { cs[i] = INFINITY; ci[i] = -1; }
+            float thr = valid ? m + W : -INFINITY;       // padding rows never enter the candidate path
+            int ncand = 0;
             float dropped = INFINITY;
 
             for (int t = 0; t < p.ntiles; ++t, ++t_it) {
                 const int tb = t_it & 1;
                 mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
                 tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * MB * TILE_N + rb * TILE_N);
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) +
+                                       (uint32_t)(tb * MB * TILE_N + rb * TILE_N + half * 64);
 #pragma unroll 1
-                for (int c0 = 0; c0 < TILE_N; c0 += 32) {
+                for (int c = 0; c < 2; ++c) {
                     uint32_t v[32];
-                    __syncwarp();                      // tcgen05.ld is warp-collective: reconverge after the candidate branch
-                    tmem_ld32(taddr + c0, v);
+                    __syncwarp();                          // tcgen05.ld is warp-collective
+                    tmem_ld32(taddr + c * 32, v);
                     tmem_ld_wait();
-                    const float *cn_t = cn_s + t * TILE_N + c0;
+                    if (c == 1) {                          // every TMEM read of this tile is done: release the buffer
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(t_empty + tb));
+                    }
+                    const int j0 = t * TILE_N + half * 64 + c * 32;
+                    const float *cn_t = cn_s + j0;
+                    float sc[32];
 #pragma unroll
-                    for (int g8 = 0; g8 < 4; ++g8) {
-                        float s[8];
-                        const float4 o0 = *reinterpret_cast<const float4 *>(cn_t + g8 * 8);
-                        const float4 o1 = *reinterpret_cast<const float4 *>(cn_t + g8 * 8 + 4);
-                        s[0] = fmaf(__uint_as_float(v[g8 * 8 + 0]), scale, o0.x);
-                        s[1] = fmaf(__uint_as_float(v[g8 * 8 + 1]), scale, o0.y);
-                        s[2] = fmaf(__uint_as_float(v[g8 * 8 + 2]), scale, o0.z);
-                        s[3] = fmaf(__uint_as_float(v[g8 * 8 + 3]), scale, o0.w);
-                        s[4] = fmaf(__uint_as_float(v[g8 * 8 + 4]), scale, o1.x);
-                        s[5] = fmaf(__uint_as_float(v[g8 * 8 + 5]), scale, o1.y);
-                        s[6] = fmaf(__uint_as_float(v[g8 * 8 + 6]), scale, o1.z);
-                        s[7] = fmaf(__uint_as_float(v[g8 * 8 + 7]), scale, o1.w);
-                        const float cm = fminf(fminf(fminf(s[0], s[1]), fminf(s[2], s[3])),
-                                               fminf(fminf(s[4], s[5]), fminf(s[6], s[7])));
-                        if (cm <= thr) {
-                            const int j0 = t * TILE_N + c0 + g8 * 8;
+                    for (int g = 0; g < 8; ++g) {
+                        const float4 o = *reinterpret_cast<const float4 *>(cn_t + g * 4);
+                        sc[g * 4 + 0] = fmaf(__uint_as_float(v[g * 4 + 0]), scale, o.x);
+                        sc[g * 4 + 1] = fmaf(__uint_as_float(v[g * 4 + 1]), scale, o.y);
+                        sc[g * 4 + 2] = fmaf(__uint_as_float(v[g * 4 + 2]), scale, o.z);
+                        sc[g * 4 + 3] = fmaf(__uint_as_float(v[g * 4 + 3]), scale, o.w);
+                    }
+                    float g8[4];
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                if (s[i] <= thr) {
-                                    dropped = fminf(dropped, cs[MAX_CAND - 1]);
+                    for (int g = 0; g < 4; ++g) {
+                        const float a1 = fminf(fminf(sc[g * 8 + 0], sc[g * 8 + 1]), sc[g * 8 + 2]);     // FMNMX3
+                        const float a2 = fminf(fminf(sc[g * 8 + 3], sc[g * 8 + 4]), sc[g * 8 + 5]);
+                        g8[g] = fminf(fminf(sc[g * 8 + 6], sc[g * 8 + 7]), fminf(a1, a2));
+                    }
+                    const float cmin = fminf(fminf(g8[0], g8[1]), fminf(g8[2], g8[3]));
+                    // tighten first: every score <= (final minimum + W) is still <= thr, so the recorded set
+                    // stays a superset of the true candidates
+                    m = fminf(m, cmin);
+                    thr = valid ? m + W : -INFINITY;
+                    if (cmin <= thr) {
 #pragma unroll
-                                    for (int u = MAX_CAND - 1; u > 0; --u) { cs[u] = cs[u - 1]; ci[u] = ci[u - 1]; }
-                                    cs[0] = s[i];
-                                    ci[0] = j0 + i;
-                                    if (s[i] < m) { m = s[i]; best = j0 + i; thr = m + W; }
+                        for (int g = 0; g < 4; ++g) {
+                            if (g8[g] <= thr) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    if (sc[g * 8 + i] <= thr) {
+                                        const int slot = ncand & (MAX_CAND - 1);
+                                        if (ncand >= MAX_CAND) dropped = fminf(dropped, my_ring[slot].y);
+                                        my_ring[slot] = make_float2(__int_as_float(j0 + g * 8 + i), sc[g * 8 + i]);
+                                        ++ncand;
+                                    }
                                 }
                             }
                         }
                     }
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(t_empty + tb));
             }
-            // ---- certificate
+            // ---- merge the two column halves of each row, then the certificate (half 0 owns the row)
+            if (half == 1) { xch[0] = m; xch[1] = dropped; xch[2] = __int_as_float(ncand); }
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
             bool need_exact = false;
             int cand[MAX_CAND];
-            if (valid) {
-                const float thrF = m + W;
-                int cnt = 0;
+            if (half == 0) {
+                const float m2 = xch[0], dropped2 = xch[1];
+                const int ncand2 = __float_as_int(xch[2]);
+                if (valid) {
+                    const float mF = fminf(m, m2);
+                    const float thrF = mF + W;
+                    int cnt = 0, best = -1;
 #pragma unroll
-                for (int i = 0; i < MAX_CAND; ++i) {
-                    const bool in = cs[i] <= thrF;
-                    cand[i] = in ? ci[i] : -1;
-                    cnt += in ? 1 : 0;
+                    for (int i = 0; i < MAX_CAND; ++i) cand[i] = -1;
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const float2 *ring = h2 ? peer_ring : my_ring;
+                        const int nc = h2 ? ncand2 : ncand;
+#pragma unroll
+                        for (int i = 0; i < MAX_CAND; ++i) {
+                            const float2 cv = ring[i];
+                            if (i < nc && cv.y <= thrF) {
+                                const int j = __float_as_int(cv.x);
+                                if (cnt < MAX_CAND) cand[cnt] = j;
+                                if (cv.y == mF) best = j;
+                                ++cnt;
+                            }
+                        }
+                    }
+                    const bool overflow = !(dropped > thrF) || !(dropped2 > thrF) || cnt > MAX_CAND;   // true for NaN too
+                    if (best < 0 && cnt > 0) best = cand[0];
+                    need_exact = overflow || cnt != 1 || best < 0 || best >= p.k;
+#pragma unroll
+                    for (int i = 0; i < MAX_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
+                    if (overflow || best < 0 || best >= p.k) cand[0] = -2;
+                    p.labels[row] = best;
+                    if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
                 }
-                const bool overflow = !(dropped > thrF);        // also true for NaN
-                need_exact = overflow || cnt != 1 || best < 0 || best >= p.k;
+                const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
+                if (mask) {
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(p.counters, __popc(mask));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (need_exact) {
+                        const int pos = base + __popc(mask & ((1u << lane) - 1));
+                        p.wl_rows[pos] = (int32_t)row;
 #pragma unroll
-                for (int i = 0; i < MAX_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
-                if (overflow || best < 0 || best >= p.k) cand[0] = -2;
-                p.labels[row] = best;
-            }
-            const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
-            if (mask) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(p.counters, __popc(mask));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (need_exact) {
-                    const int pos = base + __popc(mask & ((1u << lane) - 1));
-                    p.wl_rows[pos] = (int32_t)row;
-#pragma unroll
-                    for (int i = 0; i < MAX_CAND; ++i) p.wl_cand[(size_t)pos * MAX_CAND + i] = cand[i];
+                        for (int i = 0; i < MAX_CAND; ++i) p.wl_cand[(size_t)pos * MAX_CAND + i] = cand[i];
+                    }
                 }
             }
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // rings may be reused for the next group
         }
     }
     // ---- teardown
@@ -469,7 +530,9 @@ __global__ void x16_build_kernel(const T *__restrict__ X, int64_t n, int d, int 
 // single CTA: fp16 centroid operand (scaled), score offsets, per-pass constants
 __global__ void __launch_bounds__(1024)
 c16_build_kernel(const double *__restrict__ C, const double *__restrict__ clabel, int k, int kpad, int d, int d16,
-                 int metric, int sx, __half *__restrict__ c16, float *__restrict__ cn, PassConst *__restrict__ pc) {
+                 int metric, int sx, __half *__restrict__ c16, float *__restrict__ cn, PassConst *__restrict__ pc,
+                 const double *__restrict__ Cprev, const int *__restrict__ remap, int k_prev,
+                 float *__restrict__ sig_old) {
     __shared__ float red[32];
     __shared__ int s_sc, s_bad;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -524,6 +587,15 @@ c16_build_kernel(const double *__restrict__ C, const double *__restrict__ clabel
                 cn[j] = PAD_SCORE;
             }
         }
+    }
+    // how far did the centroid of each OLD label move? (remap: old index -> new index, -1 = dropped)
+    for (int a = warp; a < k_prev; a += 32) {
+        const int j = remap ? remap[a] : a;
+        double s2 = 0.0;
+        if (j >= 0 && j < k)
+            for (int c = lane; c < d; c += 32) { const double df = C[(size_t)j * d + c] - Cprev[(size_t)a * d + c]; s2 = fma(df, df, s2); }
+        for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+        if (lane == 0) sig_old[a] = (j >= 0 && j < k) ? __double2float_ru(sqrt(s2) * (1.0 + 1e-9)) : INFINITY;
     }
     __shared__ float r1[32], r2[32], r3[32];
     if (lane == 0) { r1[warp] = w_c16; r2[warp] = w_dc; r3[warp] = w_c; }
@@ -634,7 +706,11 @@ struct TensorCtx {
     int32_t *wl_rows = nullptr, *wl_cand = nullptr, *exact_rows = nullptr; int64_t wl_cap = 0;
     int *counters = nullptr;     // [0] worklist, [1] exact list
     unsigned *absmax = nullptr;
-    int fail_count = 0;
+    // seeds (only for the cached training partition)
+    float *useed = nullptr; int64_t useed_cap = 0;
+    double *Cprev = nullptr; float *sig_old = nullptr; int prev_cap = 0;
+    int k_prev = 0; int64_t seed_rows = -1; const void *seed_x16 = nullptr;
+    int chain = 0, step_prev = -1;
 };
 
 static TensorCtx *ctx_of(akm_handle h) {
@@ -647,6 +723,7 @@ void tensor_free(akm_handle h) {
     if (!c) return;
     cudaFree(c->c16); cudaFree(c->cn); cudaFree(c->pc); cudaFree(c->wl_rows); cudaFree(c->wl_cand);
     cudaFree(c->exact_rows); cudaFree(c->counters); cudaFree(c->absmax);
+    cudaFree(c->useed); cudaFree(c->Cprev); cudaFree(c->sig_old);
     delete c;
     h->tc = nullptr;
 }
@@ -720,7 +797,7 @@ static int launch_search(akm_handle h, const CUtensorMap &mx, const CUtensorMap 
     AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)grid);
-    cfg.blockDim = dim3(64 + 128 * MB);
+    cfg.blockDim = dim3(64 + 256 * MB);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = h->stream;
     cudaLaunchAttribute attr[1];
@@ -733,8 +810,15 @@ static int launch_search(akm_handle h, const CUtensorMap &mx, const CUtensorMap 
     return AKM_OK;
 }
 
+void tensor_invalidate_seeds(akm_handle h) {
+    TensorCtx *c = (TensorCtx *)h->tc;
+    if (c) { c->k_prev = 0; c->chain = 0; }
+}
+
+// chain: 0 = stand-alone pass (no seeds), 1 = akm_step sequence (remap = compaction map of the last update),
+//        2 = sequence of host-buffer passes (identity map, only while k is unchanged)
 int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *clabel, int k0, int k, int32_t *labels,
-                  double *mind) {
+                  double *mind, int chain, const int *remap) {
     TensorCtx *c = ctx_of(h);
     const int d = h->d;
     if (!c->encode) {
@@ -746,8 +830,9 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     }
     AKM_TRY(tensor_prepare_x16(h, rs));
     auto exact_all = [&]() {
+        if (labels == h->labels) c->k_prev = 0;      // the seeds no longer describe the labels in that buffer
         h->stats.engine_used = AKM_ENGINE_EXACT;
-        h->stats.rows_certified = 0; h->stats.rows_refined = rs.n;
+        h->stats.rows_certified = 0; h->stats.rows_refined = rs.n; h->stats.rows_exact_all = rs.n;
         return launch_assign_exact(h, rs, nullptr, rs.n, C, clabel, k0, k, labels, mind, nullptr);
     };
     if (rs.x16_shift == INT_MIN || k <= 0) return exact_all();
@@ -775,14 +860,39 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     }
     if (rs.n >= ((int64_t)1 << 31) - 256) return exact_all();
 
+    // seeds are valid only when this pass continues the previous one on the same rows and label buffer
+    const bool train_rows = (&rs == &h->rows) && labels == h->labels && chain != 0;
+    bool use_seed = train_rows && c->k_prev > 0 && c->chain == chain && c->seed_rows == rs.n && c->seed_x16 == rs.x16;
+    if (use_seed && chain == 1 && c->step_prev != h->step - 1) use_seed = false;
+    if (use_seed && chain == 2 && c->k_prev != k) use_seed = false;
+    if (train_rows) {
+        if (c->useed_cap < rs.n) {
+            cudaFree(c->useed); c->useed = nullptr;
+            AKM_CUDA(h, cudaMalloc((void **)&c->useed, sizeof(float) * (size_t)rs.n));
+            c->useed_cap = rs.n;
+            use_seed = false;
+        }
+        if (c->prev_cap < k0) {
+            cudaFree(c->Cprev); cudaFree(c->sig_old); c->Cprev = nullptr; c->sig_old = nullptr;
+            AKM_CUDA(h, cudaMalloc((void **)&c->Cprev, sizeof(double) * (size_t)k0 * d));
+            AKM_CUDA(h, cudaMalloc((void **)&c->sig_old, sizeof(float) * (size_t)k0));
+            c->prev_cap = k0;
+            use_seed = false;
+        }
+    }
+    static const bool no_seed_env = getenv("AKM_NOSEED") != nullptr;      // debugging aid
+    if (no_seed_env) use_seed = false;
+    const int k_prev = use_seed ? c->k_prev : 0;
     AKM_CUDA(h, cudaMemsetAsync(c->counters, 0, 4 * sizeof(int), h->stream));
-    c16_build_kernel<<<1, 1024, 0, h->stream>>>(C, clabel, k, kpad, d, d16, h->metric, rs.x16_shift, c->c16, c->cn, c->pc);
+    c16_build_kernel<<<1, 1024, 0, h->stream>>>(C, clabel, k, kpad, d, d16, h->metric, rs.x16_shift, c->c16, c->cn, c->pc,
+                                                c->Cprev, (chain == 1) ? remap : nullptr, k_prev, c->sig_old);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
 
     // shared-memory plan
     const size_t A_STAGE = (size_t)MB * KB * BOX_BYTES, B_STAGE = (size_t)KB * BOX_BYTES;
-    const size_t fixed = (size_t)kpad * 4 + (4 + 2 * MAX_BSLOTS + 4) * 8 + 64 + 1024;   // offsets, barriers, misc, alignment slack
+    const size_t fixed = (size_t)kpad * 4 + (4 + 2 * MAX_BSLOTS + 4) * 8 + 64 + (size_t)2 * MB * TILE_M * MAX_CAND * 8 +
+                         (size_t)MB * TILE_M * 16 + 1024;   // offsets, barriers, misc, candidate rings, exchange, alignment slack
     const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
     const int a_stages = 2;
     if (a_stages * A_STAGE + 2 * B_STAGE + fixed > budget) return exact_all();
@@ -805,6 +915,9 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     sp.cn = c->cn; sp.pc = c->pc; sp.xerr = rs.xerr; sp.labels = labels;
     sp.wl_rows = c->wl_rows; sp.wl_cand = c->wl_cand; sp.counters = c->counters;
     sp.eta = (float)(KB * KBLK + 32) * 2.3841858e-7f;       // (d16 + 32) * 2^-22
+    sp.useed = train_rows ? c->useed : nullptr;
+    sp.sig_old = c->sig_old;
+    sp.k_prev = k_prev;
     const int nsuper = (sp.groups + CL - 1) / CL;
     int grid = std::min(h->num_sms / CL, nsuper) * CL;
     if (grid < CL) grid = CL;
@@ -812,6 +925,12 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     if (KB == 1) rc = (CL == 2) ? launch_search<2, 1, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 1, 1>(h, mapX, mapC, sp, smem, grid);
     else rc = (CL == 2) ? launch_search<2, 2, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 2, 1>(h, mapX, mapC, sp, smem, grid);
     AKM_TRY(rc);
+    if (train_rows) {
+        AKM_CUDA(h, cudaMemcpyAsync(c->Cprev, C, sizeof(double) * (size_t)k * d, cudaMemcpyDeviceToDevice, h->stream));
+        c->k_prev = k; c->chain = chain; c->step_prev = h->step; c->seed_rows = rs.n; c->seed_x16 = rs.x16;
+    } else if (labels == h->labels) {
+        c->k_prev = 0;                       // somebody else's labels now live in the buffer the seeds refer to
+    }
     if (h->profiling && h->mid_event) { cudaEventRecord(h->mid_event, h->stream); h->mid_recorded = true; }
 
     // refinement: candidates first, then the exact list (lengths stay on the device)

@@ -203,6 +203,7 @@ typedef struct {
     int64_t kernel_launches;
     int32_t engine_used;      /* AKM_ENGINE_EXACT or AKM_ENGINE_TENSOR */
     int32_t storage_bytes;    /* 4 or 8 */
+    int64_t rows_exact_all;   /* subset of rows_refined that was evaluated against all k centroids */
 } akm_stats;
 int akm_get_stats(akm_handle h, akm_stats *out);
 

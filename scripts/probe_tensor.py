@@ -32,3 +32,28 @@ bad += run(20000, 128, 1000, 300, 4)
 bad += run(3000, 100, 257, 60, 5, native.COSINE)
 bad += run(70000, 128, 300, 100, 6)
 print("TOTAL MISMATCHES", bad)
+
+# multi-pass training: exercises the seeded thresholds (chain of akm_step passes)
+def train_check(n, d, k, kc, seed, metric=native.EUCLIDEAN, iters=8):
+    rng = np.random.default_rng(seed)
+    centers = rng.uniform(-10, 10, size=(kc, d))
+    X = (centers[rng.integers(0, kc, size=n)] + rng.normal(size=(n, d))).astype(np.float32).astype(np.float64)
+    C0 = X[rng.choice(n, k, replace=False)].copy()
+    ref = orc.train(metric, X, C0, max_iter=iters, tol=0.0, threads=16)
+    with native.Handle(d, metric) as h:
+        h.set_engine(native.ENGINE_TENSOR)
+        h.upload_rows(X)
+        m = h.train(C0, max_iter=iters, tol=0.0)
+        labels = h.get_labels()
+        st = h.stats()
+    bad = int((labels != ref["labels"]).sum())
+    cerr = float(np.abs(m["C"][:m["k"]] - ref["C"][:ref["k"]]).max()) if m["k"] == ref["k"] else -1
+    print("train n=%d d=%d k=%d metric=%d: mismatches=%d k=%d/%d max|dC|=%.3g certified=%d refined=%d" % (
+        n, d, k, metric, bad, m["k"], ref["k"], cerr, st["rows_certified"], st["rows_refined"]), flush=True)
+    return bad
+
+bad = 0
+bad += train_check(30000, 128, 1000, 300, 11)
+bad += train_check(30000, 64, 100, 100, 12)
+bad += train_check(20000, 100, 200, 50, 13, native.COSINE)
+print("TRAIN MISMATCHES", bad)

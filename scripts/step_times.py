@@ -1,0 +1,21 @@
+"""Per-step phase timings of the device-resident loop (debugging / tuning aid)."""
+import sys, os
+import numpy as np
+sys.path.insert(0, '.')
+from alink_b200 import native
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 20_000_000
+d, k, steps = 128, 1000, int(sys.argv[2]) if len(sys.argv) > 2 else 8
+h = native.Handle(d, native.EUCLIDEAN)
+h.reserve_rows(N)
+h.blobs_append(20260101, k, 0, N)
+C0 = h.blobs_rows(20260101, k, (np.arange(k, dtype=np.int64) * N) // k).astype(np.float64)
+h.set_centroids(C0)
+h.set_profiling(True)
+for s in range(steps):
+    h.get_profile(reset=True)
+    conv, kk, obj = h.step(0.0)
+    p = h.get_profile()
+    st = h.stats()
+    print("step %d: search %.2f refine %.2f acc %.2f upd %.2f ms | k=%d refined=%.2f%% exact_all=%.3f%% obj=%.6g" % (
+        s + 1, p["search_ms"], p["refine_ms"], p["accumulate_ms"], p["update_ms"], kk,
+        100.0 * st["rows_refined"] / max(1, st["rows"]), 100.0 * st["rows_exact_all"] / max(1, st["rows"]), obj), flush=True)
