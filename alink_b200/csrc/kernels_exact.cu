@@ -6,8 +6,11 @@
 // (dgemv 'T': BLAS.java:204-212; daxpy: BLAS.java:96-98; own dot: BLAS.java:103-110).
 // These kernels are the ground truth on the device: the tensor-core search
 // (kernels_tensor.cu) only proposes candidates and falls back to them.
+#include <algorithm>
 #include <cfloat>
 #include <climits>
+#include <cstdlib>
+#include <type_traits>
 
 #include "akm_internal.cuh"
 
@@ -353,11 +356,19 @@ int launch_assign_exact_list(akm_handle h, const RowStore &rs, const int32_t *ro
 // The objective is accumulated on the way: EUCL sum (x-c)^2 (robust form of D^2),
 // COS count - c.S.
 // =====================================================================================
-constexpr int ACC_THREADS = 512;
+constexpr int ACC_THREADS = 256;
 constexpr int ACC_MAX_CHUNK = 65536;   // row offsets are uint16
 
-template <typename T, int DC, int METRIC>
-__global__ void __launch_bounds__(ACC_THREADS)
+template <typename T> struct Vec16;
+template <> struct Vec16<float> { using type = float4; static constexpr int N = 4;
+    static __device__ __forceinline__ void unpack(const float4 &v, double (&o)[4]) { o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; } };
+template <> struct Vec16<double> { using type = double2; static constexpr int N = 2;
+    static __device__ __forceinline__ void unpack(const double2 &v, double (&o)[2]) { o[0] = v.x; o[1] = v.y; } };
+
+// VEC == true: each lane owns 16-byte column groups (lane + 32*m) -> one 128-bit load per row and group
+// (requires d % (16/sizeof(T)) == 0); VEC == false: scalar columns lane + 32*m (any d).
+template <typename T, int DC, int METRIC, bool VEC>
+__global__ void __launch_bounds__(ACC_THREADS, 2)
 accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, int64_t n, int d, int k0,
                   int chunk_rows, const double *__restrict__ C, double *__restrict__ sum,
                   double *__restrict__ objective) {
@@ -367,11 +378,13 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
     unsigned short *sorted = reinterpret_cast<unsigned short *>(cursor + k0 + ((k0 & 1) ? 1 : 0));
     __shared__ int scan_tmp[ACC_THREADS];
     __shared__ double obj_red[ACC_THREADS / 32];
+    constexpr int VN = VEC ? Vec16<T>::N : 1;               // columns per lane per group
+    constexpr int COLS_PER_PASS = DC * 32 * VN;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t base = (int64_t)blockIdx.x * chunk_rows;
     const int rows = (int)min((int64_t)chunk_rows, n - base);
-    const int cb0 = blockIdx.y * (DC * 32);
+    const int cb0 = blockIdx.y * COLS_PER_PASS;
 
     for (int j = tid; j <= k0; j += ACC_THREADS) off[j] = 0;
     __syncthreads();
@@ -383,7 +396,7 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
     // inclusive scan of off[1..k0] -> off[j] = start of cluster j
     {
         const int per = (k0 + ACC_THREADS - 1) / ACC_THREADS;
-        const int lo = tid * per, hi = min(k0, lo + per);
+        const int lo = min(k0, tid * per), hi = min(k0, lo + per);
         int s = 0;
         for (int j = lo; j < hi; ++j) s += off[j + 1];
         scan_tmp[tid] = s;
@@ -416,57 +429,75 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
     for (int j = warp; j < k0; j += ACC_THREADS / 32) {
         const int s = off[j], e = off[j + 1];
         if (s == e) continue;
-        double acc[DC], cen[DC], sq[DC];
+        double acc[DC][VN], cen[DC][VN], sq[DC][VN];
 #pragma unroll
-        for (int m = 0; m < DC; ++m) {
-            acc[m] = 0.0;
-            sq[m] = 0.0;
-            const int col = cb0 + lane + 32 * m;
-            cen[m] = (col < d) ? C[(size_t)j * d + col] : 0.0;
-        }
+        for (int m = 0; m < DC; ++m)
+#pragma unroll
+            for (int v = 0; v < VN; ++v) {
+                acc[m][v] = 0.0;
+                sq[m][v] = 0.0;
+                const int col = cb0 + (lane + 32 * m) * VN + v;
+                cen[m][v] = (col < d) ? C[(size_t)j * d + col] : 0.0;
+            }
+        constexpr int U = (DC * VN <= 4) ? 6 : ((DC * VN <= 8) ? 3 : 2);   // rows in flight per warp (register budget)
         int p = s;
-        constexpr int U = (DC <= 2) ? 8 : ((DC <= 4) ? 4 : 2);   // rows in flight per warp (register budget)
         for (; p + U <= e; p += U) {
-            double v[U][DC];
+            using RawT = typename std::conditional<VEC, typename Vec16<T>::type, T>::type;
+            RawT raw[U][DC];                      // loads stay in their storage type until they are consumed
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                const T *row = X + (base + sorted[p + u]) * (int64_t)d + cb0 + lane;
+                const T *row = X + (base + sorted[p + u]) * (int64_t)d + cb0;
 #pragma unroll
-                for (int m = 0; m < DC; ++m) v[u][m] = (cb0 + lane + 32 * m < d) ? (double)row[32 * m] : 0.0;
+                for (int m = 0; m < DC; ++m) {
+                    const int c0 = (lane + 32 * m) * VN;
+                    if (cb0 + c0 < d) raw[u][m] = *reinterpret_cast<const RawT *>(row + c0);
+                    else raw[u][m] = RawT{};
+                }
             }
 #pragma unroll
             for (int u = 0; u < U; ++u)
 #pragma unroll
                 for (int m = 0; m < DC; ++m) {
-                    acc[m] += v[u][m];
-                    if (METRIC == AKM_EUCLIDEAN) {
-                        const double df = v[u][m] - cen[m];
-                        sq[m] = fma(df, df, sq[m]);
+                    double val[VN];
+                    if constexpr (VEC) Vec16<T>::unpack(raw[u][m], val);
+                    else val[0] = (double)raw[u][m];
+#pragma unroll
+                    for (int v = 0; v < VN; ++v) {
+                        acc[m][v] += val[v];
+                        if (METRIC == AKM_EUCLIDEAN) {
+                            const double df = val[v] - cen[m][v];
+                            sq[m][v] = fma(df, df, sq[m][v]);
+                        }
                     }
                 }
         }
         for (; p < e; ++p) {
-            const T *row = X + (base + sorted[p]) * (int64_t)d + cb0 + lane;
+            const T *row = X + (base + sorted[p]) * (int64_t)d + cb0;
 #pragma unroll
-            for (int m = 0; m < DC; ++m) {
-                const double v = (cb0 + lane + 32 * m < d) ? (double)row[32 * m] : 0.0;
-                acc[m] += v;
-                if (METRIC == AKM_EUCLIDEAN) {
-                    const double df = v - cen[m];
-                    sq[m] = fma(df, df, sq[m]);
+            for (int m = 0; m < DC; ++m)
+#pragma unroll
+                for (int v = 0; v < VN; ++v) {
+                    const int c0 = (lane + 32 * m) * VN + v;
+                    const double x = (cb0 + c0 < d) ? (double)row[c0] : 0.0;
+                    acc[m][v] += x;
+                    if (METRIC == AKM_EUCLIDEAN) {
+                        const double df = x - cen[m][v];
+                        sq[m][v] = fma(df, df, sq[m][v]);
+                    }
                 }
-            }
         }
         double *out = sum + (size_t)j * (d + 1);
 #pragma unroll
-        for (int m = 0; m < DC; ++m) {
-            const int col = cb0 + lane + 32 * m;
-            if (col < d) {
-                atomicAdd(out + col, acc[m]);
-                if (METRIC == AKM_EUCLIDEAN) obj += sq[m];
-                else obj -= cen[m] * acc[m];
+        for (int m = 0; m < DC; ++m)
+#pragma unroll
+            for (int v = 0; v < VN; ++v) {
+                const int col = cb0 + (lane + 32 * m) * VN + v;
+                if (col < d) {
+                    atomicAdd(out + col, acc[m][v]);
+                    if (METRIC == AKM_EUCLIDEAN) obj += sq[m][v];
+                    else obj -= cen[m][v] * acc[m][v];
+                }
             }
-        }
         if (lane == 0 && blockIdx.y == 0) {
             atomicAdd(out + d, (double)(e - s));
             if (METRIC == AKM_COSINE) obj += (double)(e - s);
@@ -516,7 +547,6 @@ template <typename T, int METRIC>
 static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_t *labels, const double *C, int k0,
                                double *sum, double *objective) {
     const int d = h->d;
-    // chunk size: <= 65536 rows, aim for >= 4 CTAs per SM, bounded by shared memory
     const size_t fixed = (size_t)(2 * k0 + 2) * sizeof(int);
     const size_t budget = h->smem_optin > 8192 ? h->smem_optin - 8192 : 0;
     if (fixed + 2048 * 2 > budget) {
@@ -526,24 +556,51 @@ static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_
         AKM_CUDA(h, cudaGetLastError());
         return AKM_OK;
     }
-    int64_t chunk = ceil_div64(n, (int64_t)h->num_sms * 4);
+    // chunk of rows per CTA: large enough that one flush per (cluster, chunk) amortises, small enough that three
+    // CTAs fit the shared memory of an SM; row offsets inside a chunk are uint16
+    static const int env_chunk = getenv("AKM_ACC_CHUNK") ? atoi(getenv("AKM_ACC_CHUNK")) : 0;   // tuning aid
+    int64_t chunk = ceil_div64(n, (int64_t)h->num_sms * 6);
     chunk = ((chunk + 1023) / 1024) * 1024;
+    const int64_t cap3 = (int64_t)(((size_t)(h->smem_optin + 1024) / 3 - 4096 - fixed) / 2);
+    int64_t chunk_max = std::min<int64_t>(32768, std::max<int64_t>(2048, (cap3 / 1024) * 1024));
+    if (env_chunk > 0) chunk_max = env_chunk;
+    if (chunk > chunk_max) chunk = chunk_max;
     if (chunk > ACC_MAX_CHUNK) chunk = ACC_MAX_CHUNK;
     const int64_t max_by_smem = (int64_t)((budget - fixed) / 2);
     if (chunk > max_by_smem) chunk = (max_by_smem / 1024) * 1024;
     if (chunk < 1024) chunk = 1024;
     const size_t smem = fixed + (size_t)chunk * 2;
-    const int dc_need = (d + 31) / 32;
-    const int DCsel = dc_need >= 8 ? 8 : dc_need;
-    const dim3 grid((unsigned)ceil_div64(n, chunk), (unsigned)((d + DCsel * 32 - 1) / (DCsel * 32)));
-#define ACC_CASE(DCV)                                                                                          \
-    case DCV: {                                                                                                \
-        auto kern = accumulate_kernel<T, DCV, METRIC>;                                                         \
+    constexpr int VN = 16 / (int)sizeof(T);
+    const bool vec = (d % VN) == 0;
+    const int groups = vec ? (d / VN + 31) / 32 : (d + 31) / 32;       // 32-lane column groups needed
+    const int maxdc = vec ? (VN == 4 ? 2 : 4) : 8;                      // register budget: DC*VN <= 8
+    const int DCsel = groups >= maxdc ? maxdc : groups;
+    const int cols_per_pass = DCsel * 32 * (vec ? VN : 1);
+    const dim3 grid((unsigned)ceil_div64(n, chunk), (unsigned)((d + cols_per_pass - 1) / cols_per_pass));
+#define ACC_CASE(DCV, VECV)                                                                                    \
+    {                                                                                                          \
+        auto kern = accumulate_kernel<T, DCV, METRIC, VECV>;                                                   \
         AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
         kern<<<grid, ACC_THREADS, smem, h->stream>>>(X, labels, n, d, k0, (int)chunk, C, sum, objective);      \
-    } break
-    switch (DCsel) {
-        ACC_CASE(1); ACC_CASE(2); ACC_CASE(3); ACC_CASE(4); ACC_CASE(5); ACC_CASE(6); ACC_CASE(7); ACC_CASE(8);
+    }
+    if (vec) {
+        switch (DCsel) {
+            case 1: ACC_CASE(1, true) break;
+            case 2: ACC_CASE(2, true) break;
+            case 3: ACC_CASE(3, true) break;
+            default: ACC_CASE(4, true) break;
+        }
+    } else {
+        switch (DCsel) {
+            case 1: ACC_CASE(1, false) break;
+            case 2: ACC_CASE(2, false) break;
+            case 3: ACC_CASE(3, false) break;
+            case 4: ACC_CASE(4, false) break;
+            case 5: ACC_CASE(5, false) break;
+            case 6: ACC_CASE(6, false) break;
+            case 7: ACC_CASE(7, false) break;
+            default: ACC_CASE(8, false) break;
+        }
     }
 #undef ACC_CASE
     h->stats.kernel_launches++;

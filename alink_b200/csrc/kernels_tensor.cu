@@ -137,7 +137,8 @@ constexpr int TILE_M = 128;           // rows per MMA (TMEM lanes)
 constexpr int TILE_N = 128;           // centroids per tile (TMEM columns per accumulator)
 constexpr int KBLK = 64;              // halfs per 128-byte swizzled row
 constexpr int BOX_BYTES = TILE_M * KBLK * 2;   // 16 KB
-constexpr int MAX_CAND = 4;
+constexpr int MAX_CAND = 4;            // per column half (ring size)
+constexpr int WL_CAND = 8;             // per worklist entry (both halves)
 constexpr int MAX_BSLOTS = 16;
 constexpr float PAD_SCORE = 1.0e30f;  // score offset of padding centroids (never candidates)
 
@@ -162,7 +163,7 @@ struct SearchParams {
     const float2 *xerr;     // per row {||x||, ||x - x16||}
     int32_t *labels;
     int32_t *wl_rows;       // worklist: rows that need exact work
-    int32_t *wl_cand;       // MAX_CAND candidates per entry (-1 = unused, first == -2: all centroids)
+    int32_t *wl_cand;       // WL_CAND candidates per entry (-1 = unused, first == -2: all centroids)
     int *counters;          // [0] worklist length
     float eta;              // accumulation error factor
     // seeds: a rigorous upper bound of this pass's minimum score per row, derived from the previous pass
@@ -413,7 +414,7 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
             if (half == 1) { xch[0] = m; xch[1] = dropped; xch[2] = __int_as_float(ncand); }
             asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
             bool need_exact = false;
-            int cand[MAX_CAND];
+            int cand[WL_CAND];
             if (half == 0) {
                 const float m2 = xch[0], dropped2 = xch[1];
                 const int ncand2 = __float_as_int(xch[2]);
@@ -422,7 +423,7 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
                     const float thrF = mF + W;
                     int cnt = 0, best = -1;
 #pragma unroll
-                    for (int i = 0; i < MAX_CAND; ++i) cand[i] = -1;
+                    for (int i = 0; i < WL_CAND; ++i) cand[i] = -1;
 #pragma unroll
                     for (int h2 = 0; h2 < 2; ++h2) {
                         const float2 *ring = h2 ? peer_ring : my_ring;
@@ -432,17 +433,18 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
                             const float2 cv = ring[i];
                             if (i < nc && cv.y <= thrF) {
                                 const int j = __float_as_int(cv.x);
-                                if (cnt < MAX_CAND) cand[cnt] = j;
+#pragma unroll
+                                for (int u = 0; u < WL_CAND; ++u) if (u == cnt) cand[u] = j;
                                 if (cv.y == mF) best = j;
                                 ++cnt;
                             }
                         }
                     }
-                    const bool overflow = !(dropped > thrF) || !(dropped2 > thrF) || cnt > MAX_CAND;   // true for NaN too
+                    const bool overflow = !(dropped > thrF) || !(dropped2 > thrF);   // true for NaN too
                     if (best < 0 && cnt > 0) best = cand[0];
                     need_exact = overflow || cnt != 1 || best < 0 || best >= p.k;
 #pragma unroll
-                    for (int i = 0; i < MAX_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
+                    for (int i = 0; i < WL_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
                     if (overflow || best < 0 || best >= p.k) cand[0] = -2;
                     p.labels[row] = best;
                     if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
@@ -455,8 +457,9 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
                     if (need_exact) {
                         const int pos = base + __popc(mask & ((1u << lane) - 1));
                         p.wl_rows[pos] = (int32_t)row;
-#pragma unroll
-                        for (int i = 0; i < MAX_CAND; ++i) p.wl_cand[(size_t)pos * MAX_CAND + i] = cand[i];
+                        int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
+                        dst[0] = make_int4(cand[0], cand[1], cand[2], cand[3]);
+                        dst[1] = make_int4(cand[4], cand[5], cand[6], cand[7]);
                     }
                 }
             }
@@ -627,29 +630,41 @@ __global__ void refine_candidates_kernel(const T *__restrict__ X, const double *
     const int stride = (gridDim.x * blockDim.x) >> 5;
     for (; e < nwl; e += stride) {
         const int row = wl_rows[e];
-        int cand[MAX_CAND];
-#pragma unroll
-        for (int i = 0; i < MAX_CAND; ++i) cand[i] = wl_cand[(size_t)e * MAX_CAND + i];
+        int cand[WL_CAND];
+        {
+            const int4 c0 = *reinterpret_cast<const int4 *>(wl_cand + (size_t)e * WL_CAND);
+            const int4 c1 = *reinterpret_cast<const int4 *>(wl_cand + (size_t)e * WL_CAND + 4);
+            cand[0] = c0.x; cand[1] = c0.y; cand[2] = c0.z; cand[3] = c0.w;
+            cand[4] = c1.x; cand[5] = c1.y; cand[6] = c1.z; cand[7] = c1.w;
+        }
         bool to_exact = cand[0] == -2;
         int winner = -1;
         if (!to_exact) {
-            double acc[MAX_CAND];
+            const bool wide = cand[4] >= 0 || cand[5] >= 0 || cand[6] >= 0 || cand[7] >= 0;   // warp-uniform
+            double acc[WL_CAND];
 #pragma unroll
-            for (int i = 0; i < MAX_CAND; ++i) acc[i] = 0.0;
+            for (int i = 0; i < WL_CAND; ++i) acc[i] = 0.0;
+#pragma unroll 4
             for (int c = lane; c < d; c += 32) {
                 const double xv = (double)X[(int64_t)row * d + c];
 #pragma unroll
-                for (int i = 0; i < MAX_CAND; ++i)
+                for (int i = 0; i < 4; ++i)
                     if (cand[i] >= 0) acc[i] = fma(xv, C[(size_t)cand[i] * d + c], acc[i]);
+                if (wide) {
+#pragma unroll
+                    for (int i = 4; i < WL_CAND; ++i)
+                        if (cand[i] >= 0) acc[i] = fma(xv, C[(size_t)cand[i] * d + c], acc[i]);
+                }
             }
 #pragma unroll
-            for (int i = 0; i < MAX_CAND; ++i)
-                for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+            for (int i = 0; i < WL_CAND; ++i)
+                if (i < 4 || wide)
+                    for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
             const double xl = (METRIC == AKM_EUCLIDEAN) ? xlabel[row] : 1.0;
             double v1 = DBL_MAX, v2 = DBL_MAX, clmax = 0.0;
             int i1 = -1;
 #pragma unroll
-            for (int i = 0; i < MAX_CAND; ++i) {
+            for (int i = 0; i < WL_CAND; ++i) {
                 if (cand[i] < 0) continue;
                 const double cl = (METRIC == AKM_EUCLIDEAN) ? clabel[cand[i]] : 1.0;
                 clmax = fmax(clmax, cl);
@@ -854,7 +869,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
         cudaFree(c->wl_rows); cudaFree(c->wl_cand); cudaFree(c->exact_rows);
         c->wl_rows = c->wl_cand = c->exact_rows = nullptr;
         AKM_CUDA(h, cudaMalloc((void **)&c->wl_rows, sizeof(int32_t) * (size_t)rs.n));
-        AKM_CUDA(h, cudaMalloc((void **)&c->wl_cand, sizeof(int32_t) * (size_t)rs.n * MAX_CAND));
+        AKM_CUDA(h, cudaMalloc((void **)&c->wl_cand, sizeof(int32_t) * (size_t)rs.n * WL_CAND));
         AKM_CUDA(h, cudaMalloc((void **)&c->exact_rows, sizeof(int32_t) * (size_t)rs.n));
         c->wl_cap = rs.n;
     }
