@@ -66,7 +66,7 @@ def test_train_op_writes_reference_wire_format_and_matches_oracle():
     assert out.getColNames() == ["id", "cluster", "dist"]
     got = out.collect()
     assert got[5] == (99, None, None)
-    idx_ref, dist_ref, _ = orc.predict(orc.EUCLIDEAN, X[:5], ref["C"][: ref["k"]])
+    idx_ref, dist_ref, _ = orc.predict(orc.EUCLIDEAN, X[:5], md["centroids"])     # same model bytes on both sides
     assert [r[1] for r in got[:5]] == idx_ref.tolist() and [r[2] for r in got[:5]] == dist_ref.tolist()
 
 
