@@ -1,0 +1,73 @@
+package com.alibaba.alink.operator.common.clustering.kmeans.gpu;
+
+import com.alibaba.alink.common.comqueue.ComContext;
+import com.alibaba.alink.common.comqueue.ComputeFunction;
+import com.alibaba.alink.operator.batch.clustering.KMeansTrainBatchOp;
+import com.alibaba.alink.operator.common.distance.FastDistanceMatrixData;
+import com.alibaba.alink.operator.common.distance.FastDistanceVectorData;
+import org.apache.flink.api.java.tuple.Tuple2;
+
+/**
+ * Drop-in for KMeansAssignCluster (same ComContext keys, same outputs).  Superstep 1 uploads the cached
+ * partition once (the GPU analogue of the JVM-heap cache of BaseComQueue.java:497-527); every superstep then
+ * costs one k0 x d upload and one k0 x (d+1) download.
+ *
+ * Note: the cached samples were already label-updated by KMeansTrainBatchOp (prepareVectorData).  For
+ * EUCLIDEAN the vectors are untouched, so uploading them reproduces the labels bit for bit; for COSINE the
+ * vectors are already unit length and akm's normalisation (x * (1/||x||)) is applied to them once more, which
+ * can move the last bit -- to stay bit-identical build the handle before prepareVectorData (or skip the Java
+ * side normalisation when the GPU path is on).
+ */
+public class GpuKMeansAssignCluster extends ComputeFunction {
+    static final String HANDLE = "akmHandle";
+    private final int metric;
+    private final int device;
+
+    public GpuKMeansAssignCluster(int metric, int device) {
+        this.metric = metric;
+        this.device = device;
+    }
+
+    @Override
+    public void calc(ComContext context) {
+        Integer vectorSize = context.getObj(KMeansTrainBatchOp.VECTOR_SIZE);
+        Integer k = context.getObj(KMeansTrainBatchOp.K);
+        Tuple2<Integer, FastDistanceMatrixData> centroids = context.getStepNo() % 2 == 0
+            ? context.getObj(KMeansTrainBatchOp.CENTROID1) : context.getObj(KMeansTrainBatchOp.CENTROID2);
+        int k0 = centroids.f1.getVectors().numCols();
+
+        double[] sumMatrixData = context.getObj(KMeansTrainBatchOp.CENTROID_ALL_REDUCE);
+        if (sumMatrixData == null) {
+            sumMatrixData = new double[k0 * (vectorSize + 1)];
+            context.putObj(KMeansTrainBatchOp.CENTROID_ALL_REDUCE, sumMatrixData);
+        }
+        Iterable<FastDistanceVectorData> trainData = context.getObj(KMeansTrainBatchOp.TRAIN_DATA);
+        if (trainData == null) {
+            return;
+        }
+        Long handle = context.getObj(HANDLE);
+        if (handle == null) {
+            long[] h = new long[1];
+            AkmNative.check(0, AkmNative.create(device + context.getTaskId(), vectorSize, metric, h));
+            handle = h[0];
+            context.putObj(HANDLE, handle);
+            final int chunk = Math.max(1, (1 << 23) / vectorSize);      // 64 MB staging buffers
+            double[] buf = new double[chunk * vectorSize];
+            int filled = 0;
+            for (FastDistanceVectorData sample : trainData) {
+                double[] v = ((com.alibaba.alink.common.linalg.DenseVector) sample.getVector()).getData();
+                System.arraycopy(v, 0, buf, filled * vectorSize, vectorSize);
+                if (++filled == chunk) {
+                    AkmNative.check(handle, AkmNative.uploadRows(handle, buf, filled));
+                    filled = 0;
+                }
+            }
+            if (filled > 0) {
+                AkmNative.check(handle, AkmNative.uploadRows(handle, buf, filled));
+            }
+        }
+        // DenseMatrix is column-major d x k0 == row-major k0 x d: pass the backing array as is
+        AkmNative.check(handle, AkmNative.assignAccumulate(handle, centroids.f1.getVectors().getData(), k0, k,
+            sumMatrixData, null));
+    }
+}
