@@ -230,6 +230,24 @@ int akm_blobs_append(akm_handle h, uint64_t seed, int k_true, double spread, dou
 int akm_blobs_rows(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, const int64_t *rows,
                    int64_t m, float *out_host);
 
+/* Centroid update for callers that may not allocate device memory (no counterpart in the reference).
+ * Meant for hosts that share a GPU under a fixed memory reservation or run on a latency-critical thread:
+ * cudaMalloc/cudaFree can fail there and they stall every stream on the device.  The caller passes DEVICE
+ * pointers for input and output; the kernel's working memory (the empty-cluster compaction map) is a fixed
+ * array built into the library image (about 64 KB per GPU, held until the process exits), so this call
+ * performs no allocation at all and needs no handle.
+ *   sum_dev    double[k0*(d+1)] on `device`, the all-reduced accumulator
+ *   c_out_dev  double[k0*d] on `device`, fully rewritten exactly like akm_update_centroids does
+ *   k_out_dev  int on `device`, the new cluster count
+ * Limits and rules: k0 <= AKM_PREALLOC_MAX_K, otherwise AKM_ERR_BADARG.  All calls on a device share the
+ * built-in array and it keeps the previous call's contents (the call clears what it accumulates into), so
+ * calls that overlap on the GPU race: serialise them.  The first call on each device looks up the array's
+ * device address; make that call before any stream capture.  Work is enqueued on `cuda_stream` (may be
+ * NULL); outputs are valid once that stream has reached the end of the call's work. */
+#define AKM_PREALLOC_MAX_K 16384
+int akm_update_centroids_prealloc(int device, void *cuda_stream, int metric, int d, const double *sum_dev,
+                                  int k0, int k, double *c_out_dev, int *k_out_dev);
+
 #ifdef __cplusplus
 }
 #endif
