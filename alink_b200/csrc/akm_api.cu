@@ -2,6 +2,7 @@
 // per-partition work Alink's ComQueue stages perform (KMeansAssignCluster, AllReduce,
 // KMeansUpdateCentroids, KMeansIterTermination, KMeansOutputModel, KMeansModelMapper.map).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -41,9 +42,10 @@ static void dev_free(T *&p) {
 }
 
 static void rowstore_free(RowStore &rs) {
-    dev_free(rs.x32); dev_free(rs.x64); dev_free(rs.xlabel); dev_free(rs.x16); dev_free(rs.xerr);
+    dev_free(rs.x32); dev_free(rs.x64); dev_free(rs.xlabel); dev_free(rs.x16); dev_free(rs.xerr); dev_free(rs.orig);
     rs.n = rs.cap = 0;
     rs.x16_valid = false;
+    rs.x16_cap = 0; rs.orig_cap = rs.orig_n = 0; rs.reordered = false;
 }
 
 // Grow (or create) the exact store so that `need` rows fit; keeps existing rows.
@@ -139,6 +141,7 @@ static int upload_rows(akm_handle h, RowStore &rs, const void *src, SrcKind kind
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     rs.n += n;
     rs.x16_valid = false;
+    if (rs.reordered) AKM_TRY(ensure_orig(h, rs));   // appended rows keep their own index
     return AKM_OK;
 }
 
@@ -255,6 +258,21 @@ static void absorb_tensor_stats(akm_handle h) {
     }
 }
 
+// Keep the cached partition grouped by cluster (reorder.cu).  Policy: after the first tensor-engine pass, and
+// again whenever more than a quarter of the rows changed cluster since the last regrouping.
+static int maybe_reorder(akm_handle h, int k) {
+    static const int env = getenv("AKM_REORDER") ? atoi(getenv("AKM_REORDER")) : -1;   // 0 = never, 1 = policy
+    if (env == 0) return AKM_OK;
+    if (h->stats.engine_used != AKM_ENGINE_TENSOR || h->rows.n < h->reorder_min_rows) return AKM_OK;
+    h->changed_since_reorder += h->h_iscal[6];
+    const bool first = !h->rows.reordered;
+    if (!first && h->changed_since_reorder * 4 < h->rows.n) return AKM_OK;
+    AKM_TRY(reorder_rows_by_label(h, h->rows, h->labels, tensor_useed(h), k));
+    h->changed_since_reorder = 0;
+    h->reorders++;
+    return AKM_OK;
+}
+
 static int check_error_flag(akm_handle h) {
     // h_iscal[2] was copied back by the caller
     if (h->h_iscal[2] != 0) {
@@ -330,6 +348,8 @@ int akm_destroy(akm_handle h) {
     if (h->h_iscal) cudaFreeHost(h->h_iscal);
     if (h->stage) cudaFree(h->stage);
     if (h->hstage) cudaFreeHost(h->hstage);
+    if (h->reorder_scratch) cudaFree(h->reorder_scratch);
+    if (h->reorder_dest) cudaFree(h->reorder_dest);
     for (int i = 0; i < 5; ++i) if (h->pev[i]) cudaEventDestroy(h->pev[i]);
     if (h->mid_event) cudaEventDestroy(h->mid_event);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -416,13 +436,13 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
     AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], k0, s->sum, s->sum + L));
     AKM_CUDA(h, cudaMemcpyAsync(sum_out, s->sum, sizeof(double) * L, cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    if (labels_out)
-        AKM_CUDA(h, cudaMemcpyAsync(labels_out, h->labels, sizeof(int32_t) * (size_t)h->rows.n, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 5 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (labels_out) AKM_TRY(copy_rows_out_i32(h, h->rows, h->labels, labels_out, h->rows.n));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     absorb_tensor_stats(h);
     if (objective_out) *objective_out = h->h_dscal[0];
-    return check_error_flag(h);
+    AKM_TRY(check_error_flag(h));
+    return maybe_reorder(h, k);
 }
 
 int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int step_no, const double *prev,
@@ -477,6 +497,7 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     const int d = h->d, k0 = h->k0;
     const size_t L = (size_t)k0 * (size_t)(d + 1);
     const int s = ++h->step;
+    const int k_before = h->k;
     const int rd = (s % 2 == 0) ? 0 : 1;   // even: CENTROID1, odd: CENTROID2 (KMeansAssignCluster.java:38-42)
     const int wr = 1 - rd;
     AKM_TRY(ensure_labels(h, std::max<int64_t>(h->rows.n, 1)));
@@ -492,7 +513,7 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     AKM_TRY(launch_update(h, h->sum, h->k, k0, h->cent[wr], h->clabel[wr], h->cent[rd], h->clabel[rd],
                           /*new_is_c1=*/wr == 0, tol, h->shift, h->iscal));
     if (prof) cudaEventRecord(h->pev[3], h->stream);
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 6 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 7 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     absorb_tensor_stats(h);
@@ -516,7 +537,9 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     if (converged_out) *converged_out = h->h_iscal[1];
     if (k_out) *k_out = h->k;
     if (objective_out) *objective_out = h->h_dscal[0];
-    return check_error_flag(h);
+    AKM_TRY(check_error_flag(h));
+    // labels index the centroids this step assigned against (k_before clusters)
+    return maybe_reorder(h, k_before);
 }
 
 int akm_get_model(akm_handle h, double *c_out, int *k_out, double *weights_out, int *steps_out) {
@@ -542,7 +565,7 @@ int akm_get_labels(akm_handle h, int32_t *labels_out) {
     REQUIRE(h, labels_out, "labels_out is null");
     if (h->rows.n == 0) return AKM_OK;
     if (!h->labels || h->labels_cap < h->rows.n) return akm_fail(h, AKM_ERR_STATE, "no assignment pass has run");
-    AKM_CUDA(h, cudaMemcpyAsync(labels_out, h->labels, sizeof(int32_t) * (size_t)h->rows.n, cudaMemcpyDeviceToHost, h->stream));
+    AKM_TRY(copy_rows_out_i32(h, h->rows, h->labels, labels_out, h->rows.n));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     return AKM_OK;
 }
@@ -586,8 +609,8 @@ static int predict_store(akm_handle h, RowStore &rs, const double *dC, const dou
         AKM_TRY(run_assign(h, rs, dC, dl, k, k, h->labels, dist_out ? h->mind : nullptr));
     }
     AKM_TRY(launch_labels_to_i64(h, h->labels, n, s->idx64));
-    AKM_CUDA(h, cudaMemcpyAsync(idx_out, s->idx64, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
-    if (dist_out) AKM_CUDA(h, cudaMemcpyAsync(dist_out, h->mind, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    AKM_TRY(copy_rows_out_i64(h, rs, s->idx64, idx_out, n));
+    if (dist_out) AKM_TRY(copy_rows_out_f64(h, rs, h->mind, dist_out, n));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     if (!probs_out) absorb_tensor_stats(h);
@@ -734,4 +757,10 @@ extern "C" int akm_blobs_rows(akm_handle h, uint64_t seed, int k_true, double sp
     } while (0);
     cudaFree(drows); cudaFree(dout);
     return rc;
+}
+
+extern "C" int akm_set_option(akm_handle h, const char *name, double value) {
+    if (!h || !name) return akm_fail(h, AKM_ERR_BADARG, "null argument");
+    if (strcmp(name, "reorder_min_rows") == 0) { h->reorder_min_rows = (int64_t)value; return AKM_OK; }
+    return akm_fail(h, AKM_ERR_BADARG, std::string("unknown option: ") + name);
 }

@@ -28,6 +28,9 @@ struct RowStore {
     bool want16 = false;
     int x16_shift = 0;        // x16 = fp16(x * 2^x16_shift)
     bool x16_valid = false;
+    // cluster-ordered layout (reorder.cu): orig[pos] = caller's row index of the row now stored at pos
+    int32_t *orig = nullptr; int64_t orig_cap = 0, orig_n = 0;
+    bool reordered = false;
 };
 
 struct Scratch;   // akm_api.cu
@@ -66,6 +69,13 @@ struct akm_handle_s {
 
     // NCCL
     void *comm = nullptr; int rank = 0, world = 1;
+
+    // cluster-ordered layout scratch and policy state (reorder.cu)
+    void *reorder_scratch = nullptr; size_t reorder_scratch_bytes = 0;
+    int32_t *reorder_dest = nullptr; int64_t reorder_dest_cap = 0;
+    int64_t changed_since_reorder = 0;
+    int reorders = 0;
+    int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
 
     // optional per-phase profiling of akm_step
     bool profiling = false;
@@ -134,6 +144,14 @@ void tensor_free(akm_handle h);
 // ---------------------------------------------------------------- akm_nccl.cu
 int nccl_allreduce_device(akm_handle h, double *dbuf, int64_t count);
 void nccl_destroy(akm_handle h);
+
+// ---------------------------------------------------------------- reorder.cu
+int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *useed, int k);
+int ensure_orig(akm_handle h, RowStore &rs);
+int copy_rows_out_i32(akm_handle h, const RowStore &rs, const int32_t *dev, int32_t *host, int64_t n);
+int copy_rows_out_i64(akm_handle h, const RowStore &rs, const int64_t *dev, int64_t *host, int64_t n);
+int copy_rows_out_f64(akm_handle h, const RowStore &rs, const double *dev, double *host, int64_t n);
+float *tensor_useed(akm_handle h);   // kernels_tensor.cu: per-row seeds of the cached partition (may be null)
 
 // ---------------------------------------------------------------- blobs.cu
 int launch_blobs(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, const int64_t *rows_dev,

@@ -413,7 +413,7 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
             // ---- merge the two column halves of each row, then the certificate (half 0 owns the row)
             if (half == 1) { xch[0] = m; xch[1] = dropped; xch[2] = __int_as_float(ncand); }
             asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-            bool need_exact = false;
+            bool need_exact = false, changed = false;
             int cand[WL_CAND];
             if (half == 0) {
                 const float m2 = xch[0], dropped2 = xch[1];
@@ -446,9 +446,12 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
 #pragma unroll
                     for (int i = 0; i < WL_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
                     if (overflow || best < 0 || best >= p.k) cand[0] = -2;
+                    if (p.k_prev > 0 && p.labels[row] != best) changed = true;
                     p.labels[row] = best;
                     if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
                 }
+                const unsigned chm = __ballot_sync(0xffffffffu, changed);
+                if (chm && lane == 0) atomicAdd(p.counters + 2, __popc(chm));
                 const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
                 if (mask) {
                     int base = 0;
@@ -825,6 +828,11 @@ static int launch_search(akm_handle h, const CUtensorMap &mx, const CUtensorMap 
     return AKM_OK;
 }
 
+float *tensor_useed(akm_handle h) {
+    TensorCtx *c = (TensorCtx *)h->tc;
+    return (c && c->k_prev > 0) ? c->useed : nullptr;
+}
+
 void tensor_invalidate_seeds(akm_handle h) {
     TensorCtx *c = (TensorCtx *)h->tc;
     if (c) { c->k_prev = 0; c->chain = 0; }
@@ -971,7 +979,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
         AKM_CUDA(h, cudaGetLastError());
     }
     // counts for akm_get_stats (read back with the other scalars by the caller)
-    AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 4, c->counters, 2 * sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 4, c->counters, 3 * sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
     h->stats.engine_used = AKM_ENGINE_TENSOR;
     return AKM_OK;
 }

@@ -84,6 +84,7 @@ def lib():
         L.akm_predict_cached.argtypes = [_H, _c_dp, ctypes.c_int, _c_lp, _c_dp]
         L.akm_get_stats.argtypes = [_H, ctypes.POINTER(Stats)]
         L.akm_time_kernel.argtypes = [_H, ctypes.c_char_p, ctypes.c_int, _c_dp]
+        L.akm_set_option.argtypes = [_H, ctypes.c_char_p, ctypes.c_double]
         L.akm_set_profiling.argtypes = [_H, ctypes.c_int]
         L.akm_get_profile.argtypes = [_H, _c_dp, ctypes.c_int]
         L.akm_blobs_append.argtypes = [_H, ctypes.c_uint64, ctypes.c_int, ctypes.c_double, ctypes.c_double,
@@ -281,6 +282,9 @@ class Handle:
         ms = ctypes.c_double()
         self._ck(lib().akm_time_kernel(self._h, name.encode(), int(reps), ctypes.byref(ms)))
         return ms.value
+
+    def set_option(self, name, value):
+        self._ck(lib().akm_set_option(self._h, name.encode(), float(value)))
 
     def set_profiling(self, on=True):
         self._ck(lib().akm_set_profiling(self._h, 1 if on else 0))

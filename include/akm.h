@@ -212,6 +212,11 @@ int akm_get_stats(akm_handle h, akm_stats *out);
  * roofline object. name: "assign" | "accumulate". */
 int akm_time_kernel(akm_handle h, const char *name, int reps, double *ms_out);
 
+/* Tuning options (no reference counterpart).  "reorder_min_rows": partitions with at least this many rows are
+ * kept grouped by cluster inside the library (outputs are always returned in the caller's row order);
+ * default 262144, a huge value disables it. */
+int akm_set_option(akm_handle h, const char *name, double value);
+
 /* Per-phase device timing of akm_step with CUDA events on the handle's stream (off by default).
  * akm_get_profile fills out[0..4] = cumulative milliseconds of {nearest-centroid search, exact
  * refinement, per-cluster accumulation, all-reduce + centroid update} and the number of steps

@@ -265,3 +265,34 @@ def test_iris_config1():
         labels = h.get_labels()
     assert m["iters"] == ref["iters"] and (labels == ref["labels"]).all()
     np.testing.assert_allclose(m["C"][:3], ref["C"][:3], rtol=1e-12)
+
+
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_cluster_ordered_layout_is_invisible_to_the_caller(metric):
+    # the library regroups rows by cluster internally; labels, predictions and appended rows must still come
+    # back in the caller's order, and the training result must not change
+    n, d, k = 9000, 32, 24
+    X = blobs(n, d, 12, seed=77)
+    C0 = X[np.random.default_rng(1).choice(n, k, replace=False)].copy()
+    ref = orc.train(metric, X, C0, max_iter=6, tol=0.0)
+    with native.Handle(d, metric) as h:
+        h.set_engine(native.ENGINE_TENSOR)
+        h.set_option("reorder_min_rows", 1)
+        h.upload_rows(X[:7000])
+        h.set_centroids(C0)
+        h.step(0.0)                                     # rows get regrouped after this pass
+        h.upload_rows(X[7000:])                         # appended after a regrouping
+        h.set_centroids(C0)
+        for _ in range(6):
+            conv, kk, obj = h.step(0.0)
+        labels = h.get_labels()
+        m = h.get_model()
+        idx, dist = h.predict_cached(m["C"][: m["k"]])
+        s, _, l2 = h.assign_accumulate(ref["C"], k=ref["k"], want_labels=True)
+    assert (labels == ref["labels"]).all()
+    np.testing.assert_allclose(m["C"][: m["k"]], ref["C"][: ref["k"]], rtol=1e-9, atol=1e-12)
+    idx_r, dist_r, _ = orc.predict(metric, X, m["C"][: m["k"]])
+    assert (idx == idx_r).all() and (dist == dist_r).all()
+    Cp, s_ref, l_ref, _, _ = oracle_pass(metric, X, ref["C"], k=ref["k"]) if metric == native.EUCLIDEAN else (None, None, None, None, None)
+    if l_ref is not None:
+        assert (l2 == l_ref).all()
