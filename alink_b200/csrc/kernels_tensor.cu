@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 
 #include "akm_internal.cuh"
@@ -101,6 +102,19 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// Same MMA with the descriptors passed as 32-bit halves: only the low word (start address) varies per
+// instruction, so the issuing thread spends a single integer add per operand between MMAs.
+__device__ __forceinline__ void umma_f16_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -139,6 +153,7 @@ constexpr int KBLK = 64;              // halfs per 128-byte swizzled row
 constexpr int BOX_BYTES = TILE_M * KBLK * 2;   // 16 KB
 constexpr int MAX_CAND = 4;            // per column half (ring size)
 constexpr int WL_CAND = 8;             // per worklist entry (both halves)
+constexpr int WL_BLOCK = 2048;         // worklist slots a warp reserves at a time
 constexpr int MAX_BSLOTS = 16;
 constexpr float PAD_SCORE = 1.0e30f;  // score offset of padding centroids (never candidates)
 
@@ -164,12 +179,15 @@ struct SearchParams {
     int32_t *labels;
     int32_t *wl_rows;       // worklist: rows that need exact work
     int32_t *wl_cand;       // WL_CAND candidates per entry (-1 = unused, first == -2: all centroids)
-    int *counters;          // [0] worklist length
+    int *counters;          // [0] reserved worklist slots, [2] labels changed, [3] worklist entries used
     float eta;              // accumulation error factor
     // seeds: a rigorous upper bound of this pass's minimum score per row, derived from the previous pass
     float *useed;           // in: previous pass min score + its error bound; out: same for this pass (nullable)
     const float *sig_old;   // per OLD label: distance its centroid moved (INF if the cluster was dropped)
     int k_prev;             // 0: no seeds this pass
+    const float2 *wm;       // per row {window W, seeded upper bound of the minimum score (INF: none)} from rowprep_kernel
+    int dbg;                // tuning aid: 1 = skip score processing, 2 = also skip the TMEM loads
+    long long *trace;       // tuning aid: clock64 stamps of CTA 0 (nullable)
 };
 
 // ------------------------------------------------------------------------------------------ search kernel
@@ -255,8 +273,10 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
                     for (int t = 0; t < p.ntiles; ++t, ++b_it) {
                         const int slot = b_it % p.b_slots;
                         const uint32_t ph = (b_it / p.b_slots) & 1;
-                        mbar_wait(smem_u32(b_empty + slot), ph ^ 1);
-                        load_b(slot, t);
+                        if (!(p.dbg & 4)) {
+                            mbar_wait(smem_u32(b_empty + slot), ph ^ 1);
+                            load_b(slot, t);
+                        }
                         // next group's rows go out after this group's first centroid tile, so the tile
                         // stream never waits behind the (longer) wait for a free row stage
                         if (more && t == 0) load_a(a_it++, sg + nclusters);
@@ -266,30 +286,36 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
         }
     } else if (warp == 1) {
         // =============================== MMA issuer (one thread)
+        // descriptor = lo word (start address >> 4 | LBO = 1 << 16) + constant hi word (SBO, version, swizzle)
+        constexpr uint32_t DESC_HI = 64u | (1u << 14) | (2u << 29);
+        const uint32_t a_lo0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+        const uint32_t b_lo0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) | (1u << 16);
         int a_it = 0, b_it = 0, t_it = 0;
         for (int sg = cluster_id; sg < nsuper; sg += nclusters, ++a_it) {
             const int as = a_it % p.a_stages;
             mbar_wait(smem_u32(a_full + as), (a_it / p.a_stages) & 1);
             for (int t = 0; t < p.ntiles; ++t, ++b_it, ++t_it) {
                 const int slot = p.resident ? t : (b_it % p.b_slots);
-                mbar_wait(smem_u32(b_full + slot), p.resident ? 0u : (uint32_t)((b_it / p.b_slots) & 1));
+                if (!(p.dbg & 4)) mbar_wait(smem_u32(b_full + slot), p.resident ? 0u : (uint32_t)((b_it / p.b_slots) & 1));
                 const int tb = t_it & 1;
                 mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
                 tc_fence_after();
-                if (lane == 0) {
+                if (lane == 0 && !(p.dbg & 8)) {
+                    const uint32_t a_lo = a_lo0 + (uint32_t)as * (A_STAGE >> 4);
+                    const uint32_t b_lo = b_lo0 + (uint32_t)slot * (B_STAGE >> 4);
+                    const uint32_t d0 = tmem_base + (uint32_t)(tb * MB * TILE_N);
 #pragma unroll
-                    for (int rb = 0; rb < MB; ++rb) {
-                        const uint32_t d_tmem = tmem_base + (uint32_t)(tb * MB * TILE_N + rb * TILE_N);
+                    for (int rb = 0; rb < MB; ++rb)
 #pragma unroll
-                        for (int kb = 0; kb < KB; ++kb) {
-                            const uint64_t ad = make_desc(smem_u32(a_smem + (size_t)as * A_STAGE + (rb * KB + kb) * BOX_BYTES));
-                            const uint64_t bd = make_desc(smem_u32(b_smem + (size_t)slot * B_STAGE + kb * BOX_BYTES));
+                        for (int kb = 0; kb < KB; ++kb)
 #pragma unroll
                             for (int k4 = 0; k4 < KBLK / 16; ++k4)
-                                umma_f16(d_tmem, ad + 2 * k4, bd + 2 * k4, IDESC_F16_128x128, (kb | k4) != 0);
-                        }
-                    }
-                    if (!p.resident) {
+                                umma_f16_lo(d0 + rb * TILE_N, a_lo + (uint32_t)(((rb * KB + kb) * BOX_BYTES) >> 4) + 2 * k4,
+                                            b_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4, DESC_HI, IDESC_F16_128x128,
+                                            (kb | k4) != 0);
+                }
+                if (lane == 0) {
+                    if (!p.resident && !(p.dbg & 4)) {
                         if (CL > 1) umma_commit_mc(smem_u32(b_empty + slot), (uint16_t)((1u << CL) - 1));
                         else umma_commit(smem_u32(b_empty + slot));
                     }
@@ -309,45 +335,32 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
         const int sub = e >> 2;
         const int rb = sub >> 1, half = sub & 1;
         const int q = warp & 3;
-        const float c16_max = pc_s[0], dc_max = pc_s[1], c_max = pc_s[2], scale = pc_s[3];
+        const float scale = pc_s[3];
         const int rt = rb * TILE_M + q * 32 + lane;                 // row slot within the CTA's group
         float2 *my_ring = cand_s + ((size_t)half * (MB * TILE_M) + rt) * MAX_CAND;
         float2 *peer_ring = cand_s + ((size_t)1 * (MB * TILE_M) + rt) * MAX_CAND;
         float *xch = reinterpret_cast<float *>(cand_s + (size_t)2 * MB * TILE_M * MAX_CAND) + rt * 4;   // {m, dropped, ncand}
         const int bar_id = 1 + rb * 4 + q;
         int t_it = 0;
+        int wl_pos = 0, wl_end = 0, wl_used = 0;        // this warp's reserved worklist block
+        // per-row window and seed come precomputed (rowprep_kernel) and are fetched one group ahead
+        auto fetch_wm = [&](int sg_, float2 &wm_, int &a_) {
+            wm_ = make_float2(0.f, INFINITY); a_ = -1;
+            if (sg_ < nsuper) {
+                const int64_t row_ = (((int64_t)sg_ * CL + rank) * MB + rb) * TILE_M + q * 32 + lane;
+                if (row_ < p.n) { wm_ = p.wm[row_]; a_ = (p.k_prev > 0 && half == 0) ? p.labels[row_] : -1; }
+            }
+        };
+        float2 wm_next; int a_next;
+        fetch_wm(cluster_id, wm_next, a_next);
         for (int sg = cluster_id; sg < nsuper; sg += nclusters) {
             const int64_t row = (((int64_t)sg * CL + rank) * MB + rb) * TILE_M + q * 32 + lane;
             const bool valid = row < p.n;
-            float W = 0.f, m = INFINITY;
-            if (valid) {
-                const float2 xe = p.xerr[row];
-                const float r = xe.x, er = xe.y;
-                const float rc = r + c_max;
-                // |S - true| <= 2(|dx||c16| + |x||dc|) + 2 eta |x16||c16| + fp32 epilogue rounding
-                const float B = 2.f * (er * c16_max + r * dc_max) + 2.f * p.eta * (r + er) * c16_max + 4.8e-7f * rc * rc;
-                const float epsJ = (float)(p.d + 16) * 4.5e-16f * rc * rc;    // Java's own fp64 rounding
-                W = 2.004f * B + 2.f * epsJ + 1e-30f;
-                if (pc_s[4] != 0.f) W = NAN;                                  // non-finite centroids: everything goes exact
-                if (p.k_prev > 0) {
-                    // Seed: the previous winner a had true score <= useed (its approximate minimum + bound); its
-                    // centroid moved by sig_old[a], so this pass's minimum approximate score is at most u.
-                    const int a = p.labels[row];
-                    if (a >= 0 && a < p.k_prev) {
-                        const float sg_a = p.sig_old[a];
-                        const float u0 = p.useed[row];
-                        float u;
-                        if (p.metric == AKM_EUCLIDEAN) {
-                            const float r2 = r * r;
-                            const float t = sqrtf(fmaxf(u0 + r2 * 1.000001f, 0.f)) * 1.000001f + sg_a;
-                            u = t * t * 1.000001f - r2 * 0.999998f + 0.5f * W + 1e-5f * (t * t + r2);
-                        } else {
-                            u = u0 + sg_a * (r + er) * 1.000001f + 0.5f * W + 1e-6f;
-                        }
-                        if (u == u) m = u;                                    // NaN: no seed
-                    }
-                }
-            }
+            const float2 wm = wm_next;
+            const int a_old = a_next;
+            fetch_wm(sg + nclusters, wm_next, a_next);
+            const float W = wm.x;
+            float m = wm.y;
             float thr = valid ? m + W : -INFINITY;       // padding rows never enter the candidate path
             int ncand = 0;
             float dropped = INFINITY;
@@ -446,7 +459,7 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
 #pragma unroll
                     for (int i = 0; i < WL_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
                     if (overflow || best < 0 || best >= p.k) cand[0] = -2;
-                    if (p.k_prev > 0 && p.labels[row] != best) changed = true;
+                    if (p.k_prev > 0 && a_old != best) changed = true;
                     p.labels[row] = best;
                     if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
                 }
@@ -454,9 +467,19 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
                 if (chm && lane == 0) atomicAdd(p.counters + 2, __popc(chm));
                 const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
                 if (mask) {
-                    int base = 0;
-                    if (lane == 0) base = atomicAdd(p.counters, __popc(mask));
-                    base = __shfl_sync(0xffffffffu, base, 0);
+                    // Worklist slots are reserved WL_BLOCK at a time per warp, so the (slow) returning atomic is
+                    // off the per-group critical path; unused slots of a block are marked empty (row = -1).
+                    const int cnt = __popc(mask);
+                    if (wl_pos + cnt > wl_end) {
+                        for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
+                        int base = 0;
+                        if (lane == 0) base = atomicAdd(p.counters, WL_BLOCK);
+                        wl_pos = __shfl_sync(0xffffffffu, base, 0);
+                        wl_end = wl_pos + WL_BLOCK;
+                    }
+                    const int base = wl_pos;
+                    wl_pos += cnt;
+                    wl_used += cnt;
                     if (need_exact) {
                         const int pos = base + __popc(mask & ((1u << lane) - 1));
                         p.wl_rows[pos] = (int32_t)row;
@@ -468,12 +491,371 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
             }
             asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // rings may be reused for the next group
         }
+        if (half == 0) {
+            for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
+            if (lane == 0 && wl_used) atomicAdd(p.counters + 3, wl_used);
+        }
     }
     // ---- teardown
     tc_fence_before();
     __syncthreads();
     if (CL > 1) cluster_sync_all();
     if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------ per-row window / seed
+// Runs once per pass before the search: everything the epilogue needs per row that lives in global memory
+// (norms, previous label -> centroid movement, previous minimum) is folded into two floats, so the search
+// kernel's per-group prologue is a single coalesced load.
+//   W  = 2.004 * B + 2 * eps_J   (NaN when the centroids are not finite -> every row goes exact)
+//   m0 = rigorous upper bound of this pass's minimum approximate score (INF when there is no seed):
+//        the previous winner a had true score <= useed; its centroid moved by sig_old[a].
+__global__ void rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restrict__ pc,
+                               const float2 *__restrict__ xerr, const int32_t *__restrict__ labels,
+                               const float *__restrict__ useed, const float *__restrict__ sig_old, int k_prev,
+                               float2 *__restrict__ wm) {
+    const float c16_max = pc->c16_max, dc_max = pc->dc_max, c_max = pc->c_max;
+    const bool bad = pc->bad != 0;
+    int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; row < n; row += stride) {
+        const float2 xe = xerr[row];
+        const float r = xe.x, er = xe.y;
+        const float rc = r + c_max;
+        // |S - true| <= 2(|dx||c16| + |x||dc|) + 2 eta |x16||c16| + fp32 epilogue rounding
+        const float B = 2.f * (er * c16_max + r * dc_max) + 2.f * eta * (r + er) * c16_max + 4.8e-7f * rc * rc;
+        const float epsJ = (float)(d + 16) * 4.5e-16f * rc * rc;    // Java's own fp64 rounding
+        float W = 2.004f * B + 2.f * epsJ + 1e-30f;
+        if (bad) W = NAN;
+        float m0 = INFINITY;
+        if (k_prev > 0) {
+            const int a = labels[row];
+            if (a >= 0 && a < k_prev) {
+                const float sg_a = sig_old[a], u0 = useed[row];
+                float u;
+                if (metric == AKM_EUCLIDEAN) {
+                    const float r2 = r * r;
+                    const float t = sqrtf(fmaxf(u0 + r2 * 1.000001f, 0.f)) * 1.000001f + sg_a;
+                    u = t * t * 1.000001f - r2 * 0.999998f + 0.5f * W + 1e-5f * (t * t + r2);
+                } else {
+                    u = u0 + sg_a * (r + er) * 1.000001f + 0.5f * W + 1e-6f;
+                }
+                if (u == u) m0 = u;                                 // NaN: no seed
+            }
+        }
+        wm[row] = make_float2(W, m0);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ pair kernel
+// cta_group::2 variant for the case where the whole fp16 centroid matrix fits the shared memory of a CTA
+// PAIR (each CTA keeps half of every 256-centroid tile): centroids are loaded once per CTA and never move
+// again, one thread of the leader CTA issues M=256 x N=256 x K=16 MMAs that read A and B from both CTAs'
+// shared memory and write each CTA's 128 rows x 256 columns into its own TMEM.  Per CTA: 2 stages of X16
+// rows (128 rows each) + resident centroids + score offsets + candidate rings.
+namespace {
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap *map, uint32_t leader_bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_f16_2sm(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"(mask) : "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(bar), "r"(cta));
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;   // clears the CTA-pair bit: address of the leader CTA's copy
+constexpr uint32_t IDESC_F16_256x256 = (1u << 4) | ((256u >> 3) << 17) | ((256u >> 4) << 24);
+constexpr int PAIR_N = 256;                       // centroids per tile (128 per CTA)
+}  // namespace
+
+template <int KB>
+__global__ void __launch_bounds__(576, 1)
+search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__ CUtensorMap tmapC,
+                   const SearchParams p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    constexpr int A_STAGE = KB * BOX_BYTES;            // 128 rows of this CTA
+    constexpr int B_TILE = KB * BOX_BYTES;             // this CTA's 128 centroids of a 256-centroid tile
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int pair_id = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int nt = p.ntiles;                           // tiles of 256 centroids
+
+    unsigned char *a_smem = smem;
+    unsigned char *b_smem = smem + 2 * A_STAGE;
+    float *cn_s = reinterpret_cast<float *>(b_smem + (size_t)nt * B_TILE);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(cn_s + nt * PAIR_N);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *b_full = bars + 4, *t_full = bars + 5, *t_empty = bars + 7;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 9);
+    float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);
+    float2 *cand_s = reinterpret_cast<float2 *>(pc_s + 8);                 // [4 quarters][128 rows][MAX_CAND]
+    float *xch_s = reinterpret_cast<float *>(cand_s + 4 * TILE_M * MAX_CAND);   // [4 quarters][128 rows][4]
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
+        mbar_init(smem_u32(b_full), 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), 32); }
+        fence_barrier_init();
+        pc_s[0] = p.pc->c16_max; pc_s[1] = p.pc->dc_max; pc_s[2] = p.pc->c_max; pc_s[3] = p.pc->score_scale;
+        pc_s[4] = p.pc->bad ? 1.f : 0.f;
+    }
+    for (int i = threadIdx.x; i < nt * PAIR_N; i += blockDim.x) cn_s[i] = p.cn[i];
+    if (warp == 1) tmem_alloc_2sm(smem_u32(tmem_slot), 512);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int ngroups = (int)((p.n + 2 * TILE_M - 1) / (2 * TILE_M));     // 256 rows per pair and group
+
+    if (warp == 0) {
+        // =============================== TMA producer (both CTAs; completion lands on the leader's barriers)
+        if (lane == 0) {
+            const uint32_t bfull_leader = smem_u32(b_full) & PEER_BIT_MASK;
+            if (leader) mbar_expect_tx(smem_u32(b_full), 2u * (uint32_t)nt * B_TILE);
+            for (int t = 0; t < nt; ++t)
+                for (int kb = 0; kb < KB; ++kb)
+                    tma_load_2d_2sm(smem_u32(b_smem + (size_t)t * B_TILE + kb * BOX_BYTES), &tmapC, bfull_leader, kb * KBLK,
+                                    t * PAIR_N + (int)rank * TILE_M);
+            int it = 0;
+            for (int g = pair_id; g < ngroups; g += npairs, ++it) {
+                const int as = it & 1;
+                mbar_wait(smem_u32(a_empty + as), ((it >> 1) & 1) ^ 1);
+                if (leader) mbar_expect_tx(smem_u32(a_full + as), 2u * A_STAGE);
+                const uint32_t afull_leader = smem_u32(a_full + as) & PEER_BIT_MASK;
+                const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
+                for (int kb = 0; kb < KB; ++kb)
+                    tma_load_2d_2sm(smem_u32(a_smem + (size_t)as * A_STAGE + kb * BOX_BYTES), &tmapX, afull_leader, kb * KBLK,
+                                    (int)row0);
+            }
+        }
+    } else if (warp == 1) {
+        // =============================== MMA issuer: one thread of the leader CTA drives both tensor cores
+        if (leader) {
+            constexpr uint32_t DESC_HI = 64u | (1u << 14) | (2u << 29);
+            const uint32_t a_lo0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+            const uint32_t b_lo0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+            mbar_wait(smem_u32(b_full), 0);
+            int it = 0, t_it = 0;
+            for (int g = pair_id; g < ngroups; g += npairs, ++it) {
+                const int as = it & 1;
+                mbar_wait(smem_u32(a_full + as), (it >> 1) & 1);
+                for (int t = 0; t < nt; ++t, ++t_it) {
+                    const int tb = t_it & 1;
+                    mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t a_lo = a_lo0 + (uint32_t)as * (A_STAGE >> 4);
+                        const uint32_t b_lo = b_lo0 + (uint32_t)t * (B_TILE >> 4);
+                        const uint32_t d0 = tmem_base + (uint32_t)(tb * PAIR_N);
+#pragma unroll
+                        for (int kb = 0; kb < KB; ++kb)
+#pragma unroll
+                            for (int k4 = 0; k4 < KBLK / 16; ++k4)
+                                umma_f16_2sm(d0, a_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4,
+                                             b_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4, DESC_HI, IDESC_F16_256x256,
+                                             (kb | k4) != 0);
+                        umma_commit_2sm(smem_u32(t_full + tb), 3);
+                    }
+                    __syncwarp();
+                }
+                if (lane == 0) umma_commit_2sm(smem_u32(a_empty + as), 3);
+                __syncwarp();
+            }
+        }
+    } else {
+        // =============================== epilogue: 16 warps per CTA, one thread per (row, 64-column quarter)
+        const int e = warp - 2;
+        const int quarter = e >> 2;
+        const int q = warp & 3;
+        const float scale = pc_s[3];
+        const int rt = q * 32 + lane;
+        float2 *my_ring = cand_s + ((size_t)quarter * TILE_M + rt) * MAX_CAND;
+        float *my_xch = xch_s + ((size_t)quarter * TILE_M + rt) * 4;
+        const int bar_id = 1 + q;
+        int t_it = 0;
+        int wl_pos = 0, wl_end = 0, wl_used = 0;
+        float2 wm_next = make_float2(0.f, INFINITY);
+        int a_next = -1;
+        {
+            const int64_t row0 = (int64_t)pair_id * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+            if (pair_id < ngroups && row0 < p.n) { wm_next = p.wm[row0]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[row0] : -1; }
+        }
+        for (int g = pair_id; g < ngroups; g += npairs) {
+            const int64_t row = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+            const bool valid = row < p.n;
+            const float2 wm = wm_next;
+            const int a_old = a_next;
+            {   // prefetch the next group's two floats (and old label) while this group is processed
+                const int64_t rown = (int64_t)(g + npairs) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+                if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[rown] : -1; }
+            }
+            const float W = wm.x;
+            float m = wm.y;
+            float thr = valid ? m + W : -INFINITY;
+            int ncand = 0;
+            float dropped = INFINITY;
+
+            for (int t = 0; t < nt; ++t, ++t_it) {
+                const int tb = t_it & 1;
+                mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * PAIR_N + quarter * 64);
+#pragma unroll 1
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v[32];
+                    __syncwarp();
+                    tmem_ld32(taddr + c * 32, v);
+                    tmem_ld_wait();
+                    if (c == 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);   // the leader's MMA thread waits on it
+                    }
+                    const int j0 = t * PAIR_N + quarter * 64 + c * 32;
+                    const float *cn_t = cn_s + j0;
+                    float sc[32];
+#pragma unroll
+                    for (int gq = 0; gq < 8; ++gq) {
+                        const float4 o = *reinterpret_cast<const float4 *>(cn_t + gq * 4);
+                        sc[gq * 4 + 0] = fmaf(__uint_as_float(v[gq * 4 + 0]), scale, o.x);
+                        sc[gq * 4 + 1] = fmaf(__uint_as_float(v[gq * 4 + 1]), scale, o.y);
+                        sc[gq * 4 + 2] = fmaf(__uint_as_float(v[gq * 4 + 2]), scale, o.z);
+                        sc[gq * 4 + 3] = fmaf(__uint_as_float(v[gq * 4 + 3]), scale, o.w);
+                    }
+                    float g8[4];
+#pragma unroll
+                    for (int gq = 0; gq < 4; ++gq) {
+                        const float a1 = fminf(fminf(sc[gq * 8 + 0], sc[gq * 8 + 1]), sc[gq * 8 + 2]);
+                        const float a2 = fminf(fminf(sc[gq * 8 + 3], sc[gq * 8 + 4]), sc[gq * 8 + 5]);
+                        g8[gq] = fminf(fminf(sc[gq * 8 + 6], sc[gq * 8 + 7]), fminf(a1, a2));
+                    }
+                    const float cmin = fminf(fminf(g8[0], g8[1]), fminf(g8[2], g8[3]));
+                    m = fminf(m, cmin);
+                    thr = valid ? m + W : -INFINITY;
+                    if (cmin <= thr) {
+#pragma unroll
+                        for (int gq = 0; gq < 4; ++gq) {
+                            if (g8[gq] <= thr) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    if (sc[gq * 8 + i] <= thr) {
+                                        const int slot = ncand & (MAX_CAND - 1);
+                                        if (ncand >= MAX_CAND) dropped = fminf(dropped, my_ring[slot].y);
+                                        my_ring[slot] = make_float2(__int_as_float(j0 + gq * 8 + i), sc[gq * 8 + i]);
+                                        ++ncand;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            // ---- merge the four column quarters of each row (quarter 0 owns the row), then the certificate
+            if (quarter != 0) { my_xch[0] = m; my_xch[1] = dropped; my_xch[2] = __int_as_float(ncand); }
+            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+            if (quarter == 0) {
+                bool need_exact = false, changed = false;
+                int cand[WL_CAND];
+                if (valid) {
+                    float mF = m;
+                    bool overflow = false;
+#pragma unroll
+                    for (int qq = 1; qq < 4; ++qq) mF = fminf(mF, xch_s[((size_t)qq * TILE_M + rt) * 4 + 0]);
+                    const float thrF = mF + W;
+                    int cnt = 0, best = -1;
+#pragma unroll
+                    for (int i = 0; i < WL_CAND; ++i) cand[i] = -1;
+#pragma unroll
+                    for (int qq = 0; qq < 4; ++qq) {
+                        const float2 *ring = cand_s + ((size_t)qq * TILE_M + rt) * MAX_CAND;
+                        const int nc = qq ? __float_as_int(xch_s[((size_t)qq * TILE_M + rt) * 4 + 2]) : ncand;
+                        const float dr = qq ? xch_s[((size_t)qq * TILE_M + rt) * 4 + 1] : dropped;
+                        overflow = overflow || !(dr > thrF);
+#pragma unroll
+                        for (int i = 0; i < MAX_CAND; ++i) {
+                            const float2 cv = ring[i];
+                            if (i < nc && cv.y <= thrF) {
+                                const int j = __float_as_int(cv.x);
+#pragma unroll
+                                for (int u = 0; u < WL_CAND; ++u) if (u == cnt) cand[u] = j;
+                                if (cv.y == mF) best = j;
+                                ++cnt;
+                            }
+                        }
+                    }
+                    overflow = overflow || cnt > WL_CAND;
+                    if (best < 0 && cnt > 0) best = cand[0];
+                    need_exact = overflow || cnt != 1 || best < 0 || best >= p.k;
+#pragma unroll
+                    for (int i = 0; i < WL_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
+                    if (overflow || best < 0 || best >= p.k) cand[0] = -2;
+                    if (p.k_prev > 0 && a_old != best) changed = true;
+                    p.labels[row] = best;
+                    if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
+                }
+                const unsigned chm = __ballot_sync(0xffffffffu, changed);
+                if (chm && lane == 0) atomicAdd(p.counters + 2, __popc(chm));
+                const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
+                if (mask) {
+                    const int cnt = __popc(mask);
+                    if (wl_pos + cnt > wl_end) {
+                        for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
+                        int base = 0;
+                        if (lane == 0) base = atomicAdd(p.counters, WL_BLOCK);
+                        wl_pos = __shfl_sync(0xffffffffu, base, 0);
+                        wl_end = wl_pos + WL_BLOCK;
+                    }
+                    const int base = wl_pos;
+                    wl_pos += cnt;
+                    wl_used += cnt;
+                    if (need_exact) {
+                        const int pos = base + __popc(mask & ((1u << lane) - 1));
+                        p.wl_rows[pos] = (int32_t)row;
+                        int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
+                        dst[0] = make_int4(cand[0], cand[1], cand[2], cand[3]);
+                        dst[1] = make_int4(cand[4], cand[5], cand[6], cand[7]);
+                    }
+                }
+            }
+            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        }
+        if (quarter == 0) {
+            for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
+            if (lane == 0 && wl_used) atomicAdd(p.counters + 3, wl_used);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc_2sm(tmem_base, 512);
 }
 
 // ------------------------------------------------------------------------------------------ operand preparation
@@ -633,6 +1015,7 @@ __global__ void refine_candidates_kernel(const T *__restrict__ X, const double *
     const int stride = (gridDim.x * blockDim.x) >> 5;
     for (; e < nwl; e += stride) {
         const int row = wl_rows[e];
+        if (row < 0) continue;                       // unused slot of a reserved block
         int cand[WL_CAND];
         {
             const int4 c0 = *reinterpret_cast<const int4 *>(wl_cand + (size_t)e * WL_CAND);
@@ -724,6 +1107,7 @@ struct TensorCtx {
     int32_t *wl_rows = nullptr, *wl_cand = nullptr, *exact_rows = nullptr; int64_t wl_cap = 0;
     int *counters = nullptr;     // [0] worklist, [1] exact list
     unsigned *absmax = nullptr;
+    float2 *wm = nullptr; int64_t wm_cap = 0;
     // seeds (only for the cached training partition)
     float *useed = nullptr; int64_t useed_cap = 0;
     double *Cprev = nullptr; float *sig_old = nullptr; int prev_cap = 0;
@@ -741,7 +1125,7 @@ void tensor_free(akm_handle h) {
     if (!c) return;
     cudaFree(c->c16); cudaFree(c->cn); cudaFree(c->pc); cudaFree(c->wl_rows); cudaFree(c->wl_cand);
     cudaFree(c->exact_rows); cudaFree(c->counters); cudaFree(c->absmax);
-    cudaFree(c->useed); cudaFree(c->Cprev); cudaFree(c->sig_old);
+    cudaFree(c->useed); cudaFree(c->Cprev); cudaFree(c->sig_old); cudaFree(c->wm);
     delete c;
     h->tc = nullptr;
 }
@@ -840,6 +1224,25 @@ void tensor_invalidate_seeds(akm_handle h) {
 
 // chain: 0 = stand-alone pass (no seeds), 1 = akm_step sequence (remap = compaction map of the last update),
 //        2 = sequence of host-buffer passes (identity map, only while k is unchanged)
+template <int KB>
+static int launch_pair(akm_handle h, const CUtensorMap &mx, const CUtensorMap &mc, const SearchParams &sp, size_t smem, int grid) {
+    auto kern = search_pair_kernel<KB>;
+    AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(576);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = h->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AKM_CUDA(h, cudaLaunchKernelEx(&cfg, kern, mx, mc, sp));
+    h->stats.kernel_launches++;
+    return AKM_OK;
+}
+
 int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *clabel, int k0, int k, int32_t *labels,
                   double *mind, int chain, const int *remap) {
     TensorCtx *c = ctx_of(h);
@@ -862,7 +1265,15 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
 
     const int KB = (d + KBLK - 1) / KBLK;
     const int MB = 2;
-    const int ntiles = (k + TILE_N - 1) / TILE_N, kpad = ntiles * TILE_N;
+    // pair kernel (cta_group::2, centroids resident in the shared memory of a CTA pair) when they fit
+    static const bool pair_off = getenv("AKM_TC_PAIR") && atoi(getenv("AKM_TC_PAIR")) == 0;   // tuning aid
+    const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
+    const int nt2 = (k + PAIR_N - 1) / PAIR_N;
+    const size_t pair_smem = (size_t)2 * KB * BOX_BYTES + (size_t)nt2 * KB * BOX_BYTES + (size_t)nt2 * PAIR_N * 4 + 256 +
+                             (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 + 1024;
+    const bool use_pair = !pair_off && pair_smem <= budget && h->num_sms >= 2 && rs.n > 2 * TILE_M;
+    const int ntiles = use_pair ? nt2 : (k + TILE_N - 1) / TILE_N;
+    const int kpad = use_pair ? nt2 * PAIR_N : ntiles * TILE_N;
     const int d16 = rs.d16;
     if (c->kpad_cap < kpad) {
         cudaFree(c->c16); cudaFree(c->cn);
@@ -876,8 +1287,9 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     if (c->wl_cap < rs.n) {
         cudaFree(c->wl_rows); cudaFree(c->wl_cand); cudaFree(c->exact_rows);
         c->wl_rows = c->wl_cand = c->exact_rows = nullptr;
-        AKM_CUDA(h, cudaMalloc((void **)&c->wl_rows, sizeof(int32_t) * (size_t)rs.n));
-        AKM_CUDA(h, cudaMalloc((void **)&c->wl_cand, sizeof(int32_t) * (size_t)rs.n * WL_CAND));
+        const size_t slots = (size_t)rs.n + (size_t)h->num_sms * 8 * WL_BLOCK;   // + one partial block per epilogue warp
+        AKM_CUDA(h, cudaMalloc((void **)&c->wl_rows, sizeof(int32_t) * slots));
+        AKM_CUDA(h, cudaMalloc((void **)&c->wl_cand, sizeof(int32_t) * slots * WL_CAND));
         AKM_CUDA(h, cudaMalloc((void **)&c->exact_rows, sizeof(int32_t) * (size_t)rs.n));
         c->wl_cap = rs.n;
     }
@@ -916,19 +1328,19 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     const size_t A_STAGE = (size_t)MB * KB * BOX_BYTES, B_STAGE = (size_t)KB * BOX_BYTES;
     const size_t fixed = (size_t)kpad * 4 + (4 + 2 * MAX_BSLOTS + 4) * 8 + 64 + (size_t)2 * MB * TILE_M * MAX_CAND * 8 +
                          (size_t)MB * TILE_M * 16 + 1024;   // offsets, barriers, misc, candidate rings, exchange, alignment slack
-    const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
     const int a_stages = 2;
-    if (a_stages * A_STAGE + 2 * B_STAGE + fixed > budget) return exact_all();
+    if (!use_pair && a_stages * A_STAGE + 2 * B_STAGE + fixed > budget) return exact_all();
     int b_slots = (int)((budget - fixed - a_stages * A_STAGE) / B_STAGE);
     b_slots = std::min(b_slots, MAX_BSLOTS);
     const int resident = ntiles <= b_slots ? 1 : 0;
     if (resident) b_slots = ntiles;
     const size_t smem = a_stages * A_STAGE + (size_t)b_slots * B_STAGE + fixed;
 
-    const int CL = resident ? 1 : 2;          // multicast only pays when centroid tiles stream
+    const int CL = (use_pair || !resident) ? 2 : 1;          // multicast only pays when centroid tiles stream
     CUtensorMap mapX, mapC;
     AKM_TRY(encode_2d(h, c, &mapX, rs.x16, (uint64_t)d, (uint64_t)rs.n, (uint64_t)d16 * 2, KBLK, TILE_M));
-    AKM_TRY(encode_2d(h, c, &mapC, c->c16, (uint64_t)d, (uint64_t)kpad, (uint64_t)d16 * 2, KBLK, TILE_N / CL));
+    AKM_TRY(encode_2d(h, c, &mapC, c->c16, (uint64_t)d, (uint64_t)kpad, (uint64_t)d16 * 2, KBLK,
+                      use_pair ? TILE_M : TILE_N / CL));
 
     SearchParams sp{};
     sp.n = rs.n;
@@ -941,11 +1353,28 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     sp.useed = train_rows ? c->useed : nullptr;
     sp.sig_old = c->sig_old;
     sp.k_prev = k_prev;
+    if (c->wm_cap < rs.n) {
+        cudaFree(c->wm); c->wm = nullptr;
+        AKM_CUDA(h, cudaMalloc((void **)&c->wm, sizeof(float2) * (size_t)rs.n));
+        c->wm_cap = rs.n;
+    }
+    rowprep_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,
+                                                          c->sig_old, k_prev, c->wm);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    sp.wm = c->wm;
+    static const int dbg_env = getenv("AKM_TC_DBG") ? atoi(getenv("AKM_TC_DBG")) : 0;
+    sp.dbg = dbg_env;
+    sp.trace = nullptr;
     const int nsuper = (sp.groups + CL - 1) / CL;
     int grid = std::min(h->num_sms / CL, nsuper) * CL;
     if (grid < CL) grid = CL;
     int rc;
-    if (KB == 1) rc = (CL == 2) ? launch_search<2, 1, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 1, 1>(h, mapX, mapC, sp, smem, grid);
+    if (use_pair) {
+        const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
+        const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;
+        rc = (KB == 1) ? launch_pair<1>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2>(h, mapX, mapC, sp, pair_smem, pgrid);
+    } else if (KB == 1) rc = (CL == 2) ? launch_search<2, 1, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 1, 1>(h, mapX, mapC, sp, smem, grid);
     else rc = (CL == 2) ? launch_search<2, 2, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 2, 1>(h, mapX, mapC, sp, smem, grid);
     AKM_TRY(rc);
     if (train_rows) {
@@ -979,7 +1408,9 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
         AKM_CUDA(h, cudaGetLastError());
     }
     // counts for akm_get_stats (read back with the other scalars by the caller)
-    AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 4, c->counters, 3 * sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
+    // iscal[4] = rows refined, [5] = rows evaluated against all k, [6] = labels changed
+    AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 4, c->counters + 3, sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 5, c->counters + 1, 2 * sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
     h->stats.engine_used = AKM_ENGINE_TENSOR;
     return AKM_OK;
 }

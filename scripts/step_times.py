@@ -4,7 +4,9 @@ import numpy as np
 sys.path.insert(0, '.')
 from alink_b200 import native
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 20_000_000
-d, k, steps = 128, 1000, int(sys.argv[2]) if len(sys.argv) > 2 else 8
+d = 128
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+k = int(sys.argv[3]) if len(sys.argv) > 3 else 1000
 h = native.Handle(d, native.EUCLIDEAN)
 h.reserve_rows(N)
 h.blobs_append(20260101, k, 0, N)
