@@ -258,16 +258,26 @@ static void absorb_tensor_stats(akm_handle h) {
     }
 }
 
-// Keep the cached partition grouped by cluster (reorder.cu).  Policy: after the first tensor-engine pass, and
-// again whenever more than a quarter of the rows changed cluster since the last regrouping.
+// Keep the cached partition grouped by cluster (reorder.cu).  Policy: regroup after the first tensor-engine
+// pass, once more two passes later (the first labels come from the initial centroids and move a lot), and
+// afterwards only when a single pass moved more than a quarter of the rows.
 static int maybe_reorder(akm_handle h, int k) {
-    static const int env = getenv("AKM_REORDER") ? atoi(getenv("AKM_REORDER")) : -1;   // 0 = never, 1 = policy
+    static const int env = getenv("AKM_REORDER") ? atoi(getenv("AKM_REORDER")) : -1;   // 0 = never
     if (env == 0) return AKM_OK;
     if (h->stats.engine_used != AKM_ENGINE_TENSOR || h->rows.n < h->reorder_min_rows) return AKM_OK;
-    h->changed_since_reorder += h->h_iscal[6];
-    const bool first = !h->rows.reordered;
-    if (!first && h->changed_since_reorder * 4 < h->rows.n) return AKM_OK;
+    h->changed_since_reorder++;                       // tensor passes since the last regrouping (or since upload)
+    bool go = !h->rows.reordered && h->changed_since_reorder >= 2;   // labels of the very first pass still move a lot
+    if (!go && h->rows.reordered && (int64_t)h->h_iscal[6] * 4 > h->rows.n) go = true;
+    if (!go) return AKM_OK;
+    if (h->profiling) cudaEventRecord(h->pev[3], h->stream);
     AKM_TRY(reorder_rows_by_label(h, h->rows, h->labels, tensor_useed(h), k));
+    if (h->profiling) {
+        cudaEventRecord(h->pev[4], h->stream);
+        cudaEventSynchronize(h->pev[4]);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->pev[3], h->pev[4]);
+        h->reorder_ms += ms;
+    }
     h->changed_since_reorder = 0;
     h->reorders++;
     return AKM_OK;
@@ -713,11 +723,13 @@ extern "C" int akm_set_profiling(akm_handle h, int on) {
     return AKM_OK;
 }
 
-extern "C" int akm_get_profile(akm_handle h, double *out5, int reset) {
+extern "C" int akm_get_profile(akm_handle h, double *out5, int reset) {  // out5 has room for 7 values
     if (!h || !out5) return akm_fail(h, AKM_ERR_BADARG, "null argument");
     for (int i = 0; i < 4; ++i) out5[i] = h->prof_ms[i];
     out5[4] = (double)h->prof_steps;
-    if (reset) { for (int i = 0; i < 4; ++i) h->prof_ms[i] = 0; h->prof_steps = 0; }
+    out5[5] = h->reorder_ms;
+    out5[6] = (double)h->reorders;
+    if (reset) { for (int i = 0; i < 4; ++i) h->prof_ms[i] = 0; h->prof_steps = 0; h->reorder_ms = 0; }
     return AKM_OK;
 }
 

@@ -75,6 +75,7 @@ struct akm_handle_s {
     int32_t *reorder_dest = nullptr; int64_t reorder_dest_cap = 0;
     int64_t changed_since_reorder = 0;
     int reorders = 0;
+    double reorder_ms = 0;
     int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
 
     // optional per-phase profiling of akm_step

@@ -511,9 +511,9 @@ search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__
 //   m0 = rigorous upper bound of this pass's minimum approximate score (INF when there is no seed):
 //        the previous winner a had true score <= useed; its centroid moved by sig_old[a].
 __global__ void rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restrict__ pc,
-                               const float2 *__restrict__ xerr, const int32_t *__restrict__ labels,
+                               const float2 *__restrict__ xerr, int32_t *__restrict__ labels,
                                const float *__restrict__ useed, const float *__restrict__ sig_old, int k_prev,
-                               float2 *__restrict__ wm) {
+                               const int *__restrict__ remap, float2 *__restrict__ wm) {
     const float c16_max = pc->c16_max, dc_max = pc->dc_max, c_max = pc->c_max;
     const bool bad = pc->bad != 0;
     int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -541,6 +541,9 @@ __global__ void rowprep_kernel(int64_t n, int d, int metric, float eta, const Pa
                     u = u0 + sg_a * (r + er) * 1.000001f + 0.5f * W + 1e-6f;
                 }
                 if (u == u) m0 = u;                                 // NaN: no seed
+                // express the old label in this pass's cluster numbering (empty clusters were compacted away),
+                // so the search kernel can tell which rows really changed cluster
+                if (remap) labels[row] = remap[a];
             }
         }
         wm[row] = make_float2(W, m0);
@@ -587,6 +590,14 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) 
     uint32_t remote;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(bar), "r"(cta));
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+// two fp32 FMAs in one instruction (FFMA2): {d0,d1} = {a0,a1} * {s,s} + {c0,c1}
+__device__ __forceinline__ void ffma2(float &d0, float &d1, uint32_t a0, uint32_t a1, uint64_t s2, float c0, float c1) {
+    uint64_t a, c, d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "r"(a0), "r"(a1));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(c0), "f"(c1));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(s2), "l"(c));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
 }
 constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;   // clears the CTA-pair bit: address of the leader CTA's copy
 constexpr uint32_t IDESC_F16_256x256 = (1u << 4) | ((256u >> 3) << 17) | ((256u >> 4) << 24);
@@ -696,6 +707,9 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         const int quarter = e >> 2;
         const int q = warp & 3;
         const float scale = pc_s[3];
+        uint64_t scale2;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(scale2) : "f"(scale));
+        const float *cn_q = cn_s + quarter * 64;
         const int rt = q * 32 + lane;
         float2 *my_ring = cand_s + ((size_t)quarter * TILE_M + rt) * MAX_CAND;
         float *my_xch = xch_s + ((size_t)quarter * TILE_M + rt) * 4;
@@ -717,9 +731,9 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 const int64_t rown = (int64_t)(g + npairs) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
                 if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[rown] : -1; }
             }
-            const float W = wm.x;
+            const float W = valid ? wm.x : NAN;          // padding rows: NaN thresholds never admit a candidate
             float m = wm.y;
-            float thr = valid ? m + W : -INFINITY;
+            float thr = m + W;
             int ncand = 0;
             float dropped = INFINITY;
 
@@ -728,7 +742,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * PAIR_N + quarter * 64);
-#pragma unroll 1
+#pragma unroll
                 for (int c = 0; c < 2; ++c) {
                     uint32_t v[32];
                     __syncwarp();
@@ -739,16 +753,13 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                         __syncwarp();
                         if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);   // the leader's MMA thread waits on it
                     }
-                    const int j0 = t * PAIR_N + quarter * 64 + c * 32;
-                    const float *cn_t = cn_s + j0;
+                    const float *cn_t = cn_q + t * PAIR_N + c * 32;
                     float sc[32];
 #pragma unroll
                     for (int gq = 0; gq < 8; ++gq) {
                         const float4 o = *reinterpret_cast<const float4 *>(cn_t + gq * 4);
-                        sc[gq * 4 + 0] = fmaf(__uint_as_float(v[gq * 4 + 0]), scale, o.x);
-                        sc[gq * 4 + 1] = fmaf(__uint_as_float(v[gq * 4 + 1]), scale, o.y);
-                        sc[gq * 4 + 2] = fmaf(__uint_as_float(v[gq * 4 + 2]), scale, o.z);
-                        sc[gq * 4 + 3] = fmaf(__uint_as_float(v[gq * 4 + 3]), scale, o.w);
+                        ffma2(sc[gq * 4 + 0], sc[gq * 4 + 1], v[gq * 4 + 0], v[gq * 4 + 1], scale2, o.x, o.y);
+                        ffma2(sc[gq * 4 + 2], sc[gq * 4 + 3], v[gq * 4 + 2], v[gq * 4 + 3], scale2, o.z, o.w);
                     }
                     float g8[4];
 #pragma unroll
@@ -759,8 +770,9 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     }
                     const float cmin = fminf(fminf(g8[0], g8[1]), fminf(g8[2], g8[3]));
                     m = fminf(m, cmin);
-                    thr = valid ? m + W : -INFINITY;
+                    thr = m + W;                                   // padding rows: W = -INF (set above)
                     if (cmin <= thr) {
+                        const int j0 = t * PAIR_N + quarter * 64 + c * 32;
 #pragma unroll
                         for (int gq = 0; gq < 4; ++gq) {
                             if (g8[gq] <= thr) {
@@ -1003,49 +1015,60 @@ c16_build_kernel(const double *__restrict__ C, const double *__restrict__ clabel
 // One warp per worklist entry.  fp64 FMA evaluation of the candidate scores; if the best is separated from the
 // runner-up by more than the combined rounding bound of this evaluation and of Java's, it is Java's argmin.
 // Otherwise (or when the entry asks for all centroids) the row goes to the exact list.
+// One THREAD per worklist entry: the work per entry is tiny (a few 128-long fp64 dot products), so the
+// kernel is all about memory behaviour.  A thread streams its own sample row and its candidates' centroid
+// rows 16-32 bytes at a time; neighbouring entries come from neighbouring rows of a cluster-ordered
+// partition, so they share candidates and the centroid rows are L1 hits for the rest of the warp.
 template <typename T, int METRIC>
-__global__ void refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int d,
-                                         const double *__restrict__ C, const double *__restrict__ clabel, int k,
-                                         const int32_t *__restrict__ wl_rows, const int32_t *__restrict__ wl_cand,
-                                         const int *__restrict__ counters, int32_t *__restrict__ labels,
-                                         int32_t *__restrict__ exact_rows, int *__restrict__ exact_count) {
-    const int lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(128)
+refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int d,
+                         const double *__restrict__ C, const double *__restrict__ clabel, int k,
+                         const int32_t *__restrict__ wl_rows, const int32_t *__restrict__ wl_cand,
+                         const int *__restrict__ counters, int32_t *__restrict__ labels,
+                         int32_t *__restrict__ exact_rows, int *__restrict__ exact_count) {
     const int nwl = counters[0];
-    int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int stride = (gridDim.x * blockDim.x) >> 5;
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    const int stride = gridDim.x * blockDim.x;
     for (; e < nwl; e += stride) {
         const int row = wl_rows[e];
-        if (row < 0) continue;                       // unused slot of a reserved block
-        int cand[WL_CAND];
-        {
-            const int4 c0 = *reinterpret_cast<const int4 *>(wl_cand + (size_t)e * WL_CAND);
-            const int4 c1 = *reinterpret_cast<const int4 *>(wl_cand + (size_t)e * WL_CAND + 4);
-            cand[0] = c0.x; cand[1] = c0.y; cand[2] = c0.z; cand[3] = c0.w;
-            cand[4] = c1.x; cand[5] = c1.y; cand[6] = c1.z; cand[7] = c1.w;
-        }
+        if (row < 0) continue;                           // unused slot of a reserved block
+        const int4 c0 = *reinterpret_cast<const int4 *>(wl_cand + (size_t)e * WL_CAND);
+        const int4 c1 = *reinterpret_cast<const int4 *>(wl_cand + (size_t)e * WL_CAND + 4);
+        const int cand[WL_CAND] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
         bool to_exact = cand[0] == -2;
         int winner = -1;
         if (!to_exact) {
-            const bool wide = cand[4] >= 0 || cand[5] >= 0 || cand[6] >= 0 || cand[7] >= 0;   // warp-uniform
+            int nc = 0;
+#pragma unroll
+            for (int i = 0; i < WL_CAND; ++i) nc += (cand[i] >= 0) ? 1 : 0;
+            const T *x = X + (int64_t)row * d;
             double acc[WL_CAND];
 #pragma unroll
             for (int i = 0; i < WL_CAND; ++i) acc[i] = 0.0;
-#pragma unroll 4
-            for (int c = lane; c < d; c += 32) {
-                const double xv = (double)X[(int64_t)row * d + c];
+            const bool wide = nc > 3;
+            for (int c = 0; c < d; c += 4) {
+                double xv[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (cand[i] >= 0) acc[i] = fma(xv, C[(size_t)cand[i] * d + c], acc[i]);
+                for (int u = 0; u < 4; ++u) xv[u] = (c + u < d) ? (double)x[c + u] : 0.0;
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    if (cand[i] >= 0) {
+                        const double *cr = C + (size_t)cand[i] * d + c;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) if (c + u < d) acc[i] = fma(xv[u], cr[u], acc[i]);
+                    }
+                }
                 if (wide) {
 #pragma unroll
-                    for (int i = 4; i < WL_CAND; ++i)
-                        if (cand[i] >= 0) acc[i] = fma(xv, C[(size_t)cand[i] * d + c], acc[i]);
+                    for (int i = 3; i < WL_CAND; ++i) {
+                        if (cand[i] >= 0) {
+                            const double *cr = C + (size_t)cand[i] * d + c;
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) if (c + u < d) acc[i] = fma(xv[u], cr[u], acc[i]);
+                        }
+                    }
                 }
             }
-#pragma unroll
-            for (int i = 0; i < WL_CAND; ++i)
-                if (i < 4 || wide)
-                    for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
             const double xl = (METRIC == AKM_EUCLIDEAN) ? xlabel[row] : 1.0;
             double v1 = DBL_MAX, v2 = DBL_MAX, clmax = 0.0;
             int i1 = -1;
@@ -1063,10 +1086,8 @@ __global__ void refine_candidates_kernel(const T *__restrict__ X, const double *
             if (i1 >= 0 && (v2 - v1) > tau) winner = i1;   // false for NaN
             else to_exact = true;
         }
-        if (lane == 0) {
-            if (to_exact) exact_rows[atomicAdd(exact_count, 1)] = row;
-            else labels[row] = winner;
-        }
+        if (to_exact) exact_rows[atomicAdd(exact_count, 1)] = row;
+        else labels[row] = winner;
     }
 }
 
@@ -1359,7 +1380,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
         c->wm_cap = rs.n;
     }
     rowprep_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,
-                                                          c->sig_old, k_prev, c->wm);
+                                                          c->sig_old, k_prev, (chain == 1) ? remap : nullptr, c->wm);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     sp.wm = c->wm;
@@ -1386,9 +1407,9 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     if (h->profiling && h->mid_event) { cudaEventRecord(h->mid_event, h->stream); h->mid_recorded = true; }
 
     // refinement: candidates first, then the exact list (lengths stay on the device)
-    const int rblocks = h->num_sms * 8;
+    const int rblocks = h->num_sms * 32;
 #define REFINE(T, PTR, M)                                                                                         \
-    refine_candidates_kernel<T, M><<<rblocks, 256, 0, h->stream>>>(PTR, rs.xlabel, d, C, clabel, k, c->wl_rows, \
+    refine_candidates_kernel<T, M><<<rblocks, 128, 0, h->stream>>>(PTR, rs.xlabel, d, C, clabel, k, c->wl_rows, \
                                                                    c->wl_cand, c->counters, labels, c->exact_rows, c->counters + 1)
     if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) REFINE(float, rs.x32, AKM_EUCLIDEAN); else REFINE(double, rs.x64, AKM_EUCLIDEAN); }
     else REFINE(double, rs.x64, AKM_COSINE);

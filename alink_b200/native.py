@@ -290,9 +290,10 @@ class Handle:
         self._ck(lib().akm_set_profiling(self._h, 1 if on else 0))
 
     def get_profile(self, reset=False):
-        out = np.zeros(5, dtype=np.float64)
+        out = np.zeros(8, dtype=np.float64)
         self._ck(lib().akm_get_profile(self._h, _dp(out), 1 if reset else 0))
-        return dict(search_ms=out[0], refine_ms=out[1], accumulate_ms=out[2], update_ms=out[3], steps=int(out[4]))
+        return dict(search_ms=out[0], refine_ms=out[1], accumulate_ms=out[2], update_ms=out[3], steps=int(out[4]),
+                    reorder_ms=out[5], reorders=int(out[6]))
 
     # ---- synthetic benchmark data
     def blobs_append(self, seed, k_true, row0, n, spread=10.0, sigma=1.0):

@@ -218,11 +218,12 @@ int akm_time_kernel(akm_handle h, const char *name, int reps, double *ms_out);
 int akm_set_option(akm_handle h, const char *name, double value);
 
 /* Per-phase device timing of akm_step with CUDA events on the handle's stream (off by default).
- * akm_get_profile fills out[0..4] = cumulative milliseconds of {nearest-centroid search, exact
- * refinement, per-cluster accumulation, all-reduce + centroid update} and the number of steps
- * counted; reset != 0 clears the counters.  No reference counterpart. */
+ * akm_get_profile fills out[0..6] = cumulative milliseconds of {nearest-centroid search, exact
+ * refinement, per-cluster accumulation, all-reduce + centroid update}, the number of steps counted,
+ * the milliseconds spent regrouping rows by cluster and the number of regroupings so far;
+ * reset != 0 clears the counters.  No reference counterpart. */
 int akm_set_profiling(akm_handle h, int on);
-int akm_get_profile(akm_handle h, double *out5, int reset);
+int akm_get_profile(akm_handle h, double *out7, int reset);
 
 /* Synthetic Gaussian-blob rows of SURVEY 8(d), generated on the device by a counter-based hash RNG
  * (a pure function of seed and the global row index, so any shard can be produced independently):
