@@ -1046,25 +1046,44 @@ refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xla
 #pragma unroll
             for (int i = 0; i < WL_CAND; ++i) acc[i] = 0.0;
             const bool wide = nc > 3;
-            for (int c = 0; c < d; c += 4) {
-                double xv[4];
+            // one full 32-byte sector of the sample row per step (each sector is fetched exactly once even when
+            // the L1 cannot hold the lines of all resident warps)
+            constexpr int STEP = 32 / (int)sizeof(T);
+            const bool vec = (d % STEP) == 0;            // rows and centroid rows are then 32-byte aligned
+            for (int c = 0; c < d; c += STEP) {
+                double xv[STEP];
+                if (vec) {
+                    // 128-bit loads: a warp-wide scalar load of 32 different rows costs one L1 tag cycle per
+                    // row, so the number of load instructions (not bytes) is what bounds this kernel
+                    const int4 *xp = reinterpret_cast<const int4 *>(x + c);
+                    const int4 r0 = xp[0], r1 = xp[1];
+                    if (sizeof(T) == 4) {
+                        xv[0] = __int_as_float(r0.x); xv[1] = __int_as_float(r0.y); xv[2] = __int_as_float(r0.z); xv[3] = __int_as_float(r0.w);
+                        xv[4 % STEP] = __int_as_float(r1.x); xv[5 % STEP] = __int_as_float(r1.y);
+                        xv[6 % STEP] = __int_as_float(r1.z); xv[7 % STEP] = __int_as_float(r1.w);
+                    } else {
+                        xv[0] = __hiloint2double(r0.y, r0.x); xv[1] = __hiloint2double(r0.w, r0.z);
+                        xv[2 % STEP] = __hiloint2double(r1.y, r1.x); xv[3 % STEP] = __hiloint2double(r1.w, r1.z);
+                    }
+                } else {
 #pragma unroll
-                for (int u = 0; u < 4; ++u) xv[u] = (c + u < d) ? (double)x[c + u] : 0.0;
+                    for (int u = 0; u < STEP; ++u) xv[u] = (c + u < d) ? (double)x[c + u] : 0.0;
+                }
 #pragma unroll
-                for (int i = 0; i < 3; ++i) {
+                for (int i = 0; i < WL_CAND; ++i) {
+                    if (i >= 3 && !wide) break;
                     if (cand[i] >= 0) {
                         const double *cr = C + (size_t)cand[i] * d + c;
+                        if (vec) {
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) if (c + u < d) acc[i] = fma(xv[u], cr[u], acc[i]);
-                    }
-                }
-                if (wide) {
+                            for (int u = 0; u < STEP; u += 2) {
+                                const double2 cv = *reinterpret_cast<const double2 *>(cr + u);
+                                acc[i] = fma(xv[u], cv.x, acc[i]);
+                                acc[i] = fma(xv[u + 1], cv.y, acc[i]);
+                            }
+                        } else {
 #pragma unroll
-                    for (int i = 3; i < WL_CAND; ++i) {
-                        if (cand[i] >= 0) {
-                            const double *cr = C + (size_t)cand[i] * d + c;
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) if (c + u < d) acc[i] = fma(xv[u], cr[u], acc[i]);
+                            for (int u = 0; u < STEP; ++u) if (c + u < d) acc[i] = fma(xv[u], cr[u], acc[i]);
                         }
                     }
                 }
