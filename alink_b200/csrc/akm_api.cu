@@ -443,7 +443,7 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
     AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centroids, sizeof(double) * (size_t)k0 * d, cudaMemcpyHostToDevice, h->stream));
     AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, /*cos_normalise=*/false));
     AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], k0, k, h->labels, nullptr, /*chain=*/2, nullptr));
-    AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], k0, s->sum, s->sum + L));
+    AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], s->l[0], k0, s->sum, s->sum + L));
     AKM_CUDA(h, cudaMemcpyAsync(sum_out, s->sum, sizeof(double) * L, cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 5 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -517,7 +517,7 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     AKM_TRY(run_assign(h, h->rows, h->cent[rd], h->clabel[rd], k0, h->k, h->labels, nullptr, /*chain=*/1,
                        s > 1 ? h->cmap : nullptr));
     if (prof) cudaEventRecord(h->pev[1], h->stream);
-    AKM_TRY(launch_accumulate(h, h->rows, h->labels, h->cent[rd], k0, h->sum, h->sum + L));
+    AKM_TRY(launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->clabel[rd], k0, h->sum, h->sum + L));
     if (prof) cudaEventRecord(h->pev[2], h->stream);
     if (h->comm) AKM_TRY(nccl_allreduce_device(h, h->sum, (int64_t)L + 1));
     AKM_TRY(launch_update(h, h->sum, h->k, k0, h->cent[wr], h->clabel[wr], h->cent[rd], h->clabel[rd],
@@ -695,12 +695,12 @@ extern "C" int akm_time_kernel(akm_handle h, const char *name, int reps, double 
     int rc = AKM_OK;
     // one untimed launch, then `reps` timed ones (labels must exist before timing accumulate)
     rc = run_assign(h, h->rows, h->cent[rd], h->clabel[rd], h->k0, h->k, h->labels, nullptr);
-    if (rc == AKM_OK && is_acc) rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->k0, s->sum, s->sum + L);
+    if (rc == AKM_OK && is_acc) rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->clabel[rd], h->k0, s->sum, s->sum + L);
     if (rc == AKM_OK) {
         cudaEventRecord(e0, h->stream);
         for (int i = 0; i < reps && rc == AKM_OK; ++i) {
             if (is_assign) rc = run_assign(h, h->rows, h->cent[rd], h->clabel[rd], h->k0, h->k, h->labels, nullptr);
-            else rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->k0, s->sum, s->sum + L);
+            else rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->clabel[rd], h->k0, s->sum, s->sum + L);
         }
         cudaEventRecord(e1, h->stream);
         if (cudaEventSynchronize(e1) != cudaSuccess) rc = akm_fail(h, AKM_ERR_CUDA, "event sync failed");

@@ -123,7 +123,7 @@ int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist
 int launch_assign_exact_list(akm_handle h, const RowStore &rs, const int32_t *rowlist, const int *count_dev,
                              const double *C, const double *clabel, int k0, int k, int32_t *labels);
 // per-cluster sums/counts (+ objective) from labels
-int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C,
+int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C, const double *clabel,
                       int k0, double *sum, double *objective);
 // KMeansUpdateCentroids + KMeansIterTermination diag
 int launch_update(akm_handle h, const double *sum, int k, int k0, double *Cnew, double *clnew,

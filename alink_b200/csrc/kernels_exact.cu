@@ -368,10 +368,11 @@ template <> struct Vec16<double> { using type = double2; static constexpr int N 
 // VEC == true: each lane owns 16-byte column groups (lane + 32*m) -> one 128-bit load per row and group
 // (requires d % (16/sizeof(T)) == 0); VEC == false: scalar columns lane + 32*m (any d).
 template <typename T, int DC, int METRIC, bool VEC>
-__global__ void __launch_bounds__(ACC_THREADS, 2)
+__global__ void __launch_bounds__(ACC_THREADS, 3)
 accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, int64_t n, int d, int k0,
                   int chunk_rows, const double *__restrict__ C, double *__restrict__ sum,
-                  double *__restrict__ objective) {
+                  double *__restrict__ objective, const double *__restrict__ xlabel,
+                  const double *__restrict__ clabel) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     int *off = reinterpret_cast<int *>(smem_raw);           // k0 + 1
     int *cursor = off + (k0 + 1);                           // k0
@@ -429,13 +430,12 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
     for (int j = warp; j < k0; j += ACC_THREADS / 32) {
         const int s = off[j], e = off[j + 1];
         if (s == e) continue;
-        double acc[DC][VN], cen[DC][VN], sq[DC][VN];
+        double acc[DC][VN], cen[DC][VN];
 #pragma unroll
         for (int m = 0; m < DC; ++m)
 #pragma unroll
             for (int v = 0; v < VN; ++v) {
                 acc[m][v] = 0.0;
-                sq[m][v] = 0.0;
                 const int col = cb0 + (lane + 32 * m) * VN + v;
                 cen[m][v] = (col < d) ? C[(size_t)j * d + col] : 0.0;
             }
@@ -462,13 +462,7 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
                     if constexpr (VEC) Vec16<T>::unpack(raw[u][m], val);
                     else val[0] = (double)raw[u][m];
 #pragma unroll
-                    for (int v = 0; v < VN; ++v) {
-                        acc[m][v] += val[v];
-                        if (METRIC == AKM_EUCLIDEAN) {
-                            const double df = val[v] - cen[m][v];
-                            sq[m][v] = fma(df, df, sq[m][v]);
-                        }
-                    }
+                    for (int v = 0; v < VN; ++v) acc[m][v] += val[v];
                 }
         }
         for (; p < e; ++p) {
@@ -480,11 +474,16 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
                     const int c0 = (lane + 32 * m) * VN + v;
                     const double x = (cb0 + c0 < d) ? (double)row[c0] : 0.0;
                     acc[m][v] += x;
-                    if (METRIC == AKM_EUCLIDEAN) {
-                        const double df = x - cen[m][v];
-                        sq[m][v] = fma(df, df, sq[m][v]);
-                    }
                 }
+        }
+        // objective of the segment, the way Java's distance is put together:
+        //   EUCL  sum ||x||^2 - 2 c.S + n ||c||^2  (||x||^2 = the stored label, S = the sums just formed)
+        //   COS   n - c.S
+        if (METRIC == AKM_EUCLIDEAN && blockIdx.y == 0) {
+            double xs = 0.0;
+            for (int q = s + lane; q < e; q += 32) xs += xlabel[base + sorted[q]];
+            obj += xs;
+            if (lane == 0) obj += (double)(e - s) * clabel[j];
         }
         double *out = sum + (size_t)j * (d + 1);
 #pragma unroll
@@ -494,7 +493,7 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
                 const int col = cb0 + (lane + 32 * m) * VN + v;
                 if (col < d) {
                     atomicAdd(out + col, acc[m][v]);
-                    if (METRIC == AKM_EUCLIDEAN) obj += sq[m][v];
+                    if (METRIC == AKM_EUCLIDEAN) obj -= 2.0 * cen[m][v] * acc[m][v];
                     else obj -= cen[m][v] * acc[m][v];
                 }
             }
@@ -545,7 +544,7 @@ __global__ void accumulate_atomic_kernel(const T *__restrict__ X, const int32_t 
 
 template <typename T, int METRIC>
 static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_t *labels, const double *C, int k0,
-                               double *sum, double *objective) {
+                               double *sum, double *objective, const double *xlabel, const double *clabel) {
     const int d = h->d;
     const size_t fixed = (size_t)(2 * k0 + 2) * sizeof(int);
     const size_t budget = h->smem_optin > 8192 ? h->smem_optin - 8192 : 0;
@@ -562,7 +561,7 @@ static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_
     int64_t chunk = ceil_div64(n, (int64_t)h->num_sms * 6);
     chunk = ((chunk + 1023) / 1024) * 1024;
     const int64_t cap3 = (int64_t)(((size_t)(h->smem_optin + 1024) / 3 - 4096 - fixed) / 2);
-    int64_t chunk_max = std::min<int64_t>(32768, std::max<int64_t>(2048, (cap3 / 1024) * 1024));
+    int64_t chunk_max = std::min<int64_t>(16384, std::max<int64_t>(2048, (cap3 / 1024) * 1024));
     if (env_chunk > 0) chunk_max = env_chunk;
     if (chunk > chunk_max) chunk = chunk_max;
     if (chunk > ACC_MAX_CHUNK) chunk = ACC_MAX_CHUNK;
@@ -581,7 +580,7 @@ static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_
     {                                                                                                          \
         auto kern = accumulate_kernel<T, DCV, METRIC, VECV>;                                                   \
         AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
-        kern<<<grid, ACC_THREADS, smem, h->stream>>>(X, labels, n, d, k0, (int)chunk, C, sum, objective);      \
+        kern<<<grid, ACC_THREADS, smem, h->stream>>>(X, labels, n, d, k0, (int)chunk, C, sum, objective, xlabel, clabel); \
     }
     if (vec) {
         switch (DCsel) {
@@ -608,16 +607,16 @@ static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_
     return AKM_OK;
 }
 
-int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C, int k0, double *sum,
-                      double *objective) {
+int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C, const double *clabel,
+                      int k0, double *sum, double *objective) {
     AKM_CUDA(h, cudaMemsetAsync(sum, 0, sizeof(double) * (size_t)k0 * (h->d + 1), h->stream));   // Arrays.fill :59
     if (objective) AKM_CUDA(h, cudaMemsetAsync(objective, 0, sizeof(double), h->stream));
     if (rs.n <= 0) return AKM_OK;
     if (h->metric == AKM_EUCLIDEAN) {
-        if (rs.store == 4) return accumulate_dispatch<float, AKM_EUCLIDEAN>(h, rs.x32, rs.n, labels, C, k0, sum, objective);
-        return accumulate_dispatch<double, AKM_EUCLIDEAN>(h, rs.x64, rs.n, labels, C, k0, sum, objective);
+        if (rs.store == 4) return accumulate_dispatch<float, AKM_EUCLIDEAN>(h, rs.x32, rs.n, labels, C, k0, sum, objective, rs.xlabel, clabel);
+        return accumulate_dispatch<double, AKM_EUCLIDEAN>(h, rs.x64, rs.n, labels, C, k0, sum, objective, rs.xlabel, clabel);
     }
-    return accumulate_dispatch<double, AKM_COSINE>(h, rs.x64, rs.n, labels, C, k0, sum, objective);
+    return accumulate_dispatch<double, AKM_COSINE>(h, rs.x64, rs.n, labels, C, k0, sum, objective, rs.xlabel, clabel);
 }
 
 // =====================================================================================
