@@ -179,8 +179,11 @@ static int ensure_centroids(akm_handle h, int k0) {
 
 static int ensure_kvec(akm_handle h, int k0) {
     if (h->kvec_cap >= k0) return AKM_OK;
-    dev_free(h->cmap); dev_free(h->shift);
+    dev_free(h->cmap); dev_free(h->shift); dev_free(h->inv);
+    h->inv_cap = 0;
     AKM_TRY(dev_alloc(h, &h->cmap, (size_t)k0));
+    AKM_TRY(dev_alloc(h, &h->inv, (size_t)k0));
+    h->inv_cap = k0;
     AKM_TRY(dev_alloc(h, &h->shift, (size_t)k0));
     h->kvec_cap = k0;
     return AKM_OK;
@@ -353,7 +356,7 @@ int akm_destroy(akm_handle h) {
     rowstore_free(h->batch);
     dev_free(h->labels); dev_free(h->mind);
     for (int i = 0; i < 2; ++i) { dev_free(h->cent[i]); dev_free(h->clabel[i]); }
-    dev_free(h->sum); dev_free(h->cmap); dev_free(h->shift); dev_free(h->dscal); dev_free(h->iscal);
+    dev_free(h->sum); dev_free(h->cmap); dev_free(h->inv); dev_free(h->shift); dev_free(h->dscal); dev_free(h->iscal);
     if (h->h_dscal) cudaFreeHost(h->h_dscal);
     if (h->h_iscal) cudaFreeHost(h->h_iscal);
     if (h->stage) cudaFree(h->stage);

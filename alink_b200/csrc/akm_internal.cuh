@@ -52,7 +52,8 @@ struct akm_handle_s {
     double *clabel[2] = {nullptr, nullptr};
     int cent_cap = 0;
     double *sum = nullptr;    // k0*(d+1) + 2 : [L] = sum of xlabel / row count of this rank
-    int *cmap = nullptr;      // k0 compaction map
+    int *cmap = nullptr;      // k0 compaction map (old index -> new index)
+    int *inv = nullptr; int inv_cap = 0;   // new index -> old index
     double *shift = nullptr;  // k0
     int kvec_cap = 0;
     Scratch *sc = nullptr;    // buffers of the host-buffer entry points

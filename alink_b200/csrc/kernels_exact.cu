@@ -700,10 +700,111 @@ update_kernel(int metric, const double *__restrict__ sum, int k, int k0, int d, 
     }
 }
 
+// ---- multi-CTA version: a one-block scan builds the compaction maps, then one warp per centroid row does
+// the scaling, updateLabel and the shift distance.  Java's index-order sums are kept: the row is staged in
+// shared memory and every lane walks it in order (a 128-long dependent chain per row instead of a 128-long
+// chain of uncoalesced global loads per thread, which is what made the single-CTA kernel take 0.3 ms).
+__global__ void __launch_bounds__(UPD_THREADS)
+update_map_kernel(const double *__restrict__ sum, int k, int k0, int d, int *__restrict__ cmap, int *__restrict__ inv,
+                  int *__restrict__ iscal) {
+    __shared__ int scan_tmp[UPD_THREADS];
+    const int tid = threadIdx.x;
+    const int per = (k + UPD_THREADS - 1) / UPD_THREADS;
+    const int lo = min(k, tid * per), hi = min(k, lo + per);
+    int cnt = 0;
+    for (int j = lo; j < hi; ++j) cnt += (sum[(size_t)j * (d + 1) + d] != 0.0) ? 1 : 0;
+    scan_tmp[tid] = cnt;
+    for (int m = tid; m < k0; m += UPD_THREADS) inv[m] = -1;
+    __syncthreads();
+    for (int o = 1; o < UPD_THREADS; o <<= 1) {
+        const int v = (tid >= o) ? scan_tmp[tid - o] : 0;
+        __syncthreads();
+        scan_tmp[tid] += v;
+        __syncthreads();
+    }
+    int run = (tid > 0) ? scan_tmp[tid - 1] : 0;
+    for (int j = lo; j < hi; ++j) {
+        const bool ne = sum[(size_t)j * (d + 1) + d] != 0.0;
+        cmap[j] = ne ? run : -1;
+        if (ne) inv[run] = j;
+        run += ne ? 1 : 0;
+    }
+    if (tid == UPD_THREADS - 1) { iscal[0] = scan_tmp[UPD_THREADS - 1]; iscal[1] = 1; }   // new k; "converged" until a row objects
+}
+
+__global__ void __launch_bounds__(256)
+update_rows_kernel(int metric, const double *__restrict__ sum, int k0, int d, double *__restrict__ Cnew,
+                   double *__restrict__ clnew, const double *__restrict__ Cprev, const double *__restrict__ clprev,
+                   int new_is_c1, double tol, double *__restrict__ shift, const int *__restrict__ inv,
+                   int *__restrict__ iscal) {
+    extern __shared__ double upd_smem[];                 // [8 warps][2][d]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int m = blockIdx.x * 8 + warp;                 // destination row
+    if (m >= k0) return;
+    double *rowbuf = upd_smem + (size_t)warp * 2 * d;
+    double *prevbuf = rowbuf + d;
+    const int newk = iscal[0];
+    const int src = inv[m];
+    // Arrays.fill(data, 0) then daxpy(d, 1.0/weight, buffer, start, data, index*d): y = 0 + (1/w)*x
+    double a = 0.0;
+    if (src >= 0) a = 1.0 / sum[(size_t)src * (d + 1) + d];
+    for (int c = lane; c < d; c += 32) {
+        double v = 0.0;
+        if (src >= 0) v = DADD(0.0, DMUL(a, sum[(size_t)src * (d + 1) + c]));
+        rowbuf[c] = v;
+        if (Cprev != nullptr) prevbuf[c] = Cprev[(size_t)m * d + c];
+    }
+    __syncwarp();
+    // distance.updateLabel (all k0 rows): sum of squares in index order
+    double s = 0.0;
+    for (int i = 0; i < d; ++i) { const double v = rowbuf[i]; s = DADD(s, DMUL(v, v)); }
+    double label = s;
+    if (metric == AKM_COSINE) {
+        label = 0.0;
+        const double nrm = sqrt(s);
+        if (nrm > 0.0) {
+            const double invn = 1.0 / nrm;
+            __syncwarp();
+            for (int c = lane; c < d; c += 32) rowbuf[c] = DMUL(invn, rowbuf[c]);
+            __syncwarp();
+        }
+    }
+    for (int c = lane; c < d; c += 32) Cnew[(size_t)m * d + c] = rowbuf[c];
+    if (lane == 0) clnew[m] = label;
+    // KMeansIterTermination: left = CENTROID1, right = CENTROID2
+    if (Cprev != nullptr && m < newk) {
+        const double *c1 = new_is_c1 ? rowbuf : prevbuf, *c2 = new_is_c1 ? prevbuf : rowbuf;
+        const double l1 = new_is_c1 ? label : clprev[m], l2 = new_is_c1 ? clprev[m] : label;
+        double t = 0.0;
+        for (int l = 0; l < d; ++l) t = DADD(t, DMUL(c2[l], c1[l]));
+        double v;
+        if (metric == AKM_EUCLIDEAN) {
+            v = DMUL(-2.0, t);
+            v = sqrt(fabs(DADD(DADD(v, l2), l1)));
+        } else {
+            v = DADD(DMUL(-1.0, t), DMUL(1.0, 1.0));
+        }
+        if (lane == 0) {
+            if (shift) shift[m] = v;
+            if (v >= tol) iscal[1] = 0;                  // not converged (benign race: everybody writes 0)
+        }
+    }
+}
+
 int launch_update(akm_handle h, const double *sum, int k, int k0, double *Cnew, double *clnew, const double *Cprev,
                   const double *clprev, bool new_is_c1, double tol, double *shift, int *iscal) {
-    update_kernel<<<1, UPD_THREADS, 0, h->stream>>>(h->metric, sum, k, k0, h->d, Cnew, clnew, Cprev, clprev,
-                                                    new_is_c1 ? 1 : 0, tol, shift, h->cmap, iscal);
+    const size_t smem = (size_t)8 * 2 * h->d * sizeof(double);
+    if (smem > 96 * 1024 || h->inv_cap < k0) {
+        update_kernel<<<1, UPD_THREADS, 0, h->stream>>>(h->metric, sum, k, k0, h->d, Cnew, clnew, Cprev, clprev,
+                                                        new_is_c1 ? 1 : 0, tol, shift, h->cmap, iscal);
+    } else {
+        update_map_kernel<<<1, UPD_THREADS, 0, h->stream>>>(sum, k, k0, h->d, h->cmap, h->inv, iscal);
+        if (smem > 48 * 1024)
+            AKM_CUDA(h, cudaFuncSetAttribute(update_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        update_rows_kernel<<<(k0 + 7) / 8, 256, smem, h->stream>>>(h->metric, sum, k0, h->d, Cnew, clnew, Cprev, clprev,
+                                                                  new_is_c1 ? 1 : 0, tol, shift, h->inv, iscal);
+        h->stats.kernel_launches++;
+    }
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     return AKM_OK;

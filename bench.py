@@ -144,7 +144,7 @@ def size_cpu_sample(d, k, threads, target_s):
     return int(max(probe, min(rate * target_s, 4_000_000)))
 
 
-def run_reference(args, rank, world):
+def run_reference(args, rank, world, emit):
     """Reference arm: Alink's own CPU implementation of the path = the oracle port (no JVM on this image)."""
     if rank != 0:
         return
@@ -165,7 +165,7 @@ def run_reference(args, rank, world):
         "gpu_launches": 0,
         "note": "JVM/Alink jars are not runnable on this image (no java); the C restatement stands in for the Java path",
     }
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def workload_config(args, world):
@@ -195,9 +195,17 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # The contract is ONE JSON line on stdout.  Native libraries (NCCL's version banner, for one) write to
+    # fd 1 directly, so everything except that line is sent to stderr.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(json_fd, (json.dumps(obj) + "\n").encode())
 
     if args.impl == "reference":
-        run_reference(args, rank, world)
+        run_reference(args, rank, world, emit)
         return
 
     import torch
@@ -370,7 +378,7 @@ def main():
                                 "rows change cluster in one pass); its cost is one-off per training run"},
             "engine": {native.ENGINE_TENSOR: "tensor", native.ENGINE_EXACT: "exact"}.get(engine_used, "?"),
         }
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
