@@ -157,7 +157,7 @@ constexpr int WL_BLOCK = 2048;         // worklist slots a warp reserves at a ti
 constexpr int MAX_BSLOTS = 16;
 constexpr float PAD_SCORE = 1.0e30f;  // score offset of padding centroids (never candidates)
 
-// per-pass constants produced by c16_build_kernel
+// per-pass constants produced by c16_rows_kernel
 struct PassConst {
     float c16_max;     // max_j ||c16_j / scale||   (rounded up)
     float dc_max;      // max_j ||c_j - c16_j / scale||
@@ -927,43 +927,47 @@ __global__ void x16_build_kernel(const T *__restrict__ X, int64_t n, int d, int 
     }
 }
 
-// single CTA: fp16 centroid operand (scaled), score offsets, per-pass constants
-__global__ void __launch_bounds__(1024)
-c16_build_kernel(const double *__restrict__ C, const double *__restrict__ clabel, int k, int kpad, int d, int d16,
-                 int metric, int sx, __half *__restrict__ c16, float *__restrict__ cn, PassConst *__restrict__ pc,
-                 const double *__restrict__ Cprev, const int *__restrict__ remap, int k_prev,
-                 float *__restrict__ sig_old) {
-    __shared__ float red[32];
-    __shared__ int s_sc, s_bad;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // 1. max |c| -> scale exponent
+// fp16 centroid operand (scaled), score offsets and per-pass constants, in two multi-CTA kernels:
+// c16_max_kernel finds max |c| (-> scale exponent), c16_rows_kernel converts one centroid row per warp,
+// records the norms the error bound needs (atomic max on the float bit patterns; PassConst is zeroed
+// first) and the distance each OLD label's centroid moved since the previous pass.
+__global__ void c16_max_kernel(const double *__restrict__ C, size_t count, unsigned *__restrict__ maxbits) {
     float m = 0.f;
-    for (size_t i = tid; i < (size_t)k * d; i += blockDim.x) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < count; i += stride) {
         const float a = __double2float_ru(fabs(C[i]));
         m = (a > m || a != a) ? a : m;
     }
     for (int o = 16; o > 0; o >>= 1) { const float t = __shfl_xor_sync(0xffffffffu, m, o); m = (t > m || t != t) ? t : m; }
-    if (lane == 0) red[warp] = m;
-    __syncthreads();
-    if (tid == 0) {
-        float mm = 0.f;
-        for (int w = 0; w < 32; ++w) mm = (red[w] > mm || red[w] != red[w]) ? red[w] : mm;
-        int bad = !(mm < 3.0e38f);
-        int e = 0;
-        if (!bad && mm > 0.f) { frexpf(mm, &e); }       // mm = f * 2^e, f in [0.5, 1)
-        s_sc = bad ? 0 : (mm > 0.f ? 14 - e : 0);      // max |c| * 2^sc in [2^13, 2^14)
-        s_bad = bad;
+    if ((threadIdx.x & 31) == 0) atomicMax(maxbits, __float_as_uint(m));   // NaN bit patterns sort above +inf
+}
+
+__global__ void __launch_bounds__(256)
+c16_rows_kernel(const double *__restrict__ C, const double *__restrict__ clabel, int k, int kpad, int d, int d16,
+                int metric, int sx, const unsigned *__restrict__ maxbits, __half *__restrict__ c16,
+                float *__restrict__ cn, PassConst *__restrict__ pc, const double *__restrict__ Cprev,
+                const int *__restrict__ remap, int k_prev, float *__restrict__ sig_old) {
+    const int lane = threadIdx.x & 31;
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const float mm = __uint_as_float(*maxbits);
+    const bool bad = !(mm < 1.0e9f);                      // non-finite or absurdly large: the search is skipped
+    int e = 0;
+    if (!bad && mm > 0.f) frexpf(mm, &e);                 // mm = f * 2^e, f in [0.5, 1)
+    const int sc = (bad || !(mm > 0.f)) ? 0 : 14 - e;     // max |c| * 2^sc in [2^13, 2^14)
+    if (w == 0 && lane == 0) {
+        const float sgn = (metric == AKM_EUCLIDEAN) ? -2.f : -1.f;
+        pc->score_scale = sgn * ldexpf(1.f, -(sx + sc));
+        pc->sc = sc;
+        pc->bad = bad ? 1 : 0;
     }
-    __syncthreads();
-    const int sc = s_sc;
-    const double up = ldexp(1.0, sc), down = ldexp(1.0, -sc);
-    // 2. convert rows; per-centroid norms (one warp per centroid)
-    float w_c16 = 0.f, w_dc = 0.f, w_c = 0.f;
-    for (int j = warp; j < kpad; j += 32) {
+    if (w < kpad) {
+        const int j = w;
+        const double up = ldexp(1.0, sc), down = ldexp(1.0, -sc);
         double s2 = 0.0, e2 = 0.0, t2 = 0.0;
         for (int c = lane; c < d16; c += 32) {
             __half hv = __float2half_rn(0.f);
-            if (j < k && c < d) {
+            if (j < k && c < d && !bad) {
                 const double v = C[(size_t)j * d + c];
                 hv = __double2half(v * up);
                 const double back = (double)__half2float(hv) * down;
@@ -980,34 +984,22 @@ c16_build_kernel(const double *__restrict__ C, const double *__restrict__ clabel
         if (lane == 0) {
             if (j < k) {
                 cn[j] = (metric == AKM_EUCLIDEAN) ? (float)clabel[j] : 0.f;
-                w_c = fmaxf(w_c, __double2float_ru(sqrt(s2) * (1.0 + 1e-9)));
-                w_dc = fmaxf(w_dc, __double2float_ru(sqrt(e2) * (1.0 + 1e-9)));
-                w_c16 = fmaxf(w_c16, __double2float_ru(sqrt(t2) * (1.0 + 1e-9)));
+                atomicMax(reinterpret_cast<unsigned *>(&pc->c_max), __float_as_uint(__double2float_ru(sqrt(s2) * (1.0 + 1e-9))));
+                atomicMax(reinterpret_cast<unsigned *>(&pc->dc_max), __float_as_uint(__double2float_ru(sqrt(e2) * (1.0 + 1e-9))));
+                atomicMax(reinterpret_cast<unsigned *>(&pc->c16_max), __float_as_uint(__double2float_ru(sqrt(t2) * (1.0 + 1e-9))));
             } else {
                 cn[j] = PAD_SCORE;
             }
         }
-    }
-    // how far did the centroid of each OLD label move? (remap: old index -> new index, -1 = dropped)
-    for (int a = warp; a < k_prev; a += 32) {
+    } else if (w < kpad + k_prev) {
+        // how far did the centroid of OLD label a move? (remap: old index -> new index, -1 = dropped)
+        const int a = w - kpad;
         const int j = remap ? remap[a] : a;
         double s2 = 0.0;
         if (j >= 0 && j < k)
             for (int c = lane; c < d; c += 32) { const double df = C[(size_t)j * d + c] - Cprev[(size_t)a * d + c]; s2 = fma(df, df, s2); }
         for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
         if (lane == 0) sig_old[a] = (j >= 0 && j < k) ? __double2float_ru(sqrt(s2) * (1.0 + 1e-9)) : INFINITY;
-    }
-    __shared__ float r1[32], r2[32], r3[32];
-    if (lane == 0) { r1[warp] = w_c16; r2[warp] = w_dc; r3[warp] = w_c; }
-    __syncthreads();
-    if (tid == 0) {
-        float a = 0.f, b = 0.f, c = 0.f;
-        for (int w = 0; w < 32; ++w) { a = fmaxf(a, r1[w]); b = fmaxf(b, r2[w]); c = fmaxf(c, r3[w]); }
-        pc->c16_max = a; pc->dc_max = b; pc->c_max = c;
-        const float sgn = (metric == AKM_EUCLIDEAN) ? -2.f : -1.f;
-        pc->score_scale = sgn * ldexpf(1.f, -(sx + sc));
-        pc->sc = sc;
-        pc->bad = s_bad || !(c < 1e18f);
     }
 }
 
@@ -1359,9 +1351,13 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     if (no_seed_env) use_seed = false;
     const int k_prev = use_seed ? c->k_prev : 0;
     AKM_CUDA(h, cudaMemsetAsync(c->counters, 0, 4 * sizeof(int), h->stream));
-    c16_build_kernel<<<1, 1024, 0, h->stream>>>(C, clabel, k, kpad, d, d16, h->metric, rs.x16_shift, c->c16, c->cn, c->pc,
-                                                c->Cprev, (chain == 1) ? remap : nullptr, k_prev, c->sig_old);
-    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaMemsetAsync(c->pc, 0, sizeof(PassConst), h->stream));
+    AKM_CUDA(h, cudaMemsetAsync(c->absmax, 0, sizeof(unsigned), h->stream));
+    c16_max_kernel<<<std::min(h->num_sms, (k * d + 255) / 256), 256, 0, h->stream>>>(C, (size_t)k * d, c->absmax);
+    c16_rows_kernel<<<(kpad + k_prev + 7) / 8, 256, 0, h->stream>>>(C, clabel, k, kpad, d, d16, h->metric, rs.x16_shift,
+                                                                     c->absmax, c->c16, c->cn, c->pc, c->Cprev,
+                                                                     (chain == 1) ? remap : nullptr, k_prev, c->sig_old);
+    h->stats.kernel_launches += 2;
     AKM_CUDA(h, cudaGetLastError());
 
     // shared-memory plan
