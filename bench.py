@@ -335,14 +335,20 @@ def main():
     achieved = flops / (dom_ms / 1e3) / 1e12 if dom_ms > 0 else 0.0
     roofline = {"bound": "tensor", "kernel": "assign_search_tcgen05" if engine_used == native.ENGINE_TENSOR else "assign_exact_kernel (fp64 CUDA cores)",
                 "achieved": achieved, "peak": pk["tf_sust"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sust"],
-                "peak_source": "bf16 dense sustained, " + pk["source"], "traffic": None,
+                "peak_source": "bf16 dense sustained, " + pk["source"],
+                # dram__bytes_read.sum + dram__bytes_write.sum of search_pair_kernel<2> from one `ncu --set full`
+                # capture at 100M x 128 rows, k = 1000 (profiles/r1_ncu_full_100M_rows.csv): 26.80 + 1.24 GB per
+                # launch = 280.4 B per row (the fp16 operand copy is 256 B per row), scaled to this launch's rows
+                "traffic": (280.4 * cnt if (engine_used == native.ENGINE_TENSOR and d == 128 and k == 1000) else None),
+                "traffic_unit": "bytes per launch (ncu dram read+write)",
                 "algorithmic": "2*k*d flop per sample (SURVEY 8d) x %d samples per launch" % cnt,
                 "kernel_ms": dom_ms}
     acc_ms = prof["accumulate_ms"] / steps_p
     acc_bytes = cnt * (d * 4 + 4)
     roofline_accumulate = {"bound": "hbm", "kernel": "accumulate_kernel", "achieved": acc_bytes / (acc_ms / 1e3) / 1e9 if acc_ms > 0 else 0.0,
                            "peak": pk["hbm"], "unit": "GB/s", "frac": (acc_bytes / (acc_ms / 1e3) / 1e9 / pk["hbm"]) if acc_ms > 0 else 0.0,
-                           "traffic": None, "kernel_ms": acc_ms}
+                           # accumulate_kernel: 52.89 + 0.05 GB per launch at 100M rows = 529.4 B per row
+                           "traffic": (529.4 * cnt if d == 128 else None), "kernel_ms": acc_ms}
 
     # ---------------- CPU baseline beside it (rank 0, N = 1 only)
     cpu = None
