@@ -172,6 +172,7 @@ struct SearchParams {
     int groups;             // row groups of MB*128 rows
     int ntiles;             // centroid tiles of 128
     int a_stages, b_slots, resident;
+    int kblocks;            // K-streaming pair kernel: 64-half blocks per row (d16 / 64)
     int d, metric, k;
     const float *cn;        // ntiles*128 score offsets
     const PassConst *pc;
@@ -610,27 +611,33 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                    const SearchParams p) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    constexpr int A_STAGE = KB * BOX_BYTES;            // 128 rows of this CTA
+    // KB > 0: centroids resident, rows staged whole (2 stages).  KB == 0 (STREAM): a ring of p.a_stages stages,
+    // each one 64-half block of this CTA's 128 rows + the same block of its 128 centroids of the current tile.
+    constexpr bool STREAM = KB == 0;
+    constexpr int A_STAGE = STREAM ? 2 * BOX_BYTES : KB * BOX_BYTES;   // 128 rows of this CTA (STREAM: rows + centroids block)
     constexpr int B_TILE = KB * BOX_BYTES;             // this CTA's 128 centroids of a 256-centroid tile
+    constexpr int MAX_STAGES = 8;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
     const int pair_id = blockIdx.x >> 1, npairs = gridDim.x >> 1;
     const int nt = p.ntiles;                           // tiles of 256 centroids
+    const int ns = STREAM ? p.a_stages : 2;
+    const int nkb = STREAM ? p.kblocks : KB;
 
     unsigned char *a_smem = smem;
-    unsigned char *b_smem = smem + 2 * A_STAGE;
+    unsigned char *b_smem = smem + (size_t)ns * A_STAGE;
     float *cn_s = reinterpret_cast<float *>(b_smem + (size_t)nt * B_TILE);
     uint64_t *bars = reinterpret_cast<uint64_t *>(cn_s + nt * PAIR_N);
-    uint64_t *a_full = bars, *a_empty = bars + 2, *b_full = bars + 4, *t_full = bars + 5, *t_empty = bars + 7;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 9);
+    uint64_t *t_full = bars, *t_empty = bars + 2, *b_full = bars + 4, *a_full = bars + 5, *a_empty = a_full + MAX_STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(a_empty + MAX_STAGES);
     float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);
     float2 *cand_s = reinterpret_cast<float2 *>(pc_s + 8);                 // [4 quarters][128 rows][MAX_CAND]
     float *xch_s = reinterpret_cast<float *>(cand_s + 4 * TILE_M * MAX_CAND);   // [4 quarters][128 rows][4]
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
+        for (int i = 0; i < ns; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
         mbar_init(smem_u32(b_full), 1);
         for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), 32); }
         fence_barrier_init();
@@ -649,22 +656,39 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
     if (warp == 0) {
         // =============================== TMA producer (both CTAs; completion lands on the leader's barriers)
         if (lane == 0) {
-            const uint32_t bfull_leader = smem_u32(b_full) & PEER_BIT_MASK;
-            if (leader) mbar_expect_tx(smem_u32(b_full), 2u * (uint32_t)nt * B_TILE);
-            for (int t = 0; t < nt; ++t)
-                for (int kb = 0; kb < KB; ++kb)
-                    tma_load_2d_2sm(smem_u32(b_smem + (size_t)t * B_TILE + kb * BOX_BYTES), &tmapC, bfull_leader, kb * KBLK,
-                                    t * PAIR_N + (int)rank * TILE_M);
-            int it = 0;
-            for (int g = pair_id; g < ngroups; g += npairs, ++it) {
-                const int as = it & 1;
-                mbar_wait(smem_u32(a_empty + as), ((it >> 1) & 1) ^ 1);
-                if (leader) mbar_expect_tx(smem_u32(a_full + as), 2u * A_STAGE);
-                const uint32_t afull_leader = smem_u32(a_full + as) & PEER_BIT_MASK;
-                const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
-                for (int kb = 0; kb < KB; ++kb)
-                    tma_load_2d_2sm(smem_u32(a_smem + (size_t)as * A_STAGE + kb * BOX_BYTES), &tmapX, afull_leader, kb * KBLK,
-                                    (int)row0);
+            if constexpr (STREAM) {
+                int s_i = 0, ph = 0;
+                for (int g = pair_id; g < ngroups; g += npairs) {
+                    const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
+                    for (int t = 0; t < nt; ++t)
+                        for (int kb = 0; kb < nkb; ++kb) {
+                            mbar_wait(smem_u32(a_empty + s_i), ph ^ 1);
+                            if (leader) mbar_expect_tx(smem_u32(a_full + s_i), 2u * A_STAGE);
+                            const uint32_t full_leader = smem_u32(a_full + s_i) & PEER_BIT_MASK;
+                            const uint32_t dst = smem_u32(a_smem + (size_t)s_i * A_STAGE);
+                            tma_load_2d_2sm(dst, &tmapX, full_leader, kb * KBLK, (int)row0);
+                            tma_load_2d_2sm(dst + BOX_BYTES, &tmapC, full_leader, kb * KBLK, t * PAIR_N + (int)rank * TILE_M);
+                            if (++s_i == ns) { s_i = 0; ph ^= 1; }
+                        }
+                }
+            } else {
+                const uint32_t bfull_leader = smem_u32(b_full) & PEER_BIT_MASK;
+                if (leader) mbar_expect_tx(smem_u32(b_full), 2u * (uint32_t)nt * B_TILE);
+                for (int t = 0; t < nt; ++t)
+                    for (int kb = 0; kb < KB; ++kb)
+                        tma_load_2d_2sm(smem_u32(b_smem + (size_t)t * B_TILE + kb * BOX_BYTES), &tmapC, bfull_leader, kb * KBLK,
+                                        t * PAIR_N + (int)rank * TILE_M);
+                int it = 0;
+                for (int g = pair_id; g < ngroups; g += npairs, ++it) {
+                    const int as = it & 1;
+                    mbar_wait(smem_u32(a_empty + as), ((it >> 1) & 1) ^ 1);
+                    if (leader) mbar_expect_tx(smem_u32(a_full + as), 2u * A_STAGE);
+                    const uint32_t afull_leader = smem_u32(a_full + as) & PEER_BIT_MASK;
+                    const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
+                    for (int kb = 0; kb < KB; ++kb)
+                        tma_load_2d_2sm(smem_u32(a_smem + (size_t)as * A_STAGE + kb * BOX_BYTES), &tmapX, afull_leader, kb * KBLK,
+                                        (int)row0);
+                }
             }
         }
     } else if (warp == 1) {
@@ -672,33 +696,60 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         if (leader) {
             constexpr uint32_t DESC_HI = 64u | (1u << 14) | (2u << 29);
             const uint32_t a_lo0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) | (1u << 16);
-            const uint32_t b_lo0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) | (1u << 16);
-            mbar_wait(smem_u32(b_full), 0);
-            int it = 0, t_it = 0;
-            for (int g = pair_id; g < ngroups; g += npairs, ++it) {
-                const int as = it & 1;
-                mbar_wait(smem_u32(a_full + as), (it >> 1) & 1);
-                for (int t = 0; t < nt; ++t, ++t_it) {
-                    const int tb = t_it & 1;
-                    mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
-                    tc_fence_after();
-                    if (lane == 0) {
-                        const uint32_t a_lo = a_lo0 + (uint32_t)as * (A_STAGE >> 4);
-                        const uint32_t b_lo = b_lo0 + (uint32_t)t * (B_TILE >> 4);
+            if constexpr (STREAM) {
+                int s_i = 0, ph = 0, t_it = 0;
+                for (int g = pair_id; g < ngroups; g += npairs) {
+                    for (int t = 0; t < nt; ++t, ++t_it) {
+                        const int tb = t_it & 1;
+                        mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
+                        tc_fence_after();
                         const uint32_t d0 = tmem_base + (uint32_t)(tb * PAIR_N);
+                        for (int kb = 0; kb < nkb; ++kb) {
+                            mbar_wait(smem_u32(a_full + s_i), ph);
+                            tc_fence_after();
+                            if (lane == 0) {
+                                const uint32_t a_lo = a_lo0 + (uint32_t)s_i * (A_STAGE >> 4);
+                                const uint32_t b_lo = a_lo + (BOX_BYTES >> 4);
 #pragma unroll
-                        for (int kb = 0; kb < KB; ++kb)
-#pragma unroll
-                            for (int k4 = 0; k4 < KBLK / 16; ++k4)
-                                umma_f16_2sm(d0, a_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4,
-                                             b_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4, DESC_HI, IDESC_F16_256x256,
-                                             (kb | k4) != 0);
-                        umma_commit_2sm(smem_u32(t_full + tb), 3);
+                                for (int k4 = 0; k4 < KBLK / 16; ++k4)
+                                    umma_f16_2sm(d0, a_lo + 2 * k4, b_lo + 2 * k4, DESC_HI, IDESC_F16_256x256, (kb | k4) != 0);
+                                umma_commit_2sm(smem_u32(a_empty + s_i), 3);       // frees the stage in both CTAs
+                                if (kb == nkb - 1) umma_commit_2sm(smem_u32(t_full + tb), 3);
+                            }
+                            __syncwarp();
+                            if (++s_i == ns) { s_i = 0; ph ^= 1; }
+                        }
                     }
+                }
+            } else {
+                const uint32_t b_lo0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+                mbar_wait(smem_u32(b_full), 0);
+                int it = 0, t_it = 0;
+                for (int g = pair_id; g < ngroups; g += npairs, ++it) {
+                    const int as = it & 1;
+                    mbar_wait(smem_u32(a_full + as), (it >> 1) & 1);
+                    for (int t = 0; t < nt; ++t, ++t_it) {
+                        const int tb = t_it & 1;
+                        mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
+                        tc_fence_after();
+                        if (lane == 0) {
+                            const uint32_t a_lo = a_lo0 + (uint32_t)as * (A_STAGE >> 4);
+                            const uint32_t b_lo = b_lo0 + (uint32_t)t * (B_TILE >> 4);
+                            const uint32_t d0 = tmem_base + (uint32_t)(tb * PAIR_N);
+#pragma unroll
+                            for (int kb = 0; kb < KB; ++kb)
+#pragma unroll
+                                for (int k4 = 0; k4 < KBLK / 16; ++k4)
+                                    umma_f16_2sm(d0, a_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4,
+                                                 b_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4, DESC_HI, IDESC_F16_256x256,
+                                                 (kb | k4) != 0);
+                            umma_commit_2sm(smem_u32(t_full + tb), 3);
+                        }
+                        __syncwarp();
+                    }
+                    if (lane == 0) umma_commit_2sm(smem_u32(a_empty + as), 3);
                     __syncwarp();
                 }
-                if (lane == 0) umma_commit_2sm(smem_u32(a_empty + as), 3);
-                __syncwarp();
             }
         }
     } else {
@@ -1165,8 +1216,7 @@ void tensor_free(akm_handle h) {
 static int round_up(int a, int b) { return (a + b - 1) / b * b; }
 
 bool tensor_supported(akm_handle h, int k0) {
-    const int kb = (h->d + KBLK - 1) / KBLK;
-    if (kb > 2) return false;                 // d <= 128 for now (A tile fully resident per row group)
+    if (h->d > 8192) return false;            // K is streamed in 64-half blocks; the bound keeps eta small
     if (k0 > 8064) return false;              // score offsets live in shared memory
     if (h->smem_optin < 200 * 1024) return false;
     return true;
@@ -1301,9 +1351,18 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     static const bool pair_off = getenv("AKM_TC_PAIR") && atoi(getenv("AKM_TC_PAIR")) == 0;   // tuning aid
     const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
     const int nt2 = (k + PAIR_N - 1) / PAIR_N;
-    const size_t pair_smem = (size_t)2 * KB * BOX_BYTES + (size_t)nt2 * KB * BOX_BYTES + (size_t)nt2 * PAIR_N * 4 + 256 +
-                             (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 + 1024;
-    const bool use_pair = !pair_off && pair_smem <= budget && h->num_sms >= 2 && rs.n > 2 * TILE_M;
+    const size_t pair_fixed = (size_t)nt2 * PAIR_N * 4 + 256 + (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 + 1024;
+    size_t pair_smem = (size_t)2 * KB * BOX_BYTES + (size_t)nt2 * KB * BOX_BYTES + pair_fixed;
+    const bool pair_ok = !pair_off && h->num_sms >= 2 && rs.n > 2 * TILE_M;
+    // centroids resident (d <= 128 and they fit) or, for every other shape, both operands streamed in K blocks
+    static const bool stream_env = getenv("AKM_TC_STREAM") && atoi(getenv("AKM_TC_STREAM")) != 0;   // tuning aid
+    const bool pair_resident = pair_ok && KB <= 2 && pair_smem <= budget && !stream_env;
+    int stream_stages = 0;
+    if (pair_ok && !pair_resident && budget > pair_fixed) stream_stages = (int)std::min<size_t>(8, (budget - pair_fixed) / (2 * BOX_BYTES));
+    const bool pair_stream = stream_stages >= 3;
+    if (pair_stream) pair_smem = (size_t)stream_stages * 2 * BOX_BYTES + pair_fixed;
+    const bool use_pair = pair_resident || pair_stream;
+    if (!use_pair && KB > 2) return exact_all();       // the single-CTA kernel keeps whole rows resident: d <= 128
     const int ntiles = use_pair ? nt2 : (k + TILE_N - 1) / TILE_N;
     const int kpad = use_pair ? nt2 * PAIR_N : ntiles * TILE_N;
     const int d16 = rs.d16;
@@ -1381,7 +1440,8 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     SearchParams sp{};
     sp.n = rs.n;
     sp.groups = (int)ceil_div64(rs.n, (int64_t)MB * TILE_M);
-    sp.ntiles = ntiles; sp.a_stages = a_stages; sp.b_slots = b_slots; sp.resident = resident;
+    sp.ntiles = ntiles; sp.a_stages = pair_stream ? stream_stages : a_stages; sp.b_slots = b_slots; sp.resident = resident;
+    sp.kblocks = KB;
     sp.d = d; sp.metric = h->metric; sp.k = k;
     sp.cn = c->cn; sp.pc = c->pc; sp.xerr = rs.xerr; sp.labels = labels;
     sp.wl_rows = c->wl_rows; sp.wl_cand = c->wl_cand; sp.counters = c->counters;
@@ -1409,7 +1469,8 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     if (use_pair) {
         const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
         const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;
-        rc = (KB == 1) ? launch_pair<1>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2>(h, mapX, mapC, sp, pair_smem, pgrid);
+        rc = pair_stream ? launch_pair<0>(h, mapX, mapC, sp, pair_smem, pgrid)
+             : (KB == 1) ? launch_pair<1>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2>(h, mapX, mapC, sp, pair_smem, pgrid);
     } else if (KB == 1) rc = (CL == 2) ? launch_search<2, 1, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 1, 1>(h, mapX, mapC, sp, smem, grid);
     else rc = (CL == 2) ? launch_search<2, 2, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 2, 1>(h, mapX, mapC, sp, smem, grid);
     AKM_TRY(rc);

@@ -115,20 +115,20 @@ def cpu_rows(n, d, k, seed=SEED):
     return X.astype(np.float32).astype(np.float64)
 
 
-def cpu_lloyd_rate(X, C0, threads, steps, warmup, budget_s=None):
+def cpu_lloyd_rate(X, C0, threads, steps, warmup, metric=0):
     """sample-iters/s of the Java-order CPU restatement: assign (distances evaluated twice, like
     KMeansUtil.updateSumMatrix) + all-reduce in rank order + update, `threads` Flink subtasks."""
     import oracle as orc
     n, d = X.shape
     k0 = C0.shape[0]
-    Xp, xl = orc.prepare_rows(orc.EUCLIDEAN, X)
-    C, cl = orc.prepare_centroids(orc.EUCLIDEAN, C0)
+    Xp, xl = orc.prepare_rows(metric, X)
+    C, cl = orc.prepare_centroids(metric, C0)
     k = k0
     times = []
     for s in range(warmup + steps):
         t0 = time.perf_counter()
-        sm, _, _ = orc.assign_accumulate(orc.EUCLIDEAN, Xp, xl, C, cl, k=k, dup=True, threads=threads)
-        C, cl, k = orc.update_centroids(orc.EUCLIDEAN, sm, k, k0, d)
+        sm, _, _ = orc.assign_accumulate(metric, Xp, xl, C, cl, k=k, dup=True, threads=threads)
+        C, cl, k = orc.update_centroids(metric, sm, k, k0, d)
         t1 = time.perf_counter()
         if s >= warmup:
             times.append(t1 - t0)
@@ -136,11 +136,11 @@ def cpu_lloyd_rate(X, C0, threads, steps, warmup, budget_s=None):
     return n * len(times) / total, total / len(times)
 
 
-def size_cpu_sample(d, k, threads, target_s):
+def size_cpu_sample(d, k, threads, target_s, metric=0):
     """Rows per CPU step so that one step costs about target_s seconds (probe, then scale)."""
     probe = max(threads * 200, 1000)
     X = cpu_rows(probe, d, k, seed=1)
-    rate, _ = cpu_lloyd_rate(X, X[:k].copy() if probe >= k else cpu_rows(k, d, k, 2), threads, 1, 0)
+    rate, _ = cpu_lloyd_rate(X, X[:k].copy() if probe >= k else cpu_rows(k, d, k, 2), threads, 1, 0, metric)
     return int(max(probe, min(rate * target_s, 4_000_000)))
 
 
@@ -149,10 +149,10 @@ def run_reference(args, rank, world, emit):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    n_s = args.cpu_rows or size_cpu_sample(args.d, args.k, threads, 4.0)
+    n_s = args.cpu_rows or size_cpu_sample(args.d, args.k, threads, 4.0, args.metric)
     X = cpu_rows(n_s, args.d, args.k)
     C0 = X[(np.arange(args.k) * n_s) // args.k].copy()
-    rate, sec = cpu_lloyd_rate(X, C0, threads, args.steps, args.warmup)
+    rate, sec = cpu_lloyd_rate(X, C0, threads, args.steps, args.warmup, args.metric)
     sample = "oracle port of Alink's Java order (2 dgemv/sample, no FMA), %d threads = Flink subtasks, %d of %d rows per step" % (
         threads, n_s, args.rows)
     out = {
@@ -169,8 +169,9 @@ def run_reference(args, rank, world, emit):
 
 
 def workload_config(args, world):
-    return {"workload": "gaussian blobs %dx%d fp32-exact, k=%d, EUCLIDEAN, init = rows floor(i*N/k)" % (args.rows, args.d, args.k),
-            "rows": args.rows, "d": args.d, "k": args.k, "distance": "EUCLIDEAN", "seed": SEED,
+    return {"workload": "gaussian blobs %dx%d fp32-exact, k=%d, %s, init = rows floor(i*N/k)" % (
+                args.rows, args.d, args.k, args.distance.upper()),
+            "rows": args.rows, "d": args.d, "k": args.k, "distance": args.distance.upper(), "seed": SEED,
             "sharding": "rows by DefaultDistributedInfo over %d rank(s); allreduce k*(d+1) f64 via NCCL" % world,
             "l2": "inputs (%.1f GB per rank) far exceed the 126 MB L2; no flush needed" % (args.rows * args.d * 4 / world / 1e9),
             "epsilon": 0.0}
@@ -186,11 +187,13 @@ def main():
     ap.add_argument("--d", type=int, default=128)
     ap.add_argument("--k", type=int, default=1000)
     ap.add_argument("--engine", default="auto", choices=["auto", "exact", "tensor"])
+    ap.add_argument("--distance", default="euclidean", choices=["euclidean", "cosine"])
     ap.add_argument("--cpu-rows", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
+    args.metric = 1 if args.distance == "cosine" else 0     # akm.h AKM_EUCLIDEAN / AKM_COSINE, same in oracle/
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -241,7 +244,7 @@ def main():
     N, d, k = args.rows, args.d, args.k
     start, cnt = shard(rank, world, N)
     stream = torch.cuda.Stream()
-    h = native.Handle(d, native.EUCLIDEAN, device=local_rank)
+    h = native.Handle(d, args.metric, device=local_rank)
     h.set_stream(stream.cuda_stream)
     h.set_engine({"auto": native.ENGINE_AUTO, "exact": native.ENGINE_EXACT, "tensor": native.ENGINE_TENSOR}[args.engine])
     t0 = time.perf_counter()
@@ -315,7 +318,7 @@ def main():
     if rank == 0:
         m_up = min(cnt, 1_000_000)
         Xs = h.blobs_rows(SEED, k, np.arange(m_up, dtype=np.int64)).astype(np.float64)
-        with native.Handle(d, native.EUCLIDEAN, device=local_rank) as h2:
+        with native.Handle(d, args.metric, device=local_rank) as h2:
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             h2.upload_rows(Xs)
@@ -354,10 +357,10 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        n_cpu = args.cpu_rows or size_cpu_sample(d, k, threads, 12.0)
+        n_cpu = args.cpu_rows or size_cpu_sample(d, k, threads, 12.0, args.metric)
         n_cpu = min(n_cpu, cnt)
         Xc = h.blobs_rows(SEED, k, np.arange(n_cpu, dtype=np.int64)).astype(np.float64)
-        rate, sec = cpu_lloyd_rate(Xc, C0, threads, 1, 0)
+        rate, sec = cpu_lloyd_rate(Xc, C0, threads, 1, 0, args.metric)
         cpu = {"value": rate, "unit": "sample-iters/s", "cores": threads, "kind": "port",
                "sample": "first %d of %d rows, 1 Lloyd iteration (%.1f s), C restatement of Alink's Java order incl. the duplicated "
                          "distance evaluation, %d threads = Flink subtasks; JVM not runnable on this box (no java)" % (n_cpu, N, sec, threads)}

@@ -31,6 +31,13 @@ bad += run(20000, 128, 1000, 1000, 3)
 bad += run(20000, 128, 1000, 300, 4)
 bad += run(3000, 100, 257, 60, 5, native.COSINE)
 bad += run(70000, 128, 300, 100, 6)
+# d > 128: K-streaming pair kernel
+bad += run(20000, 256, 500, 500, 7, native.COSINE)
+bad += run(20000, 256, 500, 200, 8)
+bad += run(10000, 784, 10, 10, 9)
+bad += run(5000, 200, 300, 80, 10)
+bad += run(3000, 1000, 70, 70, 14)
+bad += run(40000, 136, 2000, 2000, 15)
 print("TOTAL MISMATCHES", bad)
 
 # multi-pass training: exercises the seeded thresholds (chain of akm_step passes)
@@ -56,4 +63,7 @@ bad = 0
 bad += train_check(30000, 128, 1000, 300, 11)
 bad += train_check(30000, 64, 100, 100, 12)
 bad += train_check(20000, 100, 200, 50, 13, native.COSINE)
+bad += train_check(20000, 256, 500, 200, 16, native.COSINE)
+bad += train_check(20000, 784, 10, 10, 17)
+bad += train_check(20000, 320, 600, 300, 18)
 print("TRAIN MISMATCHES", bad)

@@ -179,6 +179,43 @@ def test_near_ties_are_resolved_exactly(engine, metric):
         assert st["rows_refined"] > 0
 
 
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+@pytest.mark.parametrize("n,d,k", [(3000, 256, 500), (2500, 784, 10), (1500, 200, 300), (700, 1000, 70), (3000, 136, 1100)])
+def test_wide_rows_use_the_k_streaming_tensor_search(metric, n, d, k):
+    # d > 128 (BASELINE configs 2 and 5): both operands stream through shared memory in 64-half blocks
+    X = blobs(n, d, max(k // 3, 2), seed=n + d)             # several centroids per blob: real near-ties
+    C = X[np.random.default_rng(d).choice(n, k, replace=False)].copy()
+    Cp, s_ref, l_ref, _, obj_ref = oracle_pass(metric, X, C)
+    with native.Handle(d, metric) as h:
+        h.set_engine(native.ENGINE_TENSOR)
+        h.upload_rows(X)
+        s, obj, labels = h.assign_accumulate(Cp, want_labels=True)
+        st = h.stats()
+    assert st["engine_used"] == native.ENGINE_TENSOR and st["rows_certified"] > 0
+    assert (labels == l_ref).all(), "mismatches: %d" % int((labels != l_ref).sum())
+    np.testing.assert_allclose(s, s_ref, rtol=1e-12, atol=1e-9)
+    assert abs(obj - obj_ref) <= 1e-9 * max(1.0, abs(obj_ref))
+
+
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_wide_rows_training_loop_matches_oracle(metric):
+    n, d, k = 5000, 256, 60
+    X = blobs(n, d, 30, seed=77)
+    C0 = X[np.random.default_rng(3).choice(n, k, replace=False)].copy()
+    ref = orc.train(metric, X, C0, max_iter=8, tol=1e-4)
+    with native.Handle(d, metric) as h:
+        h.set_engine(native.ENGINE_TENSOR)
+        h.upload_rows(X)
+        m = h.train(C0, max_iter=8, tol=1e-4)
+        labels = h.get_labels()
+        st = h.stats()
+    assert st["engine_used"] == native.ENGINE_TENSOR
+    assert m["iters"] == ref["iters"] and m["k"] == ref["k"]
+    assert (labels == ref["labels"]).all()
+    np.testing.assert_allclose(m["C"][: m["k"]], ref["C"][: ref["k"]], rtol=1e-9, atol=1e-12)
+    assert (m["weights"] == ref["weights"]).all()
+
+
 def test_only_the_first_k_centroids_are_candidates():
     d = 8
     X = blobs(500, d, 3, seed=9)
