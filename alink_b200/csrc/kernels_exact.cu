@@ -367,10 +367,14 @@ template <> struct Vec16<double> { using type = double2; static constexpr int N 
 
 // VEC == true: each lane owns 16-byte column groups (lane + 32*m) -> one 128-bit load per row and group
 // (requires d % (16/sizeof(T)) == 0); VEC == false: scalar columns lane + 32*m (any d).
-template <typename T, int DC, int METRIC, bool VEC>
+// SUB > 1 (narrow rows, DC == 1): a warp reads SUB rows at a time, 32/SUB lanes each.
+// After the sort the chunk's rows are cut into items of item_rows consecutive SORTED positions; warps take
+// items round-robin and flush at every cluster boundary inside an item, so the work per warp does not depend
+// on how many clusters the chunk holds (a cluster-ordered partition has one or two per chunk).
+template <typename T, int DC, int METRIC, bool VEC, int SUB>
 __global__ void __launch_bounds__(ACC_THREADS, 3)
 accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, int64_t n, int d, int k0,
-                  int chunk_rows, const double *__restrict__ C, double *__restrict__ sum,
+                  int chunk_rows, int item_rows, const double *__restrict__ C, double *__restrict__ sum,
                   double *__restrict__ objective, const double *__restrict__ xlabel,
                   const double *__restrict__ clabel) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -380,9 +384,12 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
     __shared__ int scan_tmp[ACC_THREADS];
     __shared__ double obj_red[ACC_THREADS / 32];
     constexpr int VN = VEC ? Vec16<T>::N : 1;               // columns per lane per group
-    constexpr int COLS_PER_PASS = DC * 32 * VN;
+    constexpr int L = 32 / SUB;                             // lanes per row
+    constexpr int COLS_PER_PASS = DC * L * VN;
+    static_assert(SUB == 1 || DC == 1, "narrow-row mode covers the whole row with one group");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int sub = lane / L, cl = lane % L;
     const int64_t base = (int64_t)blockIdx.x * chunk_rows;
     const int rows = (int)min((int64_t)chunk_rows, n - base);
     const int cb0 = blockIdx.y * COLS_PER_PASS;
@@ -427,79 +434,117 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
     __syncthreads();
 
     double obj = 0.0;
-    for (int j = warp; j < k0; j += ACC_THREADS / 32) {
-        const int s = off[j], e = off[j + 1];
-        if (s == e) continue;
-        double acc[DC][VN], cen[DC][VN];
-#pragma unroll
-        for (int m = 0; m < DC; ++m)
-#pragma unroll
-            for (int v = 0; v < VN; ++v) {
-                acc[m][v] = 0.0;
-                const int col = cb0 + (lane + 32 * m) * VN + v;
-                cen[m][v] = (col < d) ? C[(size_t)j * d + col] : 0.0;
-            }
-        constexpr int U = (DC * VN <= 4) ? 6 : ((DC * VN <= 8) ? 3 : 2);   // rows in flight per warp (register budget)
-        int p = s;
-        for (; p + U <= e; p += U) {
-            using RawT = typename std::conditional<VEC, typename Vec16<T>::type, T>::type;
-            RawT raw[U][DC];                      // loads stay in their storage type until they are consumed
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const T *row = X + (base + sorted[p + u]) * (int64_t)d + cb0;
-#pragma unroll
-                for (int m = 0; m < DC; ++m) {
-                    const int c0 = (lane + 32 * m) * VN;
-                    if (cb0 + c0 < d) raw[u][m] = *reinterpret_cast<const RawT *>(row + c0);
-                    else raw[u][m] = RawT{};
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-#pragma unroll
-                for (int m = 0; m < DC; ++m) {
-                    double val[VN];
-                    if constexpr (VEC) Vec16<T>::unpack(raw[u][m], val);
-                    else val[0] = (double)raw[u][m];
-#pragma unroll
-                    for (int v = 0; v < VN; ++v) acc[m][v] += val[v];
-                }
+    const int total = off[k0];
+    for (int p0 = warp * item_rows; p0 < total; p0 += (ACC_THREADS / 32) * item_rows) {
+        const int p1 = min(total, p0 + item_rows);
+        int j;
+        {   // largest j with off[j] <= p0 (then off[j+1] > p0)
+            int lo = 0, hi = k0;
+            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (off[mid] <= p0) lo = mid; else hi = mid; }
+            j = lo;
         }
-        for (; p < e; ++p) {
-            const T *row = X + (base + sorted[p]) * (int64_t)d + cb0;
+        int p = p0;
+        while (p < p1) {
+            const int s = p, e = min(off[j + 1], p1);
+            double acc[DC][VN];
 #pragma unroll
             for (int m = 0; m < DC; ++m)
 #pragma unroll
-                for (int v = 0; v < VN; ++v) {
-                    const int c0 = (lane + 32 * m) * VN + v;
-                    const double x = (cb0 + c0 < d) ? (double)row[c0] : 0.0;
-                    acc[m][v] += x;
-                }
-        }
-        // objective of the segment, the way Java's distance is put together:
-        //   EUCL  sum ||x||^2 - 2 c.S + n ||c||^2  (||x||^2 = the stored label, S = the sums just formed)
-        //   COS   n - c.S
-        if (METRIC == AKM_EUCLIDEAN && blockIdx.y == 0) {
-            double xs = 0.0;
-            for (int q = s + lane; q < e; q += 32) xs += xlabel[base + sorted[q]];
-            obj += xs;
-            if (lane == 0) obj += (double)(e - s) * clabel[j];
-        }
-        double *out = sum + (size_t)j * (d + 1);
+                for (int v = 0; v < VN; ++v) acc[m][v] = 0.0;
+            constexpr int U = (DC * VN <= 4) ? 6 : ((DC * VN <= 8) ? 3 : 2);   // row loads in flight per lane (register budget)
+            for (; p + U * SUB <= e; p += U * SUB) {
+                using RawT = typename std::conditional<VEC, typename Vec16<T>::type, T>::type;
+                RawT raw[U][DC];                      // loads stay in their storage type until they are consumed
 #pragma unroll
-        for (int m = 0; m < DC; ++m)
+                for (int u = 0; u < U; ++u) {
+                    const T *row = X + (base + sorted[p + u * SUB + sub]) * (int64_t)d + cb0;
 #pragma unroll
-            for (int v = 0; v < VN; ++v) {
-                const int col = cb0 + (lane + 32 * m) * VN + v;
-                if (col < d) {
-                    atomicAdd(out + col, acc[m][v]);
-                    if (METRIC == AKM_EUCLIDEAN) obj -= 2.0 * cen[m][v] * acc[m][v];
-                    else obj -= cen[m][v] * acc[m][v];
+                    for (int m = 0; m < DC; ++m) {
+                        const int c0 = (cl + L * m) * VN;
+                        if (cb0 + c0 < d) raw[u][m] = *reinterpret_cast<const RawT *>(row + c0);
+                        else raw[u][m] = RawT{};
+                    }
                 }
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int m = 0; m < DC; ++m) {
+                        double val[VN];
+                        if constexpr (VEC) Vec16<T>::unpack(raw[u][m], val);
+                        else val[0] = (double)raw[u][m];
+#pragma unroll
+                        for (int v = 0; v < VN; ++v) acc[m][v] += val[v];
+                    }
             }
-        if (lane == 0 && blockIdx.y == 0) {
-            atomicAdd(out + d, (double)(e - s));
-            if (METRIC == AKM_COSINE) obj += (double)(e - s);
+            if (p < e) {                              // last, partial batch: same loads, predicated per row
+                using RawT = typename std::conditional<VEC, typename Vec16<T>::type, T>::type;
+                RawT raw[U][DC];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int q = p + u * SUB + sub;
+                    const bool ok = q < e;
+                    const T *row = X + (base + sorted[ok ? q : s]) * (int64_t)d + cb0;
+#pragma unroll
+                    for (int m = 0; m < DC; ++m) {
+                        const int c0 = (cl + L * m) * VN;
+                        if (ok && cb0 + c0 < d) raw[u][m] = *reinterpret_cast<const RawT *>(row + c0);
+                        else raw[u][m] = RawT{};
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int m = 0; m < DC; ++m) {
+                        double val[VN];
+                        if constexpr (VEC) Vec16<T>::unpack(raw[u][m], val);
+                        else val[0] = (double)raw[u][m];
+#pragma unroll
+                        for (int v = 0; v < VN; ++v) acc[m][v] += val[v];
+                    }
+            }
+            p = e;
+            if constexpr (SUB > 1) {
+#pragma unroll
+                for (int o = L; o < 32; o <<= 1)
+#pragma unroll
+                    for (int v = 0; v < VN; ++v) acc[0][v] += __shfl_xor_sync(0xffffffffu, acc[0][v], o);
+            }
+            // objective of the piece, the way Java's distance is put together:
+            //   EUCL  sum ||x||^2 - 2 c.S + n ||c||^2  (||x||^2 = the stored label, S = the sums just formed)
+            //   COS   n - c.S
+            if (METRIC == AKM_EUCLIDEAN && blockIdx.y == 0) {
+                double xs = 0.0;
+                for (int q = s + lane; q < e; q += 32) xs += xlabel[base + sorted[q]];
+                obj += xs;
+                if (lane == 0) obj += (double)(e - s) * clabel[j];
+            }
+            double *out = sum + (size_t)j * (d + 1);
+            if (sub == 0) {
+                double cen[DC][VN];                   // only needed here: keeps the row loop's registers free
+#pragma unroll
+                for (int m = 0; m < DC; ++m)
+#pragma unroll
+                    for (int v = 0; v < VN; ++v) {
+                        const int col = cb0 + (cl + L * m) * VN + v;
+                        cen[m][v] = (col < d) ? C[(size_t)j * d + col] : 0.0;
+                    }
+#pragma unroll
+                for (int m = 0; m < DC; ++m)
+#pragma unroll
+                    for (int v = 0; v < VN; ++v) {
+                        const int col = cb0 + (cl + L * m) * VN + v;
+                        if (col < d) {
+                            atomicAdd(out + col, acc[m][v]);
+                            if (METRIC == AKM_EUCLIDEAN) obj -= 2.0 * cen[m][v] * acc[m][v];
+                            else obj -= cen[m][v] * acc[m][v];
+                        }
+                    }
+            }
+            if (lane == 0 && blockIdx.y == 0) {
+                atomicAdd(out + d, (double)(e - s));
+                if (METRIC == AKM_COSINE) obj += (double)(e - s);
+            }
+            if (p < p1) { ++j; while (off[j + 1] <= p) ++j; }     // next non-empty cluster
         }
     }
     if (objective != nullptr) {
@@ -561,7 +606,7 @@ static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_
     int64_t chunk = ceil_div64(n, (int64_t)h->num_sms * 6);
     chunk = ((chunk + 1023) / 1024) * 1024;
     const int64_t cap3 = (int64_t)(((size_t)(h->smem_optin + 1024) / 3 - 4096 - fixed) / 2);
-    int64_t chunk_max = std::min<int64_t>(16384, std::max<int64_t>(2048, (cap3 / 1024) * 1024));
+    int64_t chunk_max = std::min<int64_t>(32768, std::max<int64_t>(2048, (cap3 / 1024) * 1024));   // = the regroup window
     if (env_chunk > 0) chunk_max = env_chunk;
     if (chunk > chunk_max) chunk = chunk_max;
     if (chunk > ACC_MAX_CHUNK) chunk = ACC_MAX_CHUNK;
@@ -574,31 +619,38 @@ static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_
     const int groups = vec ? (d / VN + 31) / 32 : (d + 31) / 32;       // 32-lane column groups needed
     const int maxdc = vec ? (VN == 4 ? 2 : 4) : 8;                      // register budget: DC*VN <= 8
     const int DCsel = groups >= maxdc ? maxdc : groups;
-    const int cols_per_pass = DCsel * 32 * (vec ? VN : 1);
+    // narrow rows: several rows per warp-wide load
+    const int subsel = (vec && d / VN <= 8) ? 4 : ((vec && d / VN <= 16) ? 2 : 1);
+    const int cols_per_pass = DCsel * (32 / subsel) * (vec ? VN : 1);
     const dim3 grid((unsigned)ceil_div64(n, chunk), (unsigned)((d + cols_per_pass - 1) / cols_per_pass));
-#define ACC_CASE(DCV, VECV)                                                                                    \
+    // items: about four per warp, a multiple of the unrolled row step, at least 48 rows
+    int item = (int)((chunk + 31) / 32);
+    item = std::max(48, ((item + 47) / 48) * 48);
+#define ACC_CASE(DCV, VECV, SUBV)                                                                              \
     {                                                                                                          \
-        auto kern = accumulate_kernel<T, DCV, METRIC, VECV>;                                                   \
+        auto kern = accumulate_kernel<T, DCV, METRIC, VECV, SUBV>;                                             \
         AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
-        kern<<<grid, ACC_THREADS, smem, h->stream>>>(X, labels, n, d, k0, (int)chunk, C, sum, objective, xlabel, clabel); \
+        kern<<<grid, ACC_THREADS, smem, h->stream>>>(X, labels, n, d, k0, (int)chunk, item, C, sum, objective, xlabel, clabel); \
     }
     if (vec) {
-        switch (DCsel) {
-            case 1: ACC_CASE(1, true) break;
-            case 2: ACC_CASE(2, true) break;
-            case 3: ACC_CASE(3, true) break;
-            default: ACC_CASE(4, true) break;
+        if (subsel == 4) ACC_CASE(1, true, 4)
+        else if (subsel == 2) ACC_CASE(1, true, 2)
+        else switch (DCsel) {
+            case 1: ACC_CASE(1, true, 1) break;
+            case 2: ACC_CASE(2, true, 1) break;
+            case 3: ACC_CASE(3, true, 1) break;
+            default: ACC_CASE(4, true, 1) break;
         }
     } else {
         switch (DCsel) {
-            case 1: ACC_CASE(1, false) break;
-            case 2: ACC_CASE(2, false) break;
-            case 3: ACC_CASE(3, false) break;
-            case 4: ACC_CASE(4, false) break;
-            case 5: ACC_CASE(5, false) break;
-            case 6: ACC_CASE(6, false) break;
-            case 7: ACC_CASE(7, false) break;
-            default: ACC_CASE(8, false) break;
+            case 1: ACC_CASE(1, false, 1) break;
+            case 2: ACC_CASE(2, false, 1) break;
+            case 3: ACC_CASE(3, false, 1) break;
+            case 4: ACC_CASE(4, false, 1) break;
+            case 5: ACC_CASE(5, false, 1) break;
+            case 6: ACC_CASE(6, false, 1) break;
+            case 7: ACC_CASE(7, false, 1) break;
+            default: ACC_CASE(8, false, 1) break;
         }
     }
 #undef ACC_CASE

@@ -3,11 +3,14 @@ import sys, os
 import numpy as np
 sys.path.insert(0, '.')
 from alink_b200 import native
+if os.environ.get("AKM_LIB"):
+    native.LIB_PATH = os.environ["AKM_LIB"]          # A/B against another build of the library
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 20_000_000
-d = 128
+d = int(sys.argv[4]) if len(sys.argv) > 4 else 128
+metric = native.COSINE if (len(sys.argv) > 5 and sys.argv[5] == "cosine") else native.EUCLIDEAN
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 k = int(sys.argv[3]) if len(sys.argv) > 3 else 1000
-h = native.Handle(d, native.EUCLIDEAN)
+h = native.Handle(d, metric)
 h.reserve_rows(N)
 h.blobs_append(20260101, k, 0, N)
 C0 = h.blobs_rows(20260101, k, (np.arange(k, dtype=np.int64) * N) // k).astype(np.float64)
