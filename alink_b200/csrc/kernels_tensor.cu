@@ -1062,8 +1062,11 @@ c16_rows_kernel(const double *__restrict__ C, const double *__restrict__ clabel,
 // kernel is all about memory behaviour.  A thread streams its own sample row and its candidates' centroid
 // rows 16-32 bytes at a time; neighbouring entries come from neighbouring rows of a cluster-ordered
 // partition, so they share candidates and the centroid rows are L1 hits for the rest of the warp.
+#ifndef RF_MINB
+#define RF_MINB 6            // 72 registers: the kernel is latency-bound, resident warps matter more than spill-free wide entries
+#endif
 template <typename T, int METRIC>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, RF_MINB)
 refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int d,
                          const double *__restrict__ C, const double *__restrict__ clabel, int k,
                          const int32_t *__restrict__ wl_rows, const int32_t *__restrict__ wl_cand,
