@@ -357,6 +357,7 @@ int akm_destroy(akm_handle h) {
     dev_free(h->labels); dev_free(h->mind);
     for (int i = 0; i < 2; ++i) { dev_free(h->cent[i]); dev_free(h->clabel[i]); }
     dev_free(h->sum); dev_free(h->cmap); dev_free(h->inv); dev_free(h->shift); dev_free(h->dscal); dev_free(h->iscal);
+    dev_free(h->init_cost); dev_free(h->init_near); dev_free(h->init_rows); dev_free(h->init_out);
     if (h->h_dscal) cudaFreeHost(h->h_dscal);
     if (h->h_iscal) cudaFreeHost(h->h_iscal);
     if (h->stage) cudaFree(h->stage);
@@ -417,6 +418,8 @@ int akm_clear_rows(akm_handle h) {
     rowstore_free(h->rows);
     h->rows.store = (h->metric == AKM_COSINE) ? 8 : 4;
     tensor_invalidate_seeds(h);
+    dev_free(h->init_cost); dev_free(h->init_near);
+    h->init_cap = 0;
     return AKM_OK;
 }
 
@@ -669,6 +672,130 @@ int akm_predict_cached(akm_handle h, const double *centroids, int k, int64_t *id
     AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centroids, sizeof(double) * (size_t)k * h->d, cudaMemcpyHostToDevice, h->stream));
     AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k, true));
     return predict_store(h, h->rows, s->c[0], s->l[0], k, idx_out, dist_out, nullptr);
+}
+
+// ---------------------------------------------------------------- initial centroids (KMeansInitCentroids)
+static int ensure_init(akm_handle h) {
+    const int64_t n = std::max<int64_t>(h->rows.n, 1);
+    if (h->init_cap >= n && h->init_cost) return AKM_OK;
+    dev_free(h->init_cost); dev_free(h->init_near);
+    h->init_cap = 0;
+    AKM_TRY(dev_alloc(h, &h->init_cost, (size_t)n));
+    AKM_TRY(dev_alloc(h, &h->init_near, (size_t)n));
+    h->init_cap = n;
+    return launch_init_reset(h, h->rows.n, h->init_cost, h->init_near);
+}
+
+static int ensure_init_lists(akm_handle h, int m, size_t out_count) {
+    if (h->init_rows_cap < m) {
+        dev_free(h->init_rows);
+        h->init_rows_cap = 0;
+        AKM_TRY(dev_alloc(h, &h->init_rows, (size_t)std::max(m, 1)));
+        h->init_rows_cap = std::max(m, 1);
+    }
+    if (h->init_out_count < out_count) {
+        dev_free(h->init_out);
+        h->init_out_count = 0;
+        AKM_TRY(dev_alloc(h, &h->init_out, std::max<size_t>(out_count, 1)));
+        h->init_out_count = std::max<size_t>(out_count, 1);
+    }
+    return AKM_OK;
+}
+
+int akm_init_reset(akm_handle h) {
+    AKM_TRY(bind_device(h));
+    if (h->init_cap >= std::max<int64_t>(h->rows.n, 1) && h->init_cost)
+        return launch_init_reset(h, h->rows.n, h->init_cost, h->init_near);
+    return ensure_init(h);
+}
+
+int akm_init_update(akm_handle h, const double *centers, int m, int id_base, double *sum_cost_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, centers && m > 0 && id_base >= 0 && sum_cost_out, "centers / sum_cost_out missing");
+    AKM_TRY(ensure_init(h));
+    AKM_TRY(ensure_scratch(h, m));
+    Scratch *s = scratch_of(h);
+    const int64_t n = h->rows.n;
+    AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centers, sizeof(double) * (size_t)m * h->d, cudaMemcpyHostToDevice, h->stream));
+    // the centres are rows of the prepared partition: labels only, no second normalisation
+    AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], m, /*cos_normalise=*/false));
+    if (n > 0) {
+        tensor_invalidate_seeds(h);
+        AKM_TRY(ensure_labels(h, n));
+        AKM_TRY(ensure_mind(h, n));
+        AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], m, m, h->labels, h->mind));
+    }
+    AKM_TRY(launch_init_merge(h, n, h->labels, h->mind, id_base, h->init_cost, h->init_near, h->dscal));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->dscal, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    absorb_tensor_stats(h);
+    AKM_TRY(check_error_flag(h));
+    *sum_cost_out = h->h_dscal[0];
+    return AKM_OK;
+}
+
+int akm_init_pick(akm_handle h, double scale, uint64_t seed, int round, int64_t row_base, int cap, int64_t *rows_out,
+                  int *count_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, cap > 0 && rows_out && count_out, "rows_out / count_out missing");
+    AKM_TRY(ensure_init(h));
+    AKM_TRY(ensure_init_lists(h, cap, 0));
+    AKM_TRY(launch_init_pick(h, h->rows, h->init_cost, h->init_near, row_base, scale, seed, round, cap, h->init_rows, h->iscal));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    const int got = h->h_iscal[0];
+    *count_out = got;                                    // may exceed cap: the caller sees that the list was cut
+    const int take = std::min(got, cap);
+    if (take > 0) {
+        AKM_CUDA(h, cudaMemcpyAsync(rows_out, h->init_rows, sizeof(int64_t) * (size_t)take, cudaMemcpyDeviceToHost, h->stream));
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+        std::sort(rows_out, rows_out + take);            // the order atomics produced is not reproducible
+    }
+    return AKM_OK;
+}
+
+static int upload_row_list(akm_handle h, const int64_t *rows_sorted, int m, size_t out_count) {
+    for (int i = 0; i < m; ++i) {
+        if (rows_sorted[i] < 0 || rows_sorted[i] >= h->rows.n || (i > 0 && rows_sorted[i] <= rows_sorted[i - 1]))
+            return akm_fail(h, AKM_ERR_BADARG, "row indices must be strictly increasing and inside the partition");
+    }
+    AKM_TRY(ensure_init_lists(h, m, out_count));
+    AKM_CUDA(h, cudaMemcpyAsync(h->init_rows, rows_sorted, sizeof(int64_t) * (size_t)m, cudaMemcpyHostToDevice, h->stream));
+    return AKM_OK;
+}
+
+int akm_init_mark(akm_handle h, const int64_t *rows_sorted, int m) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, m >= 0 && (m == 0 || rows_sorted), "rows missing");
+    if (m == 0) return AKM_OK;
+    AKM_TRY(ensure_init(h));
+    AKM_TRY(upload_row_list(h, rows_sorted, m, 0));
+    AKM_TRY(launch_init_mark(h, h->rows, h->init_rows, m, h->init_cost, h->init_near));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AKM_OK;
+}
+
+int akm_init_counts(akm_handle h, int m_total, double *counts_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, m_total > 0 && counts_out, "counts_out missing");
+    AKM_TRY(ensure_init(h));
+    AKM_TRY(ensure_init_lists(h, 1, (size_t)m_total));
+    AKM_TRY(launch_init_counts(h, h->rows.n, h->init_near, m_total, h->init_out));
+    AKM_CUDA(h, cudaMemcpyAsync(counts_out, h->init_out, sizeof(double) * (size_t)m_total, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AKM_OK;
+}
+
+int akm_get_rows(akm_handle h, const int64_t *rows_sorted, int m, double *out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, m >= 0 && (m == 0 || (rows_sorted && out)), "rows / out missing");
+    if (m == 0) return AKM_OK;
+    AKM_TRY(upload_row_list(h, rows_sorted, m, (size_t)m * h->d));
+    AKM_TRY(launch_gather_rows(h, h->rows, h->init_rows, m, h->init_out));
+    AKM_CUDA(h, cudaMemcpyAsync(out, h->init_out, sizeof(double) * (size_t)m * h->d, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AKM_OK;
 }
 
 int akm_get_stats(akm_handle h, akm_stats *out) {

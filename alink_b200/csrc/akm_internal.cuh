@@ -71,6 +71,11 @@ struct akm_handle_s {
     // NCCL
     void *comm = nullptr; int rank = 0, world = 1;
 
+    // k-means|| seeding state of the cached partition (init.cu): nearest chosen centre and the distance to it
+    double *init_cost = nullptr; int32_t *init_near = nullptr; int64_t init_cap = 0;
+    int64_t *init_rows = nullptr; int init_rows_cap = 0;      // device list of row indices (picks / gathers)
+    double *init_out = nullptr; size_t init_out_count = 0;    // gathered rows / counts
+
     // cluster-ordered layout scratch and policy state (reorder.cu)
     void *reorder_scratch = nullptr; size_t reorder_scratch_bytes = 0;
     int32_t *reorder_dest = nullptr; int64_t reorder_dest_cap = 0;
@@ -154,6 +159,16 @@ int copy_rows_out_i32(akm_handle h, const RowStore &rs, const int32_t *dev, int3
 int copy_rows_out_i64(akm_handle h, const RowStore &rs, const int64_t *dev, int64_t *host, int64_t n);
 int copy_rows_out_f64(akm_handle h, const RowStore &rs, const double *dev, double *host, int64_t n);
 float *tensor_useed(akm_handle h);   // kernels_tensor.cu: per-row seeds of the cached partition (may be null)
+
+// ---------------------------------------------------------------- init.cu
+int launch_init_reset(akm_handle h, int64_t n, double *cost, int32_t *near);
+int launch_init_merge(akm_handle h, int64_t n, const int32_t *labels, const double *mind, int id_base, double *cost,
+                      int32_t *near, double *sum_dev);
+int launch_init_pick(akm_handle h, const RowStore &rs, double *cost, int32_t *near, int64_t row_base, double scale,
+                     uint64_t seed, int round, int cap, int64_t *out_rows_dev, int *out_count_dev);
+int launch_init_mark(akm_handle h, const RowStore &rs, const int64_t *rows_sorted_dev, int m, double *cost, int32_t *near);
+int launch_gather_rows(akm_handle h, const RowStore &rs, const int64_t *rows_sorted_dev, int m, double *out_dev);
+int launch_init_counts(akm_handle h, int64_t n, const int32_t *near, int m, double *counts_dev);
 
 // ---------------------------------------------------------------- blobs.cu
 int launch_blobs(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, const int64_t *rows_dev,

@@ -37,6 +37,12 @@ class TorchDistributed:
     # arrival-order sum of AllReduce.java:307-316)
     allreduce = all_sum
 
+    def gather(self, obj):
+        """[obj of rank 0, obj of rank 1, ...] on every rank."""
+        out = [None] * self.world
+        self.dist.all_gather_object(out, obj)
+        return out
+
     def shard(self, total):
         return shard_bounds(self.rank, self.world, total)
 

@@ -13,6 +13,7 @@ import numpy as np
 
 from . import model as model_io
 from . import native
+from . import init as init_mod
 from .javafmt import java_vector_to_string
 from .vector import rows_to_matrix
 
@@ -180,33 +181,33 @@ class KMeansTrainBatchOp(_TrainParams):
             if X.shape[1] != d:
                 X = np.pad(X, ((0, 0), (0, d - X.shape[1])))
         metric = _DIST[self.get("distanceType")]
-        C0 = self._initial_centroids(X, d, dist)
         with native.Handle(d, metric, device=self.device) as h:
             h.set_engine(self.engine)
             h.upload_rows(X)
             if dist is not None:
                 dist.attach(h)
+            init_info = {}
+            C0 = self._initial_centroids(h, d, metric, dist, init_info)
             m = h.train(C0, max_iter=self.get("maxIter"), tol=self.get("epsilon"))
-            self.train_info = dict(iters=m["iters"], objective=m["objective"], stats=h.stats())
+            self.train_info = dict(iters=m["iters"], objective=m["objective"], stats=h.stats(), init=init_info)
         k = m["k"]
         self.model_rows = model_io.save_model(m["C"][:k], m["weights"][:k], k, d, self.get("distanceType"), vec_col)
         return self
 
-    def _initial_centroids(self, X, d, dist):
+    def _initial_centroids(self, h, d, metric, dist, info):
+        """KMeansInitCentroids.initKmeansCentroids (:40-66) over the rows cached in `h` (alink_b200/init.py)."""
         C0 = self.get("initCentroids")
         if C0 is not None:
             C0 = np.asarray(C0, dtype=np.float64)
             if C0.ndim != 2 or C0.shape[1] != d:
                 raise ValueError("initCentroids must be k x %d" % d)
+            info["mode"] = "given"
             return C0
-        # RANDOM: k distinct rows (KMeansInitCentroids.java:69-87 samples with Flink's sampleWithSize; the exact
-        # sample is not reproducible outside Flink).  K_MEANS_PARALLEL currently falls back to the same sampler.
-        k = self.get("k")
-        rng = np.random.default_rng(self.get("randomSeed"))
-        if dist is None:
-            pick = rng.choice(X.shape[0], size=min(k, X.shape[0]), replace=False)
-            return X[np.sort(pick)].copy()
-        return dist.sample_rows(X, k, rng)
+        k, seed, mode = self.get("k"), self.get("randomSeed"), self.get("initMode")
+        info["mode"] = mode
+        if mode == "RANDOM":
+            return init_mod.random_init(h, k, seed, dist)
+        return init_mod.kmeans_parallel_init(h, k, self.get("initSteps"), seed, metric, dist, info)
 
     def getOutputTable(self):
         return Table(self.model_rows, ["model_id", "model_info"])

@@ -85,6 +85,13 @@ def lib():
         L.akm_get_stats.argtypes = [_H, ctypes.POINTER(Stats)]
         L.akm_time_kernel.argtypes = [_H, ctypes.c_char_p, ctypes.c_int, _c_dp]
         L.akm_set_option.argtypes = [_H, ctypes.c_char_p, ctypes.c_double]
+        L.akm_init_reset.argtypes = [_H]
+        L.akm_init_mark.argtypes = [_H, _c_lp, ctypes.c_int]
+        L.akm_init_update.argtypes = [_H, _c_dp, ctypes.c_int, ctypes.c_int, _c_dp]
+        L.akm_init_pick.argtypes = [_H, ctypes.c_double, ctypes.c_uint64, ctypes.c_int, ctypes.c_int64, ctypes.c_int, _c_lp,
+                                    ctypes.POINTER(ctypes.c_int)]
+        L.akm_init_counts.argtypes = [_H, ctypes.c_int, _c_dp]
+        L.akm_get_rows.argtypes = [_H, _c_lp, ctypes.c_int, _c_dp]
         L.akm_set_profiling.argtypes = [_H, ctypes.c_int]
         L.akm_get_profile.argtypes = [_H, _c_dp, ctypes.c_int]
         L.akm_blobs_append.argtypes = [_H, ctypes.c_uint64, ctypes.c_int, ctypes.c_double, ctypes.c_double,
@@ -298,6 +305,41 @@ class Handle:
     # ---- synthetic benchmark data
     def blobs_append(self, seed, k_true, row0, n, spread=10.0, sigma=1.0):
         self._ck(lib().akm_blobs_append(self._h, int(seed), int(k_true), float(spread), float(sigma), int(row0), int(n)))
+
+    # ---- initial centroids (KMeansInitCentroids.java:89-165), see include/akm.h
+    def init_reset(self):
+        self._ck(lib().akm_init_reset(self._h))
+
+    def init_mark(self, rows_sorted):
+        rows = np.ascontiguousarray(rows_sorted, dtype=np.int64)
+        self._ck(lib().akm_init_mark(self._h, rows.ctypes.data_as(_c_lp), rows.size))
+
+    def init_update(self, centers, id_base):
+        C = np.ascontiguousarray(centers, dtype=np.float64)
+        out = np.zeros(1, dtype=np.float64)
+        self._ck(lib().akm_init_update(self._h, C.ctypes.data_as(_c_dp), C.shape[0], int(id_base), out.ctypes.data_as(_c_dp)))
+        return float(out[0])
+
+    def init_pick(self, scale, seed, round_no, row_base, cap):
+        rows = np.empty(max(int(cap), 1), dtype=np.int64)
+        cnt = ctypes.c_int(0)
+        self._ck(lib().akm_init_pick(self._h, float(scale), int(seed) & 0xFFFFFFFFFFFFFFFF, int(round_no), int(row_base),
+                                     rows.size, rows.ctypes.data_as(_c_lp), ctypes.byref(cnt)))
+        if cnt.value > rows.size:
+            raise RuntimeError("k-means|| picked %d rows, more than the %d the caller allowed for" % (cnt.value, rows.size))
+        return rows[:cnt.value].copy()
+
+    def init_counts(self, m_total):
+        out = np.zeros(int(m_total), dtype=np.float64)
+        self._ck(lib().akm_init_counts(self._h, int(m_total), out.ctypes.data_as(_c_dp)))
+        return out
+
+    def get_rows(self, rows_sorted):
+        rows = np.ascontiguousarray(rows_sorted, dtype=np.int64)
+        out = np.zeros((rows.size, self.d), dtype=np.float64)
+        if rows.size:
+            self._ck(lib().akm_get_rows(self._h, rows.ctypes.data_as(_c_lp), rows.size, out.ctypes.data_as(_c_dp)))
+        return out
 
     def blobs_rows(self, seed, k_true, rows, spread=10.0, sigma=1.0):
         rows = np.ascontiguousarray(rows, dtype=np.int64)
