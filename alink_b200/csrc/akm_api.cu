@@ -741,7 +741,7 @@ int akm_init_pick(akm_handle h, double scale, uint64_t seed, int round, int64_t 
     REQUIRE(h, cap > 0 && rows_out && count_out, "rows_out / count_out missing");
     AKM_TRY(ensure_init(h));
     AKM_TRY(ensure_init_lists(h, cap, 0));
-    AKM_TRY(launch_init_pick(h, h->rows, h->init_cost, h->init_near, row_base, scale, seed, round, cap, h->init_rows, h->iscal));
+    AKM_TRY(launch_init_pick(h, h->rows, h->init_cost, row_base, scale, seed, round, cap, h->init_rows, h->iscal));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     const int got = h->h_iscal[0];
@@ -765,17 +765,6 @@ static int upload_row_list(akm_handle h, const int64_t *rows_sorted, int m, size
     return AKM_OK;
 }
 
-int akm_init_mark(akm_handle h, const int64_t *rows_sorted, int m) {
-    AKM_TRY(bind_device(h));
-    REQUIRE(h, m >= 0 && (m == 0 || rows_sorted), "rows missing");
-    if (m == 0) return AKM_OK;
-    AKM_TRY(ensure_init(h));
-    AKM_TRY(upload_row_list(h, rows_sorted, m, 0));
-    AKM_TRY(launch_init_mark(h, h->rows, h->init_rows, m, h->init_cost, h->init_near));
-    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
-    return AKM_OK;
-}
-
 int akm_init_counts(akm_handle h, int m_total, double *counts_out) {
     AKM_TRY(bind_device(h));
     REQUIRE(h, m_total > 0 && counts_out, "counts_out missing");
@@ -795,6 +784,70 @@ int akm_get_rows(akm_handle h, const int64_t *rows_sorted, int m, double *out) {
     AKM_TRY(launch_gather_rows(h, h->rows, h->init_rows, m, h->init_out));
     AKM_CUDA(h, cudaMemcpyAsync(out, h->init_out, sizeof(double) * (size_t)m * h->d, cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AKM_OK;
+}
+
+// ---------------------------------------------------------------- cluster evaluation (EvalClusterBatchOp)
+int akm_eval_clusters(akm_handle h, const int32_t *labels, int k, double *count_out, double *mean_out,
+                      double *dist_sum_out, double *dist_sq_sum_out, double *norm_sq_sum_out, double *silhouette_sum_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, k > 0 && count_out && mean_out && dist_sum_out && dist_sq_sum_out && norm_sq_sum_out && silhouette_sum_out,
+            "output buffers missing");
+    const int64_t n = h->rows.n;
+    const int d = h->d;
+    REQUIRE(h, n == 0 || labels, "labels missing");
+    AKM_TRY(ensure_scratch(h, k));
+    Scratch *s = scratch_of(h);
+    const size_t L = (size_t)k * (d + 1);
+    std::vector<double> sums(L, 0.0);
+    if (n > 0) {
+        tensor_invalidate_seeds(h);                      // h->labels is about to hold the caller's cluster ids
+        AKM_TRY(ensure_labels(h, n));
+        AKM_TRY(ensure_init_lists(h, 1, (size_t)(n + 1) / 2 + 1));        // staging for the int32 labels
+        int32_t *stage = reinterpret_cast<int32_t *>(h->init_out);
+        AKM_CUDA(h, cudaMemcpyAsync(stage, labels, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+        AKM_TRY(launch_labels_in(h, h->rows, stage, h->labels));
+        AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], s->l[0], k, s->sum, nullptr));
+        AKM_CUDA(h, cudaMemcpyAsync(sums.data(), s->sum, sizeof(double) * L, cudaMemcpyDeviceToHost, h->stream));
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
+    // mean = sum.scale(1.0 / total)  (ClusterEvaluationUtil.java:204); |mean| for the COSINE distance to the mean
+    std::vector<double> mnorm((size_t)k, 0.0);
+    for (int j = 0; j < k; ++j) {
+        const double c = sums[(size_t)j * (d + 1) + d];
+        count_out[j] = c;
+        const double inv = 1.0 / c;
+        double nn = 0.0;
+        for (int i = 0; i < d; ++i) {
+            const double m = (c > 0.0) ? sums[(size_t)j * (d + 1) + i] * inv : 0.0;
+            mean_out[(size_t)j * d + i] = m;
+            nn += m * m;
+        }
+        mnorm[j] = std::sqrt(nn);
+    }
+    if (n == 0) {
+        for (int j = 0; j < k; ++j) dist_sum_out[j] = dist_sq_sum_out[j] = norm_sq_sum_out[j] = 0.0;
+        *silhouette_sum_out = 0.0;
+        return AKM_OK;
+    }
+    // device copies: means in c[0], |mean| in l[0], counts in l[1]; per-cluster outputs in c[1] (3k doubles, d >= 1)
+    AKM_TRY(ensure_init_lists(h, 1, (size_t)3 * k + 1));
+    double *out3k = h->init_out;
+    AKM_CUDA(h, cudaMemcpyAsync(s->c[0], mean_out, sizeof(double) * (size_t)k * d, cudaMemcpyHostToDevice, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(s->l[0], mnorm.data(), sizeof(double) * (size_t)k, cudaMemcpyHostToDevice, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(s->l[1], count_out, sizeof(double) * (size_t)k, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(launch_eval_own(h, h->rows, h->labels, k, s->c[0], s->l[0], out3k));
+    AKM_TRY(launch_eval_silhouette(h, h->rows, h->labels, k, s->c[0], s->l[1], out3k + 2 * (size_t)k, h->dscal));
+    std::vector<double> host3((size_t)3 * k);
+    AKM_CUDA(h, cudaMemcpyAsync(host3.data(), out3k, sizeof(double) * 3 * (size_t)k, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->dscal, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (int j = 0; j < k; ++j) {
+        dist_sum_out[j] = host3[j];
+        dist_sq_sum_out[j] = host3[(size_t)k + j];
+        norm_sq_sum_out[j] = host3[2 * (size_t)k + j];
+    }
+    *silhouette_sum_out = h->h_dscal[0];
     return AKM_OK;
 }
 

@@ -164,11 +164,17 @@ float *tensor_useed(akm_handle h);   // kernels_tensor.cu: per-row seeds of the 
 int launch_init_reset(akm_handle h, int64_t n, double *cost, int32_t *near);
 int launch_init_merge(akm_handle h, int64_t n, const int32_t *labels, const double *mind, int id_base, double *cost,
                       int32_t *near, double *sum_dev);
-int launch_init_pick(akm_handle h, const RowStore &rs, double *cost, int32_t *near, int64_t row_base, double scale,
+int launch_init_pick(akm_handle h, const RowStore &rs, const double *cost, int64_t row_base, double scale,
                      uint64_t seed, int round, int cap, int64_t *out_rows_dev, int *out_count_dev);
-int launch_init_mark(akm_handle h, const RowStore &rs, const int64_t *rows_sorted_dev, int m, double *cost, int32_t *near);
 int launch_gather_rows(akm_handle h, const RowStore &rs, const int64_t *rows_sorted_dev, int m, double *out_dev);
 int launch_init_counts(akm_handle h, int64_t n, const int32_t *near, int m, double *counts_dev);
+
+// ---------------------------------------------------------------- eval.cu
+int launch_labels_in(akm_handle h, const RowStore &rs, const int32_t *src_dev, int32_t *dst_dev);
+int launch_eval_own(akm_handle h, const RowStore &rs, const int32_t *labels, int k, const double *mean,
+                    const double *mean_norm, double *out3k);
+int launch_eval_silhouette(akm_handle h, const RowStore &rs, const int32_t *labels, int k, const double *mean,
+                           const double *cnt, const double *normsum, double *sil_sum);
 
 // ---------------------------------------------------------------- blobs.cu
 int launch_blobs(akm_handle h, uint64_t seed, int k_true, double spread, double sigma, const int64_t *rows_dev,

@@ -4,15 +4,16 @@
 // There every sample carries a Tuple5 (id, vector, nearestCenterId f2, nearestCenterDist f3, isCenter f4); one
 // round = SUM(f3) over the samples that are not centres, a Bernoulli pick with probability f3 * 2k / SUM
 // (FilterNewCenter :185-206) and a CalWeight map (:221-248) that lowers (f2, f3) against the new centres.
-// Here f2/f3/f4 are two device arrays in the partition's current row order (near == INIT_IS_CENTER encodes f4),
-// CalWeight is the ordinary nearest-centroid pass of the library against the new centres, and the pick uses a
-// counter-based hash of the GLOBAL row index instead of java.util.Random(subtask) so that the result does not
-// depend on how the rows are sharded over GPUs.
+// Centres are COPIES there (TransformToCenter maps the filtered records; `dataOnly` keeps every sample), so a
+// picked row stays a data row: the next CalWeight finds it at distance 0 from its own copy, which both stops it
+// from being picked again and gives every centre a weight of at least one in the final groupBy.
+// Here f2/f3 are two device arrays in the partition's current row order, CalWeight is the ordinary
+// nearest-centroid pass of the library against the new centres, and the pick uses a counter-based hash of the
+// GLOBAL row index instead of java.util.Random(subtask) so that the result does not depend on how the rows are
+// sharded over GPUs.
 #include <cfloat>
 
 #include "akm_internal.cuh"
-
-constexpr int INIT_IS_CENTER = -2;
 
 __global__ void init_reset_kernel(int64_t n, double *__restrict__ cost, int32_t *__restrict__ near) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -20,7 +21,7 @@ __global__ void init_reset_kernel(int64_t n, double *__restrict__ cost, int32_t 
     for (; i < n; i += stride) { cost[i] = DBL_MAX; near[i] = -1; }
 }
 
-// CalWeight: (near, cost) <- min over the new centres; SUM(cost) over the rows that are not centres
+// CalWeight: (near, cost) <- min over the new centres; SUM(cost) over the partition
 __global__ void __launch_bounds__(256)
 init_merge_kernel(int64_t n, const int32_t *__restrict__ labels, const double *__restrict__ mind, int id_base,
                   double *__restrict__ cost, int32_t *__restrict__ near, double *__restrict__ sum_out) {
@@ -29,7 +30,6 @@ init_merge_kernel(int64_t n, const int32_t *__restrict__ labels, const double *_
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < n; i += stride) {
-        if (near[i] == INIT_IS_CENTER) continue;
         double c = cost[i];
         const double dn = mind[i];
         if (labels[i] >= 0 && dn < c) { c = dn; cost[i] = dn; near[i] = id_base + labels[i]; }
@@ -51,21 +51,17 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {      // splitmix64 final
     return z ^ (z >> 31);
 }
 
-// FilterNewCenter: row becomes a centre when u(seed, round, global row) < cost * scale
-__global__ void init_pick_kernel(int64_t n, double *__restrict__ cost, int32_t *__restrict__ near,
-                                 const int32_t *__restrict__ orig, int64_t row_base, double scale, uint64_t seed,
+// FilterNewCenter: a copy of the row becomes a centre when u(seed, round, global row) < cost * scale
+__global__ void init_pick_kernel(int64_t n, const double *__restrict__ cost, const int32_t *__restrict__ orig, int64_t row_base, double scale, uint64_t seed,
                                  int round, int cap, int64_t *__restrict__ out_rows, int *__restrict__ out_count) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < n; i += stride) {
-        if (near[i] == INIT_IS_CENTER) continue;
         const int64_t local = orig ? (int64_t)orig[i] : i;
         const uint64_t g = (uint64_t)(row_base + local);
         const uint64_t hsh = mix64(mix64(seed + 0x9E3779B97F4A7C15ull * (uint64_t)(round + 1)) ^ (g * 0xD1B54A32D192ED03ull));
         const double u = (double)(hsh >> 11) * (1.0 / 9007199254740992.0);      // 53 bits -> [0, 1)
         if (u < cost[i] * scale) {
-            near[i] = INIT_IS_CENTER;
-            cost[i] = DBL_MAX;
             const int pos = atomicAdd(out_count, 1);
             if (pos < cap) out_rows[pos] = local;
         }
@@ -76,16 +72,6 @@ __device__ __forceinline__ int find_sorted(const int64_t *__restrict__ a, int m,
     int lo = 0, hi = m;
     while (lo < hi) { const int mid = (lo + hi) >> 1; if (a[mid] < v) lo = mid + 1; else hi = mid; }
     return (lo < m && a[lo] == v) ? lo : -1;
-}
-
-__global__ void init_mark_kernel(int64_t n, const int32_t *__restrict__ orig, const int64_t *__restrict__ rows_sorted, int m,
-                                 double *__restrict__ cost, int32_t *__restrict__ near) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; i < n; i += stride) {
-        const int64_t local = orig ? (int64_t)orig[i] : i;
-        if (find_sorted(rows_sorted, m, local) >= 0) { near[i] = INIT_IS_CENTER; cost[i] = DBL_MAX; }
-    }
 }
 
 // one warp per stored row: copy it (as double) to out[p] when the caller asked for it
@@ -103,7 +89,7 @@ __global__ void gather_rows_kernel(int64_t n, const T *__restrict__ X, int d, co
     }
 }
 
-// number of non-centre rows whose nearest centre is j (the groupBy/SUM of :140-150)
+// number of rows whose nearest centre is j (the groupBy/SUM of :140-150)
 __global__ void init_counts_kernel(int64_t n, const int32_t *__restrict__ near, int m, double *__restrict__ counts) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -133,20 +119,12 @@ int launch_init_merge(akm_handle h, int64_t n, const int32_t *labels, const doub
     return AKM_OK;
 }
 
-int launch_init_pick(akm_handle h, const RowStore &rs, double *cost, int32_t *near, int64_t row_base, double scale,
+int launch_init_pick(akm_handle h, const RowStore &rs, const double *cost, int64_t row_base, double scale,
                      uint64_t seed, int round, int cap, int64_t *out_rows_dev, int *out_count_dev) {
     AKM_CUDA(h, cudaMemsetAsync(out_count_dev, 0, sizeof(int), h->stream));
     if (rs.n <= 0) return AKM_OK;
-    init_pick_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, cost, near, rs.reordered ? rs.orig : nullptr, row_base, scale,
+    init_pick_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, cost, rs.reordered ? rs.orig : nullptr, row_base, scale,
                                                             seed, round, cap, out_rows_dev, out_count_dev);
-    h->stats.kernel_launches++;
-    AKM_CUDA(h, cudaGetLastError());
-    return AKM_OK;
-}
-
-int launch_init_mark(akm_handle h, const RowStore &rs, const int64_t *rows_sorted_dev, int m, double *cost, int32_t *near) {
-    if (rs.n <= 0 || m <= 0) return AKM_OK;
-    init_mark_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, rs.reordered ? rs.orig : nullptr, rows_sorted_dev, m, cost, near);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     return AKM_OK;

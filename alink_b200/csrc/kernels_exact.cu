@@ -83,7 +83,7 @@ prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, f
         // CosineDistance.updateLabel :60-65: norm = sqrt(dot); if (norm > 0) x *= 1.0 / norm
         const double nrm = sqrt(s);
         inv_s[tid] = (nrm > 0.0) ? (1.0 / nrm) : -1.0;   // -1 == leave untouched
-        if (myrow < n) xlabel[row0 + myrow] = 0.0;
+        if (myrow < n) xlabel[row0 + myrow] = nrm;          // |x_raw|: not a distance label, kept for EvalCluster's silhouette
         __syncthreads();
         for (int c0 = 0; c0 < d; c0 += PREP_COLS) {
 #pragma unroll 8
@@ -526,7 +526,7 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
 #pragma unroll
                     for (int v = 0; v < VN; ++v) {
                         const int col = cb0 + (cl + L * m) * VN + v;
-                        cen[m][v] = (col < d) ? C[(size_t)j * d + col] : 0.0;
+                        cen[m][v] = (col < d && objective != nullptr) ? C[(size_t)j * d + col] : 0.0;
                     }
 #pragma unroll
                 for (int m = 0; m < DC; ++m)

@@ -165,9 +165,7 @@ def kmeans_parallel_init(handle, k, init_steps, seed, metric, dist=None, info=No
     rng = np.random.default_rng(seed)
     first = np.array([int(rng.integers(total))], dtype=np.int64)        # sampleWithSize(.., 1, 0L)  (:108-111)
     handle.init_reset()
-    mine = first[(first >= starts[dist.rank]) & (first < starts[dist.rank + 1])] - row_base
-    handle.init_mark(mine)                                              # TransformToCenter
-    centers = _fetch_global_rows(handle, dist, starts, first)
+    centers = _fetch_global_rows(handle, dist, starts, first)           # TransformToCenter: centres are copies
     sum_cost = float(dist.all_sum(np.array([handle.init_update(centers, 0)]))[0])     # CalWeight + SUM
     for rnd_no in range(1, max(int(init_steps), 1)):                    # iterate(initSteps - 1)  (:119)
         if not (sum_cost > 0.0):
@@ -183,12 +181,10 @@ def kmeans_parallel_init(handle, k, init_steps, seed, metric, dist=None, info=No
         centers = np.vstack([centers, new])
         sum_cost = float(dist.all_sum(np.array([handle.init_update(new, base)]))[0])
     counts = dist.all_sum(handle.init_counts(centers.shape[0]))
-    keep = counts > 0                                                   # inner join with the per-centre counts (:140-150)
-    samples, weights = centers[keep], counts[keep]
+    keep = counts > 0                                                   # inner join with the per-centre counts (:140-150);
+    samples, weights = centers[keep], counts[keep]                      # a centre loses its own row only to an identical earlier one
     if info is not None:
         info.update(candidates=int(centers.shape[0]), kept=int(samples.shape[0]), sum_cost=sum_cost)
-    if samples.shape[0] == 0:                                           # degenerate: all rows are centres
-        return centers[: min(k, centers.shape[0])].copy()
     if samples.shape[0] <= k:                                           # LocalKmeans.mapPartition (:283-285)
         return samples.copy()
     return local_kmeans(k, weights, samples, metric)

@@ -86,12 +86,12 @@ def lib():
         L.akm_time_kernel.argtypes = [_H, ctypes.c_char_p, ctypes.c_int, _c_dp]
         L.akm_set_option.argtypes = [_H, ctypes.c_char_p, ctypes.c_double]
         L.akm_init_reset.argtypes = [_H]
-        L.akm_init_mark.argtypes = [_H, _c_lp, ctypes.c_int]
         L.akm_init_update.argtypes = [_H, _c_dp, ctypes.c_int, ctypes.c_int, _c_dp]
         L.akm_init_pick.argtypes = [_H, ctypes.c_double, ctypes.c_uint64, ctypes.c_int, ctypes.c_int64, ctypes.c_int, _c_lp,
                                     ctypes.POINTER(ctypes.c_int)]
         L.akm_init_counts.argtypes = [_H, ctypes.c_int, _c_dp]
         L.akm_get_rows.argtypes = [_H, _c_lp, ctypes.c_int, _c_dp]
+        L.akm_eval_clusters.argtypes = [_H, _c_ip, ctypes.c_int, _c_dp, _c_dp, _c_dp, _c_dp, _c_dp, _c_dp]
         L.akm_set_profiling.argtypes = [_H, ctypes.c_int]
         L.akm_get_profile.argtypes = [_H, _c_dp, ctypes.c_int]
         L.akm_blobs_append.argtypes = [_H, ctypes.c_uint64, ctypes.c_int, ctypes.c_double, ctypes.c_double,
@@ -310,10 +310,6 @@ class Handle:
     def init_reset(self):
         self._ck(lib().akm_init_reset(self._h))
 
-    def init_mark(self, rows_sorted):
-        rows = np.ascontiguousarray(rows_sorted, dtype=np.int64)
-        self._ck(lib().akm_init_mark(self._h, rows.ctypes.data_as(_c_lp), rows.size))
-
     def init_update(self, centers, id_base):
         C = np.ascontiguousarray(centers, dtype=np.float64)
         out = np.zeros(1, dtype=np.float64)
@@ -340,6 +336,17 @@ class Handle:
         if rows.size:
             self._ck(lib().akm_get_rows(self._h, rows.ctypes.data_as(_c_lp), rows.size, out.ctypes.data_as(_c_dp)))
         return out
+
+    def eval_clusters(self, labels, k):
+        """EvalClusterBatchOp's per-row passes (akm_eval_clusters). Returns dict of per-cluster arrays + silhouette sum."""
+        lab = np.ascontiguousarray(labels, dtype=np.int32)
+        k = int(k)
+        cnt = np.zeros(k); mean = np.zeros((k, self.d)); ds = np.zeros(k); dss = np.zeros(k); ns = np.zeros(k)
+        sil = np.zeros(1)
+        self._ck(lib().akm_eval_clusters(self._h, lab.ctypes.data_as(_c_ip), k, cnt.ctypes.data_as(_c_dp),
+                                         mean.ctypes.data_as(_c_dp), ds.ctypes.data_as(_c_dp), dss.ctypes.data_as(_c_dp),
+                                         ns.ctypes.data_as(_c_dp), sil.ctypes.data_as(_c_dp)))
+        return dict(count=cnt, mean=mean, dist_sum=ds, dist_sq_sum=dss, norm_sq_sum=ns, silhouette_sum=float(sil[0]))
 
     def blobs_rows(self, seed, k_true, rows, spread=10.0, sigma=1.0):
         rows = np.ascontiguousarray(rows, dtype=np.int64)

@@ -239,31 +239,48 @@ int akm_blobs_rows(akm_handle h, uint64_t seed, int k_true, double spread, doubl
 /* ---- Initial centroids on the device --------------------------------------------------------
  * Replaces the distance passes of KMeansInitCentroids.kMeansPlusPlusInit
  * (operator/common/clustering/kmeans/KMeansInitCentroids.java:89-165) over the cached partition.  The library
- * keeps, per cached row, the Tuple5 fields f2 (nearest chosen centre id), f3 (distance to it; the reference
- * uses the distance, not its square) and f4 (row is itself a centre).  Call order, one handle per partition:
- *   akm_init_reset                       after the last upload: f2 = -1, f3 = Double.MAX_VALUE, f4 = false  (:97-105)
- *   akm_init_mark(rows)                  TransformToCenter (:208-219) for rows chosen by the caller (the first centre)
+ * keeps, per cached row, the Tuple5 fields f2 (nearest chosen centre id) and f3 (distance to it; the reference
+ * uses the distance, not its square).  Centres are copies of rows (TransformToCenter :208-219 maps filtered
+ * records); the rows themselves stay samples.  Call order, one handle per partition:
+ *   akm_init_reset                       after the last upload: f2 = -1, f3 = Double.MAX_VALUE  (:97-105)
  *   akm_init_update(centers, m, base)    CalWeight (:221-248) against m new centres whose ids are base..base+m-1,
- *                                        then SUM(f3) over this partition's non-centre rows (:120) -> *sum_cost_out
- *   akm_init_pick(scale, seed, round,..) FilterNewCenter (:185-206): a non-centre row becomes a centre when
- *                                        u < f3 * scale (scale = 2k / all-reduced SUM).  u is a counter-based hash of
+ *                                        then SUM(f3) over this partition (:120) -> *sum_cost_out
+ *   akm_init_pick(scale, seed, round,..) FilterNewCenter (:185-206): a row is picked when u < f3 * scale
+ *                                        (scale = 2k / all-reduced SUM).  u is a counter-based hash of
  *                                        (seed, round, row_base + row index), not java.util.Random(subtask): the
  *                                        pick does not depend on the sharding.  Writes the picked rows' indices
  *                                        (caller's row order, ascending) to rows_out[0..min(*count_out, cap));
- *                                        *count_out > cap means the list was cut (call again with a larger cap
- *                                        is not possible: the rows are already marked; size cap generously).
+ *                                        *count_out > cap means the list was cut: repeat the call with a larger
+ *                                        cap (the call changes no state).
  *   akm_get_rows(rows, m, out)           the prepared vectors (COSINE: normalised) of the given rows, m x d
- *   akm_init_counts(m_total, counts)     number of non-centre rows whose nearest centre is j (:140-150), j < m_total
+ *   akm_init_counts(m_total, counts)     number of rows whose nearest centre is j (:140-150), j < m_total
  * Row indices are positions in upload order, strictly increasing in every list.  The weighted k-means++ /
  * Lloyd on the ~2k candidates (LocalKmeansFunc.java:36-122) is host work in the reference and stays host work
  * (alink_b200/init.py). */
 int akm_init_reset(akm_handle h);
-int akm_init_mark(akm_handle h, const int64_t *rows_sorted, int m);
 int akm_init_update(akm_handle h, const double *centers, int m, int id_base, double *sum_cost_out);
 int akm_init_pick(akm_handle h, double scale, uint64_t seed, int round, int64_t row_base, int cap, int64_t *rows_out,
                   int *count_out);
 int akm_init_counts(akm_handle h, int m_total, double *counts_out);
 int akm_get_rows(akm_handle h, const int64_t *rows_sorted, int m, double *out);
+
+/* ---- Cluster evaluation over the cached partition -------------------------------------------
+ * The per-row work of EvalClusterBatchOp (operator/batch/evaluation/EvalClusterBatchOp.java:84-104):
+ * ClusterEvaluationUtil.getClusterStatistics (operator/common/evaluation/ClusterEvaluationUtil.java:171-218) per
+ * cluster and calSilhouetteCoefficient (:106-145) per row.  `labels` are the predicted cluster ids of the cached
+ * rows in upload order, as dense ints 0..k-1 (negative = row without a prediction: skipped, like a null field).
+ * Outputs, all double, caller-allocated:
+ *   count_out[k]        rows per cluster (0 for ids that never occur; the reference has no such group)
+ *   mean_out[k*d]       sumVector.scale(1.0 / total); COSINE: mean of the normalised vectors
+ *   dist_sum_out[k]     sum of distance.calc(mean, vec) -> compactness = dist_sum / count
+ *   dist_sq_sum_out[k]  sum of the squared distances (SSW = sum over clusters)
+ *   norm_sq_sum_out[k]  vectorNormL2Sum
+ *   silhouette_sum_out  sum over rows of the silhouette value (the op divides by COUNT)
+ * The k x k remainder (SSB, separation, Davies-Bouldin, Calinski-Harabasz: ClusterMetricsSummary.java:109-150)
+ * is cheap host arithmetic on these arrays.  A COSINE handle evaluates with CosineDistance, a EUCLIDEAN one with
+ * EuclideanDistance.  Overwrites the label buffer akm_get_labels reads. */
+int akm_eval_clusters(akm_handle h, const int32_t *labels, int k, double *count_out, double *mean_out,
+                      double *dist_sum_out, double *dist_sq_sum_out, double *norm_sq_sum_out, double *silhouette_sum_out);
 
 /* Centroid update for callers that may not allocate device memory (no counterpart in the reference).
  * Meant for hosts that share a GPU under a fixed memory reservation or run on a latency-critical thread:

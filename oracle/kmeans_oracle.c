@@ -378,3 +378,126 @@ int orc_predict(int metric, const double *X, int64_t n, int d, const double *C,
     free(Cm); free(cl); free(x); free(dm);
     return rc;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * EvalClusterBatchOp, vector part.  Follows, without copying:
+ *   ClusterEvaluationUtil.getClusterStatistics  operator/common/evaluation/ClusterEvaluationUtil.java:171-218
+ *   ClusterMetricsSummary.toMetrics              operator/common/evaluation/ClusterMetricsSummary.java:109-150
+ *   ClusterEvaluationUtil.calSilhouetteCoefficient                                             :106-145
+ *   EuclideanDistance.calc(Vector,Vector) :45-47, CosineDistance.calc(Vector,Vector) :46-50
+ * labels are dense cluster ids 0..k-1 (< 0: row skipped); clusters are visited in id order (Flink's group
+ * order is unspecified; every aggregate below except the floating-point summation order is order-free).
+ * out[0..8] = ssb, ssw, compactness, separation, daviesBouldin, calinskiHarabaz, silhouette, k (non-empty), count
+ * ------------------------------------------------------------------------------------------------ */
+static double eval_dist(int metric, const double *a, const double *b, int d) {
+    if (metric == ORC_EUCLIDEAN) {
+        double s = 0.0;
+        for (int i = 0; i < d; ++i) { double df = a[i] - b[i]; s += df * df; }
+        return sqrt(s);
+    }
+    double dot = orc_dot(a, b, d);
+    double cross = sqrt(orc_dot(a, a, d)) * sqrt(orc_dot(b, b, d));
+    return 1.0 - (cross > 0.0 ? dot / cross : 0.0);
+}
+
+int orc_eval_clusters(int metric, const double *X, int64_t n, int d, const int *labels, int k,
+                      double *cnt, double *mean, double *compact, double *dss, double *nsum, double *out) {
+    double *vec = (double *)malloc(sizeof(double) * (size_t)d);
+    double *sumall = (double *)calloc((size_t)d, sizeof(double));
+    if (!vec || !sumall) { free(vec); free(sumall); return -1; }
+    int kk = 0;
+    int64_t total = 0;
+    for (int j = 0; j < k; ++j) {
+        double *m = mean + (size_t)j * d;
+        for (int i = 0; i < d; ++i) m[i] = 0.0;
+        int64_t c = 0;
+        for (int64_t r = 0; r < n; ++r) {
+            if (labels[r] != j) continue;
+            const double *x = X + (size_t)r * d;
+            if (metric == ORC_EUCLIDEAN) {
+                for (int i = 0; i < d; ++i) m[i] += x[i];
+            } else {
+                double s = 1.0 / sqrt(orc_dot(x, x, d));            /* vec.scaleEqual(1.0 / vec.normL2()) */
+                for (int i = 0; i < d; ++i) m[i] += x[i] * s;
+            }
+            ++c;
+        }
+        cnt[j] = (double)c;
+        compact[j] = dss[j] = nsum[j] = 0.0;
+        if (c == 0) continue;
+        double inv = 1.0 / (double)c;
+        for (int i = 0; i < d; ++i) m[i] = m[i] * inv;               /* sumVector.scale(1.0 / total) */
+        double dsum = 0.0;
+        for (int64_t r = 0; r < n; ++r) {
+            if (labels[r] != j) continue;
+            const double *x = X + (size_t)r * d;
+            const double *v = x;
+            if (metric != ORC_EUCLIDEAN) {
+                double s = 1.0 / sqrt(orc_dot(x, x, d));
+                for (int i = 0; i < d; ++i) vec[i] = x[i] * s;
+                v = vec;
+            }
+            double dd = eval_dist(metric, m, v, d);
+            dsum += dd;
+            dss[j] += dd * dd;
+            nsum[j] += orc_dot(v, v, d);
+        }
+        compact[j] = dsum / (double)c;
+        for (int i = 0; i < d; ++i) sumall[i] += m[i] * (double)c;    /* meanVector.scale(clusterCnt), merged */
+        ++kk;
+        total += c;
+    }
+    double ssb = 0.0, ssw = 0.0, comp = 0.0, sep = 0.0;
+    double inv_total = 1.0 / (double)total;
+    for (int i = 0; i < d; ++i) vec[i] = sumall[i] * inv_total;      /* overall mean */
+    double *db = (double *)calloc((size_t)k, sizeof(double));
+    if (!db) { free(vec); free(sumall); return -1; }
+    for (int j = 0; j < k; ++j) {
+        if (cnt[j] == 0.0) continue;
+        double dm = eval_dist(metric, mean + (size_t)j * d, vec, d);
+        ssb += pow(dm, 2) * cnt[j];
+        ssw += dss[j];
+        comp += compact[j];
+    }
+    for (int i = 0; i < k; ++i) {
+        if (cnt[i] == 0.0) continue;
+        for (int j = i + 1; j < k; ++j) {
+            if (cnt[j] == 0.0) continue;
+            double dm = eval_dist(metric, mean + (size_t)i * d, mean + (size_t)j * d, d);
+            sep += dm;
+            double tmp = (compact[i] + compact[j]) / dm;
+            if (tmp > db[i]) db[i] = tmp;
+            if (tmp > db[j]) db[j] = tmp;
+        }
+    }
+    double dbsum = 0.0;
+    for (int j = 0; j < k; ++j) if (cnt[j] != 0.0) dbsum += db[j];
+    /* silhouette */
+    double sil = 0.0;
+    for (int64_t r = 0; r < n; ++r) {
+        int lab = labels[r];
+        if (lab < 0 || lab >= k) continue;
+        const double *x = X + (size_t)r * d;
+        double cur = 0.0, nb = DBL_MAX;
+        double nsq = orc_dot(x, x, d);
+        for (int j = 0; j < k; ++j) {
+            if (cnt[j] == 0.0) continue;
+            double dt = orc_dot(x, mean + (size_t)j * d, d);
+            if (metric == ORC_EUCLIDEAN) {
+                double diss = cnt[j] * nsq - 2.0 * cnt[j] * dt + nsum[j];
+                if (j == lab) { if (cnt[j] > 1.0) cur = diss / (cnt[j] - 1.0); }
+                else { double v = diss / cnt[j]; if (v < nb) nb = v; }
+            } else {
+                double diss = 1.0 - dt;
+                if (j == lab) { if (cnt[j] > 1.0) cur = diss * cnt[j] / (cnt[j] - 1.0); }
+                else if (diss < nb) nb = diss;
+            }
+        }
+        sil += (cur < nb) ? 1.0 - (cur / nb) : (nb / cur) - 1.0;
+    }
+    out[0] = ssb; out[1] = ssw; out[2] = comp / kk; out[3] = 2.0 * sep / ((double)kk * kk - kk);
+    out[4] = dbsum / kk; out[5] = ssb * (double)(total - kk) / ssw / (double)(kk - 1);
+    out[6] = sil / (double)total; out[7] = (double)kk; out[8] = (double)total;
+    free(vec); free(sumall); free(db);
+    return 0;
+}

@@ -196,3 +196,24 @@ def shard(task, par, total):
     """DefaultDistributedInfo.startPos / localRowCnt."""
     L = lib()
     return L.orc_shard_start(task, par, total), L.orc_shard_count(task, par, total)
+
+
+def eval_clusters(metric, X, labels, k):
+    """EvalClusterBatchOp's vector metrics (getClusterStatistics + toMetrics + silhouette) on raw rows.
+    Returns dict(count[k], mean[k,d], compactness[k], dist_sq_sum[k], norm_sq_sum[k], ssb, ssw, compactness_mean,
+    separation, davies_bouldin, calinski_harabaz, silhouette, k, total)."""
+    X = _f64(X)
+    n, d = X.shape
+    lab = np.ascontiguousarray(labels, dtype=np.int32)
+    cnt = np.zeros(k); mean = np.zeros((k, d)); comp = np.zeros(k); dss = np.zeros(k); ns = np.zeros(k)
+    out = np.zeros(9)
+    L = lib()
+    L.orc_eval_clusters.restype = ctypes.c_int
+    rc = L.orc_eval_clusters(ctypes.c_int(metric), _d(X), ctypes.c_int64(n), ctypes.c_int(d),
+                             lab.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), ctypes.c_int(k),
+                             _d(cnt), _d(mean), _d(comp), _d(dss), _d(ns), _d(out))
+    if rc != 0:
+        raise MemoryError("orc_eval_clusters")
+    return dict(count=cnt, mean=mean, compactness=comp, dist_sq_sum=dss, norm_sq_sum=ns, ssb=out[0], ssw=out[1],
+                compactness_mean=out[2], separation=out[3], davies_bouldin=out[4], calinski_harabaz=out[5],
+                silhouette=out[6], k=int(out[7]), total=int(out[8]))

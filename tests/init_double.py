@@ -39,13 +39,6 @@ class InitDouble:
     def init_reset(self):
         self.cost = np.full(self.n, np.finfo(np.float64).max)
         self.near = np.full(self.n, -1, dtype=np.int64)
-        self.center = np.zeros(self.n, dtype=bool)
-
-    def init_mark(self, rows):
-        rows = np.asarray(rows, dtype=np.int64)
-        self.center[rows] = True
-        self.cost[rows] = np.finfo(np.float64).max
-        self.near[rows] = -1
 
     def init_update(self, centers, id_base):
         C = np.ascontiguousarray(centers, dtype=np.float64)
@@ -55,21 +48,19 @@ class InitDouble:
             cl = np.zeros(C.shape[0])
         if self.n:
             _, labels, mind = orc.assign_accumulate(self.metric, self.Xp, self.xl, C, cl)
-            better = (~self.center) & (mind < self.cost)
+            better = mind < self.cost
             self.cost[better] = mind[better]
             self.near[better] = id_base + labels[better]
-        return float(self.cost[~self.center].sum())
+        return float(self.cost.sum())
 
     def init_pick(self, scale, seed, round_no, row_base, cap):
         u = uniform(seed, round_no, row_base + np.arange(self.n, dtype=np.int64))
-        hit = (~self.center) & (u < self.cost * scale)
-        rows = np.nonzero(hit)[0].astype(np.int64)
+        rows = np.nonzero(u < self.cost * scale)[0].astype(np.int64)
         assert rows.size <= cap
-        self.init_mark(rows)
         return rows
 
     def init_counts(self, m_total):
-        ok = (~self.center) & (self.near >= 0)
+        ok = self.near >= 0
         return np.bincount(self.near[ok], minlength=m_total).astype(np.float64)[:m_total]
 
     def get_rows(self, rows):

@@ -33,7 +33,6 @@ def test_seeding_passes_match_the_cpu_restatement(engine, metric):
         h.upload_rows(X)
         h.init_reset()
         first = np.array([1234], dtype=np.int64)
-        h.init_mark(first); ref.init_mark(first)
         c = h.get_rows(first)
         assert (c == ref.get_rows(first)).all()                       # prepared vectors, bit for bit
         s_gpu, s_ref = h.init_update(c, 0), ref.init_update(c, 0)
@@ -50,7 +49,7 @@ def test_seeding_passes_match_the_cpu_restatement(engine, metric):
             assert abs(s_gpu - s_ref) <= 1e-12 * s_ref
             base += p_gpu.size
         assert (h.init_counts(base) == ref.init_counts(base)).all()
-        assert h.init_counts(base).sum() == n - base                  # every non-centre row has a nearest centre
+        assert h.init_counts(base).sum() == n                         # every row has a nearest centre (centres are copies)
 
 
 def test_seeding_survives_the_cluster_ordered_layout():
@@ -65,7 +64,6 @@ def test_seeding_survives_the_cluster_ordered_layout():
         assert (h.get_rows(rows) == X[rows]).all()
         ref = InitDouble(X, orc.EUCLIDEAN)
         h.init_reset()
-        h.init_mark(rows[:1]); ref.init_mark(rows[:1])
         s_gpu, s_ref = h.init_update(X[:1], 0), ref.init_update(X[:1], 0)
         assert abs(s_gpu - s_ref) <= 1e-12 * s_ref
         p_gpu, p_ref = h.init_pick(2.0 * k / s_ref, 5, 1, 0, 1024), ref.init_pick(2.0 * k / s_ref, 5, 1, 0, 1024)
