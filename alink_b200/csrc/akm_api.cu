@@ -364,6 +364,7 @@ int akm_destroy(akm_handle h) {
     if (h->hstage) cudaFreeHost(h->hstage);
     if (h->reorder_scratch) cudaFree(h->reorder_scratch);
     if (h->reorder_dest) cudaFree(h->reorder_dest);
+    if (h->reorder_hist) cudaFree(h->reorder_hist);
     for (int i = 0; i < 5; ++i) if (h->pev[i]) cudaEventDestroy(h->pev[i]);
     if (h->mid_event) cudaEventDestroy(h->mid_event);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);

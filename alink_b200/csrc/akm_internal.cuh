@@ -79,6 +79,7 @@ struct akm_handle_s {
     // cluster-ordered layout scratch and policy state (reorder.cu)
     void *reorder_scratch = nullptr; size_t reorder_scratch_bytes = 0;
     int32_t *reorder_dest = nullptr; int64_t reorder_dest_cap = 0;
+    int *reorder_hist = nullptr; size_t reorder_hist_bytes = 0;
     int64_t changed_since_reorder = 0;
     int reorders = 0;
     double reorder_ms = 0;

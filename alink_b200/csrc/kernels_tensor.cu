@@ -793,10 +793,25 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * PAIR_N + quarter * 64);
+                // columns at or beyond k are padding (score offset PAD_SCORE): a quarter or chunk that holds nothing
+                // else is not read at all -- small k (BASELINE configs 2 and 3) leaves most issue slots free
+                const int live = p.k - (t * PAIR_N + quarter * 64);      // real centroids in this quarter of the tile
+                if (live <= 0) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);
+                    continue;
+                }
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
                     uint32_t v[32];
                     __syncwarp();
+                    if (c == 1 && live <= 32) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);
+                        break;
+                    }
                     tmem_ld32(taddr + c * 32, v);
                     tmem_ld_wait();
                     if (c == 1) {

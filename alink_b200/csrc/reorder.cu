@@ -2,7 +2,7 @@
 //
 // The reference never reorders samples, and nothing it computes depends on their order except the order of
 // the fp64 additions (which the GPU path does not reproduce bit for bit anyway).  Keeping the
-// rows of a partition grouped by their current cluster inside chunks of REORDER_CHUNK rows makes the hot
+// rows of a partition grouped by their current cluster inside waves of a few million rows makes the hot
 // kernels coherent: the 32 rows a warp of the search epilogue owns share their nearest centroids (the rare
 // candidate path stops diverging), neighbouring worklist entries gather the same centroid rows, and the
 // accumulate kernel reads long contiguous runs.  Every per-row array moves together (exact copy, fp16 copy,
@@ -14,43 +14,79 @@
 constexpr int REORDER_CHUNK = 32768;
 constexpr int REORDER_THREADS = 512;
 
-// One CTA per chunk: counting sort of the chunk's rows by label -> dest[row] = new global row index.
+// Counting sort of the rows of one WAVE (as many 32K-row chunks as the scratch buffer holds, ~8M rows) by label:
+//   reorder_hist_kernel    one CTA per chunk: bucket counts of the chunk            -> hist[chunk][bucket]
+//   reorder_scan_kernel    one CTA per wave: exclusive offsets of every (bucket, chunk) pair inside the wave
+//   reorder_scatter_kernel one CTA per chunk: dest[row] = new global row index
+// A cluster's rows end up contiguous inside each wave (thousands of rows per run at the bench shape), in chunk
+// order; the order inside a (chunk, bucket) cell is whatever the atomics produce.
 __global__ void __launch_bounds__(REORDER_THREADS)
-reorder_rank_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int32_t *__restrict__ dest) {
+reorder_hist_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int *__restrict__ hist) {
     extern __shared__ int rk_smem[];
-    int *cursor = rk_smem;   // k + 2 buckets (k = invalid labels)
-    __shared__ int scan_tmp[REORDER_THREADS];
     const int tid = threadIdx.x;
     const int64_t base = (int64_t)blockIdx.x * REORDER_CHUNK;
     const int rows = (int)min((int64_t)REORDER_CHUNK, n - base);
-    const int nb = k + 1;
-    for (int j = tid; j <= nb; j += REORDER_THREADS) cursor[j] = 0;
+    const int nb = k + 1;                                   // bucket k = rows without a valid label
+    for (int j = tid; j < nb; j += REORDER_THREADS) rk_smem[j] = 0;
     __syncthreads();
     for (int r = tid; r < rows; r += REORDER_THREADS) {
         int lab = labels[base + r];
         if (lab < 0 || lab >= k) lab = k;
-        atomicAdd(&cursor[lab], 1);
+        atomicAdd(&rk_smem[lab], 1);
     }
     __syncthreads();
-    const int per = (nb + REORDER_THREADS - 1) / REORDER_THREADS;
+    for (int j = tid; j < nb; j += REORDER_THREADS) hist[(size_t)blockIdx.x * nb + j] = rk_smem[j];
+}
+
+__global__ void __launch_bounds__(1024)
+reorder_scan_kernel(int *__restrict__ hist, int nchunks, int wave_chunks, int k, int *__restrict__ totals) {
+    __shared__ int scan_tmp[1024];
+    const int tid = threadIdx.x;
+    const int nb = k + 1;
+    const int c0 = blockIdx.x * wave_chunks, c1 = min(nchunks, c0 + wave_chunks);
+    int *tot = totals + (size_t)blockIdx.x * nb;
+    for (int b = tid; b < nb; b += 1024) {                  // per bucket: running offset over the wave's chunks
+        int run = 0;
+        for (int c = c0; c < c1; ++c) { const int t = hist[(size_t)c * nb + b]; hist[(size_t)c * nb + b] = run; run += t; }
+        tot[b] = run;
+    }
+    __syncthreads();
+    const int per = (nb + 1023) / 1024;                      // exclusive scan of the bucket totals
     const int lo = min(nb, tid * per), hi = min(nb, lo + per);
     int s = 0;
-    for (int j = lo; j < hi; ++j) s += cursor[j];
+    for (int j = lo; j < hi; ++j) s += tot[j];
     scan_tmp[tid] = s;
     __syncthreads();
-    for (int o = 1; o < REORDER_THREADS; o <<= 1) {
+    for (int o = 1; o < 1024; o <<= 1) {
         const int v = (tid >= o) ? scan_tmp[tid - o] : 0;
         __syncthreads();
         scan_tmp[tid] += v;
         __syncthreads();
     }
     int run = (tid > 0) ? scan_tmp[tid - 1] : 0;
-    for (int j = lo; j < hi; ++j) { const int c = cursor[j]; cursor[j] = run; run += c; }
+    for (int j = lo; j < hi; ++j) { const int c = tot[j]; tot[j] = run; run += c; }
+    __syncthreads();
+    for (int b = tid; b < nb; b += 1024) {
+        const int off = tot[b];
+        for (int c = c0; c < c1; ++c) hist[(size_t)c * nb + b] += off;
+    }
+}
+
+__global__ void __launch_bounds__(REORDER_THREADS)
+reorder_scatter_kernel(const int32_t *__restrict__ labels, int64_t n, int k, const int *__restrict__ hist,
+                       int wave_chunks, int32_t *__restrict__ dest) {
+    extern __shared__ int rk_smem[];
+    const int tid = threadIdx.x;
+    const int64_t base = (int64_t)blockIdx.x * REORDER_CHUNK;
+    const int rows = (int)min((int64_t)REORDER_CHUNK, n - base);
+    const int nb = k + 1;
+    const int64_t wave_row0 = (int64_t)(blockIdx.x / wave_chunks) * wave_chunks * REORDER_CHUNK;
+    for (int j = tid; j < nb; j += REORDER_THREADS) rk_smem[j] = hist[(size_t)blockIdx.x * nb + j];
     __syncthreads();
     for (int r = tid; r < rows; r += REORDER_THREADS) {
         int lab = labels[base + r];
         if (lab < 0 || lab >= k) lab = k;
-        dest[base + r] = (int32_t)(base + atomicAdd(&cursor[lab], 1));
+        dest[base + r] = (int32_t)(wave_row0 + atomicAdd(&rk_smem[lab], 1));
     }
 }
 
@@ -148,9 +184,22 @@ int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *us
         h->reorder_dest_cap = n;
     }
     const size_t smem = (size_t)(k + 3) * sizeof(int);
-    AKM_CUDA(h, cudaFuncSetAttribute(reorder_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    reorder_rank_kernel<<<(unsigned)nchunks, REORDER_THREADS, smem, h->stream>>>(labels, n, k, h->reorder_dest);
-    h->stats.kernel_launches++;
+    const int64_t nwaves = ceil_div64(nchunks, wave_chunks);
+    const size_t hist_bytes = ((size_t)nchunks + (size_t)nwaves) * (size_t)(k + 1) * sizeof(int);
+    if (h->reorder_hist_bytes < hist_bytes) {
+        if (h->reorder_hist) cudaFree(h->reorder_hist);
+        h->reorder_hist = nullptr; h->reorder_hist_bytes = 0;
+        AKM_CUDA(h, cudaMalloc((void **)&h->reorder_hist, hist_bytes));
+        h->reorder_hist_bytes = hist_bytes;
+    }
+    int *hist = h->reorder_hist, *totals = hist + (size_t)nchunks * (k + 1);
+    AKM_CUDA(h, cudaFuncSetAttribute(reorder_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    AKM_CUDA(h, cudaFuncSetAttribute(reorder_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    reorder_hist_kernel<<<(unsigned)nchunks, REORDER_THREADS, smem, h->stream>>>(labels, n, k, hist);
+    reorder_scan_kernel<<<(unsigned)nwaves, 1024, 0, h->stream>>>(hist, (int)nchunks, (int)wave_chunks, k, totals);
+    reorder_scatter_kernel<<<(unsigned)nchunks, REORDER_THREADS, smem, h->stream>>>(labels, n, k, hist, (int)wave_chunks,
+                                                                                  h->reorder_dest);
+    h->stats.kernel_launches += 3;
     AKM_CUDA(h, cudaGetLastError());
     for (int64_t c0 = 0; c0 < nchunks; c0 += wave_chunks) {
         const int64_t row0 = c0 * REORDER_CHUNK;
