@@ -635,6 +635,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
     float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);
     float2 *cand_s = reinterpret_cast<float2 *>(pc_s + 8);                 // [4 quarters][128 rows][MAX_CAND]
     float *xch_s = reinterpret_cast<float *>(cand_s + 4 * TILE_M * MAX_CAND);   // [4 quarters][128 rows][4]
+    int *mstage_s = reinterpret_cast<int *>(xch_s + 4 * TILE_M * 4);            // [128 rows][WL_CAND] merged candidates
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < ns; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
@@ -861,40 +862,44 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             if (quarter == 0) {
                 bool need_exact = false, changed = false;
-                int cand[WL_CAND];
+                // merged candidate list of this row: 8 ints in the exchange area of quarter 0 (unused otherwise) + 4 more
+                int *stage = reinterpret_cast<int *>(mstage_s + (size_t)rt * WL_CAND);
                 if (valid) {
-                    float mF = m;
-                    bool overflow = false;
+                    float xm[4], xd[4];
+                    int xn[4];
+                    xm[0] = m; xd[0] = dropped; xn[0] = ncand;
 #pragma unroll
-                    for (int qq = 1; qq < 4; ++qq) mF = fminf(mF, xch_s[((size_t)qq * TILE_M + rt) * 4 + 0]);
+                    for (int qq = 1; qq < 4; ++qq) {
+                        const float4 x4 = *reinterpret_cast<const float4 *>(xch_s + ((size_t)qq * TILE_M + rt) * 4);
+                        xm[qq] = x4.x; xd[qq] = x4.y; xn[qq] = __float_as_int(x4.z);
+                    }
+                    const float mF = fminf(fminf(xm[0], xm[1]), fminf(xm[2], xm[3]));
                     const float thrF = mF + W;
-                    int cnt = 0, best = -1;
-#pragma unroll
-                    for (int i = 0; i < WL_CAND; ++i) cand[i] = -1;
+                    bool overflow = false;
+                    int cnt = 0, best = -1, first = -1;
+                    *reinterpret_cast<int4 *>(stage) = make_int4(-1, -1, -1, -1);
+                    *reinterpret_cast<int4 *>(stage + 4) = make_int4(-1, -1, -1, -1);
 #pragma unroll
                     for (int qq = 0; qq < 4; ++qq) {
+                        overflow = overflow || !(xd[qq] > thrF);
                         const float2 *ring = cand_s + ((size_t)qq * TILE_M + rt) * MAX_CAND;
-                        const int nc = qq ? __float_as_int(xch_s[((size_t)qq * TILE_M + rt) * 4 + 2]) : ncand;
-                        const float dr = qq ? xch_s[((size_t)qq * TILE_M + rt) * 4 + 1] : dropped;
-                        overflow = overflow || !(dr > thrF);
-#pragma unroll
-                        for (int i = 0; i < MAX_CAND; ++i) {
+                        const int lim = min(xn[qq], MAX_CAND);
+                        for (int i = 0; i < lim; ++i) {           // rings are nearly always empty or hold one entry
                             const float2 cv = ring[i];
-                            if (i < nc && cv.y <= thrF) {
+                            if (cv.y <= thrF) {
                                 const int j = __float_as_int(cv.x);
-#pragma unroll
-                                for (int u = 0; u < WL_CAND; ++u) if (u == cnt) cand[u] = j;
+                                if (cnt < WL_CAND) stage[cnt] = (j < p.k) ? j : -1;
+                                if (cnt == 0) first = j;
                                 if (cv.y == mF) best = j;
                                 ++cnt;
                             }
                         }
                     }
                     overflow = overflow || cnt > WL_CAND;
-                    if (best < 0 && cnt > 0) best = cand[0];
-                    need_exact = overflow || cnt != 1 || best < 0 || best >= p.k;
-#pragma unroll
-                    for (int i = 0; i < WL_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
-                    if (overflow || best < 0 || best >= p.k) cand[0] = -2;
+                    if (best < 0 && cnt > 0) best = first;
+                    const bool all = overflow || best < 0 || best >= p.k;
+                    need_exact = all || cnt != 1;
+                    if (all) stage[0] = -2;
                     if (p.k_prev > 0 && a_old != best) changed = true;
                     p.labels[row] = best;
                     if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
@@ -918,8 +923,8 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                         const int pos = base + __popc(mask & ((1u << lane) - 1));
                         p.wl_rows[pos] = (int32_t)row;
                         int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
-                        dst[0] = make_int4(cand[0], cand[1], cand[2], cand[3]);
-                        dst[1] = make_int4(cand[4], cand[5], cand[6], cand[7]);
+                        dst[0] = *reinterpret_cast<const int4 *>(stage);
+                        dst[1] = *reinterpret_cast<const int4 *>(stage + 4);
                     }
                 }
             }
@@ -1369,7 +1374,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     static const bool pair_off = getenv("AKM_TC_PAIR") && atoi(getenv("AKM_TC_PAIR")) == 0;   // tuning aid
     const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
     const int nt2 = (k + PAIR_N - 1) / PAIR_N;
-    const size_t pair_fixed = (size_t)nt2 * PAIR_N * 4 + 256 + (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 + 1024;
+    const size_t pair_fixed = (size_t)nt2 * PAIR_N * 4 + 256 + (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 + (size_t)TILE_M * WL_CAND * 4 + 1024;
     size_t pair_smem = (size_t)2 * KB * BOX_BYTES + (size_t)nt2 * KB * BOX_BYTES + pair_fixed;
     const bool pair_ok = !pair_off && h->num_sms >= 2 && rs.n > 2 * TILE_M;
     // centroids resident (d <= 128 and they fit) or, for every other shape, both operands streamed in K blocks
