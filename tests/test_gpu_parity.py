@@ -333,3 +333,52 @@ def test_cluster_ordered_layout_is_invisible_to_the_caller(metric):
     Cp, s_ref, l_ref, _, _ = oracle_pass(metric, X, ref["C"], k=ref["k"]) if metric == native.EUCLIDEAN else (None, None, None, None, None)
     if l_ref is not None:
         assert (l2 == l_ref).all()
+
+
+@pytest.mark.parametrize("cfg,n,d,k,metric,need_gb", [
+    ("config2", 1_000_000, 784, 10, native.EUCLIDEAN, 8),
+    ("config3", 10_000_000, 64, 100, native.EUCLIDEAN, 8),
+    ("config4", 100_000_000, 128, 1000, native.EUCLIDEAN, 120),
+    ("config5", 20_000_000, 256, 500, native.COSINE, 70),
+])
+def test_full_size_baseline_configs_tensor_engine_equals_exact_engine(cfg, n, d, k, metric, need_gb):
+    """Every BASELINE.json shape at full size: the certified tensor-core path and the Java-order fp64 engine
+    (itself pinned on the oracle above) must agree on every label, and the usual size-independent invariants
+    must hold.  Rows come from the library's counter-based generator, so nothing is uploaded."""
+    seed = 20260101
+    free, _ = __import__("torch").cuda.mem_get_info()
+    if free < need_gb * (1 << 30):
+        pytest.skip("needs ~%d GB of free HBM" % need_gb)
+    init_rows = (np.arange(k, dtype=np.int64) * n) // k
+    out = {}
+    for name, engine, steps in (("tensor", native.ENGINE_TENSOR, 3), ("exact", native.ENGINE_EXACT, 2)):
+        with native.Handle(d, metric) as h:
+            h.set_engine(engine)
+            h.reserve_rows(n)
+            h.blobs_append(seed, k, 0, n)
+            C0 = h.blobs_rows(seed, k, init_rows).astype(np.float64)
+            h.set_centroids(C0)
+            objs, ks = [], []
+            for _ in range(steps):
+                _, kk, obj = h.step(0.0)
+                objs.append(obj); ks.append(kk)
+                if len(objs) == 2:
+                    labels2 = h.get_labels()
+                    model2 = h.get_model()
+            out[name] = dict(objs=objs, ks=ks, labels=labels2, model=model2)
+            if name == "tensor":
+                # the third pass runs on the cluster-ordered layout with seeded thresholds: invariants only
+                lab3 = h.get_labels()
+                m3 = h.get_model()
+                assert objs[2] <= objs[1] <= objs[0]
+                assert int(m3["weights"].sum()) == n                      # every row counted exactly once
+                assert lab3.min() >= 0 and lab3.max() < ks[1]
+                assert (np.bincount(lab3, minlength=k) == m3["weights"]).all()   # model weights = counts of the last pass
+    t, e = out["tensor"], out["exact"]
+    assert t["ks"][:2] == e["ks"]
+    assert (t["labels"] == e["labels"]).all()
+    for a, b in zip(t["objs"][:2], e["objs"]):
+        assert abs(a - b) <= 1e-9 * abs(b)
+    kk = e["ks"][1]
+    np.testing.assert_allclose(t["model"]["C"][:kk], e["model"]["C"][:kk], rtol=1e-9, atol=1e-12)
+    assert (t["model"]["weights"] == e["model"]["weights"]).all()
