@@ -1,23 +1,23 @@
 // Nearest-centroid search on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), with a
 // rigorous per-row certificate and exact re-evaluation of every row the certificate does not cover.
 //
-//   search_kernel        S[n, j] = ||c_j||^2 - 2 x16_n . c16_j   (EUCLIDEAN)   /   - x16_n . c16_j   (COSINE)
+//   search_pair_kernel   S[n, j] = ||c_j||^2 - 2 x16_n . c16_j   (EUCLIDEAN)   /   - x16_n . c16_j   (COSINE)
 //                        fp16 operands (scaled by powers of two), fp32 accumulation in TMEM, the running
 //                        minimum and the set {j : S[n,j] <= min + W_n} fused in the epilogue.
 //   W_n                  = 2 * (bound on |S - true score|) + 2 * (bound on Java's own fp64 rounding), from
 //                        per-row ||x||, ||x - x16|| and per-pass max ||c||, max ||c - c16|| (Cauchy-Schwarz).
 //                        If exactly one centroid is inside the window, Java's argmin (KMeansUtil.java:162-173)
 //                        is that centroid -- no tie is possible -- and the row is "certified".
-//   refine_candidates    rows with 2..4 candidates: fp64 evaluation of just those centroids; a clear winner
+//   refine_candidates    rows with 2..8 candidates: fp64 evaluation of just those centroids; a clear winner
 //                        (gap above the fp64 error bound of both evaluations) decides the row.
-//   assign_exact (list)  everything else (true ties, > 4 candidates, non-finite data) is evaluated against
+//   assign_exact (list)  everything else (true ties, > 8 candidates, non-finite data) is evaluated against
 //                        all k centroids in the exact Java operation order (kernels_exact.cu).
 // The result is therefore identical to the exact engine by construction; the tensor cores only prune.
 //
-// Data movement: X16 tiles (128 rows x 64 halfs, 128B-swizzled) and centroid tiles arrive by TMA; centroid
-// tiles are multicast across a 2-CTA cluster so each SM pulls half of them from L2.  One CTA keeps
-// MB x 128 rows resident while all centroid tiles stream past; accumulators are double buffered in TMEM
-// so the epilogue of tile t overlaps the MMAs of tile t+1.
+// Data movement: X16 tiles (128 rows x 64 halfs, 128B-swizzled) and centroid tiles arrive by TMA into the shared
+// memory of a CTA PAIR; one thread issues cta_group::2 MMAs (M = 256, N = 256) that read both CTAs' operands, so
+// every centroid half-tile is fetched from L2 once per pair.  Accumulators are double buffered in TMEM so the
+// epilogue of tile t overlaps the MMAs of tile t+1.
 #include <cuda.h>
 #include <cfloat>
 #include <cmath>
@@ -36,9 +36,6 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -59,7 +56,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void cluster_sync_all() {
@@ -71,57 +67,6 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
     return r;
 }
 
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1,
-                                               uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%4, %5}], [%2], %3;"
-        ::"r"(dst), "l"(map), "r"(bar), "h"(mask), "r"(c0), "r"(c1)
-        : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, M = 128, N = 128, K = 16, fp16 x fp16 -> fp32
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// Same MMA with the descriptors passed as 32-bit halves: only the low word (start address) varies per
-// instruction, so the issuing thread spends a single integer add per operand between MMAs.
-__device__ __forceinline__ void umma_f16_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
-                                            uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
-        "setp.ne.b32 p, %5, 0;\n\t"
-        "mov.b64 da, {%1, %3};\n\t"
-        "mov.b64 db, {%2, %3};\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"(mask) : "memory");
-}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -137,24 +82,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major, 128B-swizzled operand tile (rows x 64 halfs, 128 B per row, 8-row atoms of 1024 B):
-// start address >> 4 | LBO = 1 | SBO = 1024 B >> 4 | version 1 (sm_100) | layout SWIZZLE_128B
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
-    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
-// kind::f16: D = F32 (bit 4), A = B = F16 (0), both K-major, N = 128 (>>3 at bit 17), M = 128 (>>4 at bit 24)
-constexpr uint32_t IDESC_F16_128x128 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
-
 }  // namespace
 
 // ------------------------------------------------------------------------------------------ constants
 constexpr int TILE_M = 128;           // rows per MMA (TMEM lanes)
-constexpr int TILE_N = 128;           // centroids per tile (TMEM columns per accumulator)
 constexpr int KBLK = 64;              // halfs per 128-byte swizzled row
 constexpr int BOX_BYTES = TILE_M * KBLK * 2;   // 16 KB
-constexpr int MAX_CAND = 4;            // per column half (ring size)
-constexpr int WL_CAND = 8;             // per worklist entry (both halves)
+constexpr int MAX_CAND = 4;            // per column quarter (ring size)
+constexpr int WL_CAND = 8;             // per worklist entry
 constexpr int WL_BLOCK = 2048;         // worklist slots a warp reserves at a time
-constexpr int MAX_BSLOTS = 16;
 constexpr float PAD_SCORE = 1.0e30f;  // score offset of padding centroids (never candidates)
 
 // per-pass constants produced by c16_rows_kernel
@@ -169,10 +105,9 @@ struct PassConst {
 
 struct SearchParams {
     int64_t n;              // rows
-    int groups;             // row groups of MB*128 rows
-    int ntiles;             // centroid tiles of 128
-    int a_stages, b_slots, resident;
-    int kblocks;            // K-streaming pair kernel: 64-half blocks per row (d16 / 64)
+    int ntiles;             // centroid tiles of 256
+    int a_stages;           // K-streaming kernel: ring stages
+    int kblocks;            // K-streaming kernel: 64-half blocks per row
     int d, metric, k;
     const float *cn;        // ntiles*128 score offsets
     const PassConst *pc;
@@ -187,322 +122,7 @@ struct SearchParams {
     const float *sig_old;   // per OLD label: distance its centroid moved (INF if the cluster was dropped)
     int k_prev;             // 0: no seeds this pass
     const float2 *wm;       // per row {window W, seeded upper bound of the minimum score (INF: none)} from rowprep_kernel
-    int dbg;                // tuning aid: 1 = skip score processing, 2 = also skip the TMEM loads
-    long long *trace;       // tuning aid: clock64 stamps of CTA 0 (nullable)
 };
-
-// ------------------------------------------------------------------------------------------ search kernel
-template <int MB, int KB, int CL>
-__global__ void __launch_bounds__(64 + 256 * MB, 1)
-search_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__ CUtensorMap tmapC,
-              const SearchParams p) {
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // SWIZZLE_128B atoms need 1024-B alignment
-    constexpr int A_STAGE = MB * KB * BOX_BYTES;
-    constexpr int B_STAGE = KB * BOX_BYTES;
-    constexpr int TMEM_COLS = (MB == 2) ? 512 : 256;
-    constexpr int EPI_WARPS = 8 * MB;
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = (CL > 1) ? cluster_ctarank() : 0;
-    const int cluster_id = blockIdx.x / CL, nclusters = gridDim.x / CL;
-
-    unsigned char *a_smem = smem;
-    unsigned char *b_smem = smem + (size_t)p.a_stages * A_STAGE;
-    float *cn_s = reinterpret_cast<float *>(b_smem + (size_t)p.b_slots * B_STAGE);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(cn_s + p.ntiles * TILE_N);
-    uint64_t *a_full = bars, *a_empty = bars + 2, *b_full = bars + 4, *b_empty = b_full + MAX_BSLOTS,
-             *t_full = b_empty + MAX_BSLOTS, *t_empty = t_full + 2;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
-    float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);   // 5 floats (+3 pad)
-    float2 *cand_s = reinterpret_cast<float2 *>(pc_s + 8);     // [2 halves][128*MB rows][MAX_CAND] (index bits, score) + exchange
-
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
-        for (int i = 0; i < MAX_BSLOTS; ++i) { mbar_init(smem_u32(b_full + i), 1); mbar_init(smem_u32(b_empty + i), CL); }
-        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), EPI_WARPS); }
-        fence_barrier_init();
-        pc_s[0] = p.pc->c16_max; pc_s[1] = p.pc->dc_max; pc_s[2] = p.pc->c_max; pc_s[3] = p.pc->score_scale;
-        pc_s[4] = p.pc->bad ? 1.f : 0.f;
-    }
-    for (int i = threadIdx.x; i < p.ntiles * TILE_N; i += blockDim.x) cn_s[i] = p.cn[i];
-    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
-    tc_fence_before();
-    __syncthreads();
-    if (CL > 1) cluster_sync_all();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-
-    // super-groups handled by this cluster: sg = cluster_id, cluster_id + nclusters, ...; this CTA's group = sg*CL + rank
-    const int nsuper = (p.groups + CL - 1) / CL;
-
-    if (warp == 0) {
-        // =============================== TMA producer
-        if (lane == 0) {
-            const uint16_t mc_mask = (uint16_t)((1u << CL) - 1);
-            constexpr int SLICE_ROWS = TILE_N / CL;                    // centroid rows this CTA fetches per tile
-            auto load_b = [&](int slot, int tile) {
-                const uint32_t bar = smem_u32(b_full + slot);
-                mbar_expect_tx(bar, B_STAGE);
-                for (int kb = 0; kb < KB; ++kb) {
-                    const uint32_t dst = smem_u32(b_smem + (size_t)slot * B_STAGE + kb * BOX_BYTES) + rank * SLICE_ROWS * 128;
-                    if (CL > 1) tma_load_2d_mc(dst, &tmapC, bar, kb * KBLK, tile * TILE_N + rank * SLICE_ROWS, mc_mask);
-                    else tma_load_2d(dst, &tmapC, bar, kb * KBLK, tile * TILE_N);
-                }
-            };
-            auto load_a = [&](int it, int sg) {
-                const int as = it % p.a_stages;
-                const uint32_t ph = (it / p.a_stages) & 1;
-                mbar_wait(smem_u32(a_empty + as), ph ^ 1);
-                const uint32_t bar = smem_u32(a_full + as);
-                mbar_expect_tx(bar, A_STAGE);
-                const int64_t row0 = ((int64_t)sg * CL + rank) * (MB * TILE_M);
-                for (int rb = 0; rb < MB; ++rb)
-                    for (int kb = 0; kb < KB; ++kb)
-                        tma_load_2d(smem_u32(a_smem + (size_t)as * A_STAGE + (rb * KB + kb) * BOX_BYTES), &tmapX, bar,
-                                    kb * KBLK, (int)(row0 + rb * TILE_M));
-            };
-            if (p.resident)
-                for (int t = 0; t < p.ntiles; ++t) load_b(t, t);
-            int a_it = 0, b_it = 0;
-            if (cluster_id < nsuper) load_a(a_it++, cluster_id);
-            for (int sg = cluster_id; sg < nsuper; sg += nclusters) {
-                const bool more = sg + nclusters < nsuper;
-                if (p.resident) {
-                    if (more) load_a(a_it++, sg + nclusters);                  // prefetch the next group's rows
-                } else {
-                    for (int t = 0; t < p.ntiles; ++t, ++b_it) {
-                        const int slot = b_it % p.b_slots;
-                        const uint32_t ph = (b_it / p.b_slots) & 1;
-                        if (!(p.dbg & 4)) {
-                            mbar_wait(smem_u32(b_empty + slot), ph ^ 1);
-                            load_b(slot, t);
-                        }
-                        // next group's rows go out after this group's first centroid tile, so the tile
-                        // stream never waits behind the (longer) wait for a free row stage
-                        if (more && t == 0) load_a(a_it++, sg + nclusters);
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // =============================== MMA issuer (one thread)
-        // descriptor = lo word (start address >> 4 | LBO = 1 << 16) + constant hi word (SBO, version, swizzle)
-        constexpr uint32_t DESC_HI = 64u | (1u << 14) | (2u << 29);
-        const uint32_t a_lo0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) | (1u << 16);
-        const uint32_t b_lo0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) | (1u << 16);
-        int a_it = 0, b_it = 0, t_it = 0;
-        for (int sg = cluster_id; sg < nsuper; sg += nclusters, ++a_it) {
-            const int as = a_it % p.a_stages;
-            mbar_wait(smem_u32(a_full + as), (a_it / p.a_stages) & 1);
-            for (int t = 0; t < p.ntiles; ++t, ++b_it, ++t_it) {
-                const int slot = p.resident ? t : (b_it % p.b_slots);
-                if (!(p.dbg & 4)) mbar_wait(smem_u32(b_full + slot), p.resident ? 0u : (uint32_t)((b_it / p.b_slots) & 1));
-                const int tb = t_it & 1;
-                mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
-                tc_fence_after();
-                if (lane == 0 && !(p.dbg & 8)) {
-                    const uint32_t a_lo = a_lo0 + (uint32_t)as * (A_STAGE >> 4);
-                    const uint32_t b_lo = b_lo0 + (uint32_t)slot * (B_STAGE >> 4);
-                    const uint32_t d0 = tmem_base + (uint32_t)(tb * MB * TILE_N);
-#pragma unroll
-                    for (int rb = 0; rb < MB; ++rb)
-#pragma unroll
-                        for (int kb = 0; kb < KB; ++kb)
-#pragma unroll
-                            for (int k4 = 0; k4 < KBLK / 16; ++k4)
-                                umma_f16_lo(d0 + rb * TILE_N, a_lo + (uint32_t)(((rb * KB + kb) * BOX_BYTES) >> 4) + 2 * k4,
-                                            b_lo + (uint32_t)((kb * BOX_BYTES) >> 4) + 2 * k4, DESC_HI, IDESC_F16_128x128,
-                                            (kb | k4) != 0);
-                }
-                if (lane == 0) {
-                    if (!p.resident && !(p.dbg & 4)) {
-                        if (CL > 1) umma_commit_mc(smem_u32(b_empty + slot), (uint16_t)((1u << CL) - 1));
-                        else umma_commit(smem_u32(b_empty + slot));
-                    }
-                    umma_commit(smem_u32(t_full + tb));
-                }
-                __syncwarp();
-            }
-            if (lane == 0) umma_commit(smem_u32(a_empty + as));
-            __syncwarp();
-        }
-    } else {
-        // =============================== epilogue: 16 warps, one thread per (row, 64-column half)
-        // Warp e = warp - 2: TMEM lane quadrant q = warp & 3 (hardware rule), sub = e >> 2 selects the row
-        // block (sub >> 1) and the column half (sub & 1).  The fast path is branch-light: 32 scores, a min
-        // tree, one compare; only 8-column groups that can hold a candidate take the (predicated) slow path.
-        const int e = warp - 2;
-        const int sub = e >> 2;
-        const int rb = sub >> 1, half = sub & 1;
-        const int q = warp & 3;
-        const float scale = pc_s[3];
-        const int rt = rb * TILE_M + q * 32 + lane;                 // row slot within the CTA's group
-        float2 *my_ring = cand_s + ((size_t)half * (MB * TILE_M) + rt) * MAX_CAND;
-        float2 *peer_ring = cand_s + ((size_t)1 * (MB * TILE_M) + rt) * MAX_CAND;
-        float *xch = reinterpret_cast<float *>(cand_s + (size_t)2 * MB * TILE_M * MAX_CAND) + rt * 4;   // {m, dropped, ncand}
-        const int bar_id = 1 + rb * 4 + q;
-        int t_it = 0;
-        int wl_pos = 0, wl_end = 0, wl_used = 0;        // this warp's reserved worklist block
-        // per-row window and seed come precomputed (rowprep_kernel) and are fetched one group ahead
-        auto fetch_wm = [&](int sg_, float2 &wm_, int &a_) {
-            wm_ = make_float2(0.f, INFINITY); a_ = -1;
-            if (sg_ < nsuper) {
-                const int64_t row_ = (((int64_t)sg_ * CL + rank) * MB + rb) * TILE_M + q * 32 + lane;
-                if (row_ < p.n) { wm_ = p.wm[row_]; a_ = (p.k_prev > 0 && half == 0) ? p.labels[row_] : -1; }
-            }
-        };
-        float2 wm_next; int a_next;
-        fetch_wm(cluster_id, wm_next, a_next);
-        for (int sg = cluster_id; sg < nsuper; sg += nclusters) {
-            const int64_t row = (((int64_t)sg * CL + rank) * MB + rb) * TILE_M + q * 32 + lane;
-            const bool valid = row < p.n;
-            const float2 wm = wm_next;
-            const int a_old = a_next;
-            fetch_wm(sg + nclusters, wm_next, a_next);
-            const float W = wm.x;
-            float m = wm.y;
-            float thr = valid ? m + W : -INFINITY;       // padding rows never enter the candidate path
-            int ncand = 0;
-            float dropped = INFINITY;
-
-            for (int t = 0; t < p.ntiles; ++t, ++t_it) {
-                const int tb = t_it & 1;
-                mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
-                tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) +
-                                       (uint32_t)(tb * MB * TILE_N + rb * TILE_N + half * 64);
-#pragma unroll 1
-                for (int c = 0; c < 2; ++c) {
-                    uint32_t v[32];
-                    __syncwarp();                          // tcgen05.ld is warp-collective
-                    tmem_ld32(taddr + c * 32, v);
-                    tmem_ld_wait();
-                    if (c == 1) {                          // every TMEM read of this tile is done: release the buffer
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(smem_u32(t_empty + tb));
-                    }
-                    const int j0 = t * TILE_N + half * 64 + c * 32;
-                    const float *cn_t = cn_s + j0;
-                    float sc[32];
-#pragma unroll
-                    for (int g = 0; g < 8; ++g) {
-                        const float4 o = *reinterpret_cast<const float4 *>(cn_t + g * 4);
-                        sc[g * 4 + 0] = fmaf(__uint_as_float(v[g * 4 + 0]), scale, o.x);
-                        sc[g * 4 + 1] = fmaf(__uint_as_float(v[g * 4 + 1]), scale, o.y);
-                        sc[g * 4 + 2] = fmaf(__uint_as_float(v[g * 4 + 2]), scale, o.z);
-                        sc[g * 4 + 3] = fmaf(__uint_as_float(v[g * 4 + 3]), scale, o.w);
-                    }
-                    float g8[4];
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        const float a1 = fminf(fminf(sc[g * 8 + 0], sc[g * 8 + 1]), sc[g * 8 + 2]);     // FMNMX3
-                        const float a2 = fminf(fminf(sc[g * 8 + 3], sc[g * 8 + 4]), sc[g * 8 + 5]);
-                        g8[g] = fminf(fminf(sc[g * 8 + 6], sc[g * 8 + 7]), fminf(a1, a2));
-                    }
-                    const float cmin = fminf(fminf(g8[0], g8[1]), fminf(g8[2], g8[3]));
-                    // tighten first: every score <= (final minimum + W) is still <= thr, so the recorded set
-                    // stays a superset of the true candidates
-                    m = fminf(m, cmin);
-                    thr = valid ? m + W : -INFINITY;
-                    if (cmin <= thr) {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            if (g8[g] <= thr) {
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) {
-                                    if (sc[g * 8 + i] <= thr) {
-                                        const int slot = ncand & (MAX_CAND - 1);
-                                        if (ncand >= MAX_CAND) dropped = fminf(dropped, my_ring[slot].y);
-                                        my_ring[slot] = make_float2(__int_as_float(j0 + g * 8 + i), sc[g * 8 + i]);
-                                        ++ncand;
-                                    }
-                                }
-                            }
-                        }
-                    }
-                }
-            }
-            // ---- merge the two column halves of each row, then the certificate (half 0 owns the row)
-            if (half == 1) { xch[0] = m; xch[1] = dropped; xch[2] = __int_as_float(ncand); }
-            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-            bool need_exact = false, changed = false;
-            int cand[WL_CAND];
-            if (half == 0) {
-                const float m2 = xch[0], dropped2 = xch[1];
-                const int ncand2 = __float_as_int(xch[2]);
-                if (valid) {
-                    const float mF = fminf(m, m2);
-                    const float thrF = mF + W;
-                    int cnt = 0, best = -1;
-#pragma unroll
-                    for (int i = 0; i < WL_CAND; ++i) cand[i] = -1;
-#pragma unroll
-                    for (int h2 = 0; h2 < 2; ++h2) {
-                        const float2 *ring = h2 ? peer_ring : my_ring;
-                        const int nc = h2 ? ncand2 : ncand;
-#pragma unroll
-                        for (int i = 0; i < MAX_CAND; ++i) {
-                            const float2 cv = ring[i];
-                            if (i < nc && cv.y <= thrF) {
-                                const int j = __float_as_int(cv.x);
-#pragma unroll
-                                for (int u = 0; u < WL_CAND; ++u) if (u == cnt) cand[u] = j;
-                                if (cv.y == mF) best = j;
-                                ++cnt;
-                            }
-                        }
-                    }
-                    const bool overflow = !(dropped > thrF) || !(dropped2 > thrF);   // true for NaN too
-                    if (best < 0 && cnt > 0) best = cand[0];
-                    need_exact = overflow || cnt != 1 || best < 0 || best >= p.k;
-#pragma unroll
-                    for (int i = 0; i < WL_CAND; ++i) if (cand[i] >= p.k) cand[i] = -1;
-                    if (overflow || best < 0 || best >= p.k) cand[0] = -2;
-                    if (p.k_prev > 0 && a_old != best) changed = true;
-                    p.labels[row] = best;
-                    if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
-                }
-                const unsigned chm = __ballot_sync(0xffffffffu, changed);
-                if (chm && lane == 0) atomicAdd(p.counters + 2, __popc(chm));
-                const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
-                if (mask) {
-                    // Worklist slots are reserved WL_BLOCK at a time per warp, so the (slow) returning atomic is
-                    // off the per-group critical path; unused slots of a block are marked empty (row = -1).
-                    const int cnt = __popc(mask);
-                    if (wl_pos + cnt > wl_end) {
-                        for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
-                        int base = 0;
-                        if (lane == 0) base = atomicAdd(p.counters, WL_BLOCK);
-                        wl_pos = __shfl_sync(0xffffffffu, base, 0);
-                        wl_end = wl_pos + WL_BLOCK;
-                    }
-                    const int base = wl_pos;
-                    wl_pos += cnt;
-                    wl_used += cnt;
-                    if (need_exact) {
-                        const int pos = base + __popc(mask & ((1u << lane) - 1));
-                        p.wl_rows[pos] = (int32_t)row;
-                        int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
-                        dst[0] = make_int4(cand[0], cand[1], cand[2], cand[3]);
-                        dst[1] = make_int4(cand[4], cand[5], cand[6], cand[7]);
-                    }
-                }
-            }
-            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // rings may be reused for the next group
-        }
-        if (half == 0) {
-            for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
-            if (lane == 0 && wl_used) atomicAdd(p.counters + 3, wl_used);
-        }
-    }
-    // ---- teardown
-    tc_fence_before();
-    __syncthreads();
-    if (CL > 1) cluster_sync_all();
-    if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
-}
 
 // ------------------------------------------------------------------------------------------ per-row window / seed
 // Runs once per pass before the search: everything the epilogue needs per row that lives in global memory
@@ -551,12 +171,13 @@ __global__ void rowprep_kernel(int64_t n, int d, int metric, float eta, const Pa
     }
 }
 
-// ------------------------------------------------------------------------------------------ pair kernel
-// cta_group::2 variant for the case where the whole fp16 centroid matrix fits the shared memory of a CTA
-// PAIR (each CTA keeps half of every 256-centroid tile): centroids are loaded once per CTA and never move
-// again, one thread of the leader CTA issues M=256 x N=256 x K=16 MMAs that read A and B from both CTAs'
-// shared memory and write each CTA's 128 rows x 256 columns into its own TMEM.  Per CTA: 2 stages of X16
-// rows (128 rows each) + resident centroids + score offsets + candidate rings.
+// ------------------------------------------------------------------------------------------ search kernel
+// cta_group::2: one thread of the leader CTA issues M=256 x N=256 x K=16 MMAs that read A and B from both CTAs'
+// shared memory and write each CTA's 128 rows x 256 columns into its own TMEM.
+//   KB = 1, 2  the whole fp16 centroid matrix fits the shared memory of the pair (each CTA keeps its half of
+//              every 256-centroid tile): centroids are loaded once and never move again; per CTA 2 stages of
+//              X16 rows (128 rows each) + resident centroids + score offsets + candidate rings.
+//   KB = 0     any other shape: rows and centroids stream through a ring of 64-half blocks.
 namespace {
 __device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap *map, uint32_t leader_bar, int c0, int c1) {
     asm volatile(
@@ -1297,26 +918,6 @@ int tensor_prepare_x16(akm_handle h, RowStore &rs) {
     return AKM_OK;
 }
 
-template <int MB, int KB, int CL>
-static int launch_search(akm_handle h, const CUtensorMap &mx, const CUtensorMap &mc, const SearchParams &sp, size_t smem,
-                         int grid) {
-    auto kern = search_kernel<MB, KB, CL>;
-    AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)grid);
-    cfg.blockDim = dim3(64 + 256 * MB);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = h->stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    AKM_CUDA(h, cudaLaunchKernelEx(&cfg, kern, mx, mc, sp));
-    h->stats.kernel_launches++;
-    return AKM_OK;
-}
-
 float *tensor_useed(akm_handle h) {
     TensorCtx *c = (TensorCtx *)h->tc;
     return (c && c->k_prev > 0) ? c->useed : nullptr;
@@ -1369,25 +970,22 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     if (rs.x16_shift == INT_MIN || k <= 0) return exact_all();
 
     const int KB = (d + KBLK - 1) / KBLK;
-    const int MB = 2;
-    // pair kernel (cta_group::2, centroids resident in the shared memory of a CTA pair) when they fit
-    static const bool pair_off = getenv("AKM_TC_PAIR") && atoi(getenv("AKM_TC_PAIR")) == 0;   // tuning aid
+    // shared-memory plan of a CTA: centroids resident (d <= 128 and they fit) or, for every other shape, both
+    // operands streamed in 64-half blocks
     const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
-    const int nt2 = (k + PAIR_N - 1) / PAIR_N;
-    const size_t pair_fixed = (size_t)nt2 * PAIR_N * 4 + 256 + (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 + (size_t)TILE_M * WL_CAND * 4 + 1024;
-    size_t pair_smem = (size_t)2 * KB * BOX_BYTES + (size_t)nt2 * KB * BOX_BYTES + pair_fixed;
-    const bool pair_ok = !pair_off && h->num_sms >= 2 && rs.n > 2 * TILE_M;
-    // centroids resident (d <= 128 and they fit) or, for every other shape, both operands streamed in K blocks
+    const int ntiles = (k + PAIR_N - 1) / PAIR_N;
+    const int kpad = ntiles * PAIR_N;
+    const size_t pair_fixed = (size_t)kpad * 4 + 256 + (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 +
+                              (size_t)TILE_M * WL_CAND * 4 + 1024;   // offsets, barriers, rings, exchange, merge staging, alignment
+    size_t pair_smem = (size_t)2 * KB * BOX_BYTES + (size_t)ntiles * KB * BOX_BYTES + pair_fixed;
     static const bool stream_env = getenv("AKM_TC_STREAM") && atoi(getenv("AKM_TC_STREAM")) != 0;   // tuning aid
-    const bool pair_resident = pair_ok && KB <= 2 && pair_smem <= budget && !stream_env;
+    const bool pair_resident = KB <= 2 && pair_smem <= budget && !stream_env;
     int stream_stages = 0;
-    if (pair_ok && !pair_resident && budget > pair_fixed) stream_stages = (int)std::min<size_t>(8, (budget - pair_fixed) / (2 * BOX_BYTES));
+    if (!pair_resident && budget > pair_fixed) stream_stages = (int)std::min<size_t>(8, (budget - pair_fixed) / (2 * BOX_BYTES));
     const bool pair_stream = stream_stages >= 3;
     if (pair_stream) pair_smem = (size_t)stream_stages * 2 * BOX_BYTES + pair_fixed;
-    const bool use_pair = pair_resident || pair_stream;
-    if (!use_pair && KB > 2) return exact_all();       // the single-CTA kernel keeps whole rows resident: d <= 128
-    const int ntiles = use_pair ? nt2 : (k + TILE_N - 1) / TILE_N;
-    const int kpad = use_pair ? nt2 * PAIR_N : ntiles * TILE_N;
+    // a partition of at most one row group (256 rows) is not worth a cluster launch
+    if (!(pair_resident || pair_stream) || h->num_sms < 2 || rs.n <= 2 * TILE_M) return exact_all();
     const int d16 = rs.d16;
     if (c->kpad_cap < kpad) {
         cudaFree(c->c16); cudaFree(c->cn);
@@ -1442,28 +1040,13 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     h->stats.kernel_launches += 2;
     AKM_CUDA(h, cudaGetLastError());
 
-    // shared-memory plan
-    const size_t A_STAGE = (size_t)MB * KB * BOX_BYTES, B_STAGE = (size_t)KB * BOX_BYTES;
-    const size_t fixed = (size_t)kpad * 4 + (4 + 2 * MAX_BSLOTS + 4) * 8 + 64 + (size_t)2 * MB * TILE_M * MAX_CAND * 8 +
-                         (size_t)MB * TILE_M * 16 + 1024;   // offsets, barriers, misc, candidate rings, exchange, alignment slack
-    const int a_stages = 2;
-    if (!use_pair && a_stages * A_STAGE + 2 * B_STAGE + fixed > budget) return exact_all();
-    int b_slots = (int)((budget - fixed - a_stages * A_STAGE) / B_STAGE);
-    b_slots = std::min(b_slots, MAX_BSLOTS);
-    const int resident = ntiles <= b_slots ? 1 : 0;
-    if (resident) b_slots = ntiles;
-    const size_t smem = a_stages * A_STAGE + (size_t)b_slots * B_STAGE + fixed;
-
-    const int CL = (use_pair || !resident) ? 2 : 1;          // multicast only pays when centroid tiles stream
     CUtensorMap mapX, mapC;
     AKM_TRY(encode_2d(h, c, &mapX, rs.x16, (uint64_t)d, (uint64_t)rs.n, (uint64_t)d16 * 2, KBLK, TILE_M));
-    AKM_TRY(encode_2d(h, c, &mapC, c->c16, (uint64_t)d, (uint64_t)kpad, (uint64_t)d16 * 2, KBLK,
-                      use_pair ? TILE_M : TILE_N / CL));
+    AKM_TRY(encode_2d(h, c, &mapC, c->c16, (uint64_t)d, (uint64_t)kpad, (uint64_t)d16 * 2, KBLK, TILE_M));
 
     SearchParams sp{};
     sp.n = rs.n;
-    sp.groups = (int)ceil_div64(rs.n, (int64_t)MB * TILE_M);
-    sp.ntiles = ntiles; sp.a_stages = pair_stream ? stream_stages : a_stages; sp.b_slots = b_slots; sp.resident = resident;
+    sp.ntiles = ntiles; sp.a_stages = pair_stream ? stream_stages : 2;
     sp.kblocks = KB;
     sp.d = d; sp.metric = h->metric; sp.k = k;
     sp.cn = c->cn; sp.pc = c->pc; sp.xerr = rs.xerr; sp.labels = labels;
@@ -1482,20 +1065,11 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     sp.wm = c->wm;
-    static const int dbg_env = getenv("AKM_TC_DBG") ? atoi(getenv("AKM_TC_DBG")) : 0;
-    sp.dbg = dbg_env;
-    sp.trace = nullptr;
-    const int nsuper = (sp.groups + CL - 1) / CL;
-    int grid = std::min(h->num_sms / CL, nsuper) * CL;
-    if (grid < CL) grid = CL;
-    int rc;
-    if (use_pair) {
-        const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
-        const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;
-        rc = pair_stream ? launch_pair<0>(h, mapX, mapC, sp, pair_smem, pgrid)
-             : (KB == 1) ? launch_pair<1>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2>(h, mapX, mapC, sp, pair_smem, pgrid);
-    } else if (KB == 1) rc = (CL == 2) ? launch_search<2, 1, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 1, 1>(h, mapX, mapC, sp, smem, grid);
-    else rc = (CL == 2) ? launch_search<2, 2, 2>(h, mapX, mapC, sp, smem, grid) : launch_search<2, 2, 1>(h, mapX, mapC, sp, smem, grid);
+    const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
+    const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;
+    const int rc = pair_stream ? launch_pair<0>(h, mapX, mapC, sp, pair_smem, pgrid)
+                   : (KB == 1) ? launch_pair<1>(h, mapX, mapC, sp, pair_smem, pgrid)
+                               : launch_pair<2>(h, mapX, mapC, sp, pair_smem, pgrid);
     AKM_TRY(rc);
     if (train_rows) {
         AKM_CUDA(h, cudaMemcpyAsync(c->Cprev, C, sizeof(double) * (size_t)k * d, cudaMemcpyDeviceToDevice, h->stream));
