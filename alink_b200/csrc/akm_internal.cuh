@@ -70,6 +70,7 @@ struct akm_handle_s {
 
     // NCCL
     void *comm = nullptr; int rank = 0, world = 1;
+    double *ar_buf = nullptr; size_t ar_cap = 0;      // device staging of akm_allreduce_sum
 
     // k-means|| seeding state of the cached partition (init.cu): nearest chosen centre and the distance to it
     double *init_cost = nullptr; int32_t *init_near = nullptr; int64_t init_cap = 0;

@@ -72,6 +72,7 @@ void nccl_destroy(akm_handle h) {
         if (a->lib) a->CommDestroy((ncclComm_t)h->comm);
         h->comm = nullptr;
     }
+    if (h->ar_buf) { cudaFree(h->ar_buf); h->ar_buf = nullptr; h->ar_cap = 0; }
 }
 
 extern "C" {
@@ -111,17 +112,18 @@ int akm_allreduce_sum(akm_handle h, double *buf, int64_t count) {
     cudaError_t e = cudaSetDevice(h->device);
     if (e != cudaSuccess) return akm_fail(h, AKM_ERR_CUDA, cudaGetErrorString(e));
     if (!h->comm || h->world <= 1 || count == 0) return AKM_OK;
-    double *d = nullptr;
-    AKM_CUDA(h, cudaMalloc((void **)&d, sizeof(double) * (size_t)count));
-    int rc = AKM_OK;
-    do {
-        if (cudaMemcpyAsync(d, buf, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, h->stream) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "H2D failed"); break; }
-        if ((rc = nccl_allreduce_device(h, d, count))) break;
-        if (cudaMemcpyAsync(buf, d, sizeof(double) * (size_t)count, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "D2H failed"); break; }
-        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = akm_fail(h, AKM_ERR_CUDA, "sync failed"); break; }
-    } while (0);
-    cudaFree(d);
-    return rc;
+    if (h->ar_cap < (size_t)count) {                     // grow-only device staging: no allocation on the per-superstep path
+        if (h->ar_buf) cudaFree(h->ar_buf);
+        h->ar_buf = nullptr; h->ar_cap = 0;
+        AKM_CUDA(h, cudaMalloc((void **)&h->ar_buf, sizeof(double) * (size_t)count));
+        h->ar_cap = (size_t)count;
+    }
+    double *d = h->ar_buf;
+    AKM_CUDA(h, cudaMemcpyAsync(d, buf, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(nccl_allreduce_device(h, d, count));
+    AKM_CUDA(h, cudaMemcpyAsync(buf, d, sizeof(double) * (size_t)count, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AKM_OK;
 }
 
 }  // extern "C"
