@@ -389,7 +389,7 @@ def main():
                 "achieved": achieved, "peak": pk["tf_sust"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sust"],
                 "peak_source": "bf16 dense sustained, " + pk["source"],
                 # dram__bytes_read.sum + dram__bytes_write.sum of search_pair_kernel<2> from one `ncu --set full`
-                # capture at 100M x 128 rows, k = 1000 (profiles/r1_ncu_full_100M_rows.csv): 26.80 + 1.24 GB per
+                # capture at 100M x 128 rows, k = 1000 (profiles/r1_ncu_full_100M_rows_final.csv): 26.81 + 1.24 GB per
                 # launch = 280.4 B per row (the fp16 operand copy is 256 B per row), scaled to this launch's rows
                 "traffic": (280.4 * cnt if (engine_used == native.ENGINE_TENSOR and d == 128 and k == 1000) else None),
                 "traffic_unit": "bytes per launch (ncu dram read+write)",
