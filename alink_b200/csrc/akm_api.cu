@@ -78,11 +78,11 @@ static int rowstore_reserve(akm_handle h, RowStore &rs, int64_t need) {
     return AKM_OK;
 }
 
-// fp32 -> fp64 storage migration (lossless: every stored value was fp32-exact)
+// fp32 -> fp64 storage migration (lossless: every stored value was fp32-exact; COSINE rows get normalised here)
 static int rowstore_widen(akm_handle h, RowStore &rs) {
     double *nx = nullptr;
     AKM_TRY(dev_alloc(h, &nx, (size_t)rs.cap * (size_t)h->d));
-    AKM_TRY(launch_widen_rows(h, rs.x32, nx, rs.n * (int64_t)h->d));
+    AKM_TRY(launch_widen_rows(h, rs.x32, rs.xlabel, nx, rs.n));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     dev_free(rs.x32);
     rs.x64 = nx;
@@ -121,11 +121,6 @@ static int upload_pass(akm_handle h, RowStore &rs, const void *src, SrcKind kind
 
 static int upload_rows(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n) {
     if (n == 0) return AKM_OK;
-    if (h->metric == AKM_COSINE && rs.store == 4) {
-        if (rs.n > 0) return akm_fail(h, AKM_ERR_STATE, "cosine partitions are always fp64");
-        rowstore_free(rs);
-        rs.store = 8;
-    }
     AKM_TRY(rowstore_reserve(h, rs, rs.n + n));
     AKM_CUDA(h, cudaMemsetAsync(h->iscal + 3, 0, sizeof(int), h->stream));
     AKM_TRY(upload_pass(h, rs, src, kind, n));
@@ -317,7 +312,7 @@ int akm_create(int device, int d, int metric, akm_handle *out) {
     akm_handle h = new (std::nothrow) akm_handle_s();
     if (!h) return akm_fail(nullptr, AKM_ERR_OOM, "host allocation failed");
     h->device = device; h->d = d; h->metric = metric;
-    h->rows.store = (metric == AKM_COSINE) ? 8 : 4;
+    h->rows.store = 4;
     h->batch.store = h->rows.store;
     int rc = AKM_OK;
     do {
@@ -417,7 +412,7 @@ int akm_clear_rows(akm_handle h) {
     AKM_TRY(bind_device(h));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     rowstore_free(h->rows);
-    h->rows.store = (h->metric == AKM_COSINE) ? 8 : 4;
+    h->rows.store = 4;
     tensor_invalidate_seeds(h);
     dev_free(h->init_cost); dev_free(h->init_near);
     h->init_cap = 0;

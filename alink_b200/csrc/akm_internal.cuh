@@ -12,7 +12,10 @@
 // A block of samples resident in HBM after FastDistance.prepareVectorData.
 //   x32 / x64 : n x d row-major, exactly the values Java holds (fp32 only when every
 //               value is fp32-representable, so widening back to double is lossless)
-//   xlabel    : EUCLIDEAN ||x||^2 summed in index order (EuclideanDistance.java:59-65)
+//   xlabel    : EUCLIDEAN ||x||^2 summed in index order (EuclideanDistance.java:59-65); COSINE |x_raw|
+//   COSINE    : an fp64 store holds the normalised rows.  An fp32 store (every RAW value fp32-representable)
+//               holds the raw rows; the value Java holds, x * (1.0 / |x|), is recomputed on the fly with exactly
+//               the rounding of CosineDistance.updateLabel (:60-65) -- see row_value().
 //   x16       : n x d16 fp16 copy scaled by 2^x16_shift, operand of the tcgen05 search
 //   xerr      : per row float2 {||x||_2 rounded up, ||x - x16/scale||_2 rounded up}
 struct RowStore {
@@ -32,6 +35,11 @@ struct RowStore {
     int32_t *orig = nullptr; int64_t orig_cap = 0, orig_n = 0;
     bool reordered = false;
 };
+
+// 1.0 / |x| the way CosineDistance.updateLabel forms it (untouched rows -- |x| not > 0 -- keep their values)
+__device__ __forceinline__ double cos_inv(double nrm) { return nrm > 0.0 ? 1.0 / nrm : 1.0; }
+// true when a partition of storage type T under METRIC keeps RAW rows that must be scaled on the fly
+template <typename T, int METRIC> struct RawCosine { static constexpr bool value = (METRIC == AKM_COSINE) && sizeof(T) == 4; };
 
 struct Scratch;   // akm_api.cu
 
@@ -120,7 +128,7 @@ int akm_fail(akm_handle h, int code, const std::string &msg);
 // prepareVectorData over `n` staged rows (src: double or float, row-major) appended at row `row0`.
 int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n);
 // widen rows [0,n) of x32 into x64 (storage migration)
-int launch_widen_rows(akm_handle h, const float *x32, double *x64, int64_t count);
+int launch_widen_rows(akm_handle h, const float *x32, const double *xlabel, double *x64, int64_t n);
 // updateLabel on k0 centroids in place (EUCL: labels; COS: normalise rows unless cos_normalise == false,
 // which is what KMeansAssignCluster sees: a matrix that was label-updated already)
 int launch_prepare_centroids(akm_handle h, double *C, double *clabel, int k0, bool cos_normalise);

@@ -23,7 +23,7 @@ __global__ void labels_in_kernel(const int32_t *__restrict__ src, const int32_t 
 template <typename T, int METRIC>
 __global__ void eval_own_kernel(const T *__restrict__ X, int64_t n, int d, const int32_t *__restrict__ labels, int k,
                                 const double *__restrict__ mean, const double *__restrict__ mean_norm,
-                                double *__restrict__ out) {
+                                const double *__restrict__ xnorm, double *__restrict__ out) {
     const int lane = threadIdx.x & 31;
     int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -33,8 +33,10 @@ __global__ void eval_own_kernel(const T *__restrict__ X, int64_t n, int d, const
         const T *x = X + row * d;
         const double *m = mean + (size_t)c * d;
         double a = 0.0, nsq = 0.0;
+        const double rinv = RawCosine<T, METRIC>::value ? cos_inv(xnorm[row]) : 1.0;
         for (int i = lane; i < d; i += 32) {
-            const double xv = (double)x[i];
+            double xv = (double)x[i];
+            if (RawCosine<T, METRIC>::value) xv = __dmul_rn(rinv, xv);
             nsq = fma(xv, xv, nsq);
             if (METRIC == AKM_EUCLIDEAN) { const double df = m[i] - xv; a = fma(df, df, a); }
             else a = fma(m[i], xv, a);
@@ -58,8 +60,9 @@ __global__ void eval_own_kernel(const T *__restrict__ X, int64_t n, int d, const
 // (the tiling of assign_exact_kernel), fp64 FMA dot products.
 //   EUCLIDEAN  diss_j = cnt_j |x|^2 - 2 cnt_j x.mean_j + normsum_j ; own: / (cnt_j - 1), others: min over j of / cnt_j
 //   COSINE     diss_j = 1 - x_raw.mean_j                           ; own: * cnt_j / (cnt_j - 1), others: min over j
-// (the reference takes the RAW vector here although the means are means of normalised vectors; rownorm carries
-// |x_raw| for a COSINE partition, whose stored rows are normalised)
+// (the reference takes the RAW vector here although the means are means of normalised vectors; rowscalar carries
+// |x_raw| for a COSINE partition: an fp64 store holds normalised rows and multiplies back, an fp32 store holds the
+// raw rows and uses them as they are)
 constexpr int SV_TR = 64, SV_TC = 64, SV_KC = 32, SV_LD = 66;
 
 template <typename T, int METRIC>
@@ -134,7 +137,7 @@ eval_silhouette_kernel(const T *__restrict__ X, const double *__restrict__ rowsc
                         if (j == lab[a]) { if (cj > 1.0) cur[a] = diss / (cj - 1.0); }
                         else nb[a] = fmin(nb[a], diss / cj);
                     } else {
-                        const double diss = 1.0 - rs[a] * t[a][b];
+                        const double diss = 1.0 - (RawCosine<T, METRIC>::value ? t[a][b] : rs[a] * t[a][b]);
                         if (j == lab[a]) { if (cj > 1.0) cur[a] = diss * cj / (cj - 1.0); }
                         else nb[a] = fmin(nb[a], diss);
                     }
@@ -177,10 +180,11 @@ int launch_eval_own(akm_handle h, const RowStore &rs, const int32_t *labels, int
     if (rs.n <= 0) return AKM_OK;
     const int blocks = h->num_sms * 8;
     if (h->metric == AKM_EUCLIDEAN) {
-        if (rs.store == 4) eval_own_kernel<float, AKM_EUCLIDEAN><<<blocks, 256, 0, h->stream>>>(rs.x32, rs.n, h->d, labels, k, mean, mean_norm, out3k);
-        else eval_own_kernel<double, AKM_EUCLIDEAN><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.n, h->d, labels, k, mean, mean_norm, out3k);
+        if (rs.store == 4) eval_own_kernel<float, AKM_EUCLIDEAN><<<blocks, 256, 0, h->stream>>>(rs.x32, rs.n, h->d, labels, k, mean, mean_norm, rs.xlabel, out3k);
+        else eval_own_kernel<double, AKM_EUCLIDEAN><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.n, h->d, labels, k, mean, mean_norm, rs.xlabel, out3k);
     } else {
-        eval_own_kernel<double, AKM_COSINE><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.n, h->d, labels, k, mean, mean_norm, out3k);
+        if (rs.store == 4) eval_own_kernel<float, AKM_COSINE><<<blocks, 256, 0, h->stream>>>(rs.x32, rs.n, h->d, labels, k, mean, mean_norm, rs.xlabel, out3k);
+        else eval_own_kernel<double, AKM_COSINE><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.n, h->d, labels, k, mean, mean_norm, rs.xlabel, out3k);
     }
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
@@ -196,7 +200,8 @@ int launch_eval_silhouette(akm_handle h, const RowStore &rs, const int32_t *labe
         if (rs.store == 4) eval_silhouette_kernel<float, AKM_EUCLIDEAN><<<blocks, 256, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, h->d, labels, k, mean, cnt, normsum, sil_sum);
         else eval_silhouette_kernel<double, AKM_EUCLIDEAN><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, h->d, labels, k, mean, cnt, normsum, sil_sum);
     } else {
-        eval_silhouette_kernel<double, AKM_COSINE><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, h->d, labels, k, mean, cnt, normsum, sil_sum);
+        if (rs.store == 4) eval_silhouette_kernel<float, AKM_COSINE><<<blocks, 256, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, h->d, labels, k, mean, cnt, normsum, sil_sum);
+        else eval_silhouette_kernel<double, AKM_COSINE><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, h->d, labels, k, mean, cnt, normsum, sil_sum);
     }
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());

@@ -75,9 +75,11 @@ __device__ __forceinline__ int find_sorted(const int64_t *__restrict__ a, int m,
 }
 
 // one warp per stored row: copy it (as double) to out[p] when the caller asked for it
+// (xnorm != nullptr: COSINE rows stored raw; the prepared vector is x * (1.0 / |x|))
 template <typename T>
-__global__ void gather_rows_kernel(int64_t n, const T *__restrict__ X, int d, const int32_t *__restrict__ orig,
-                                   const int64_t *__restrict__ rows_sorted, int m, double *__restrict__ out) {
+__global__ void gather_rows_kernel(int64_t n, const T *__restrict__ X, const double *__restrict__ xnorm, int d,
+                                   const int32_t *__restrict__ orig, const int64_t *__restrict__ rows_sorted, int m,
+                                   double *__restrict__ out) {
     const int lane = threadIdx.x & 31;
     int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -85,7 +87,11 @@ __global__ void gather_rows_kernel(int64_t n, const T *__restrict__ X, int d, co
         const int64_t local = orig ? (int64_t)orig[i] : i;
         const int p = find_sorted(rows_sorted, m, local);
         if (p < 0) continue;
-        for (int c = lane; c < d; c += 32) out[(size_t)p * d + c] = (double)X[i * d + c];
+        const double rinv = xnorm ? cos_inv(xnorm[i]) : 1.0;
+        for (int c = lane; c < d; c += 32) {
+            const double v = (double)X[i * d + c];
+            out[(size_t)p * d + c] = xnorm ? __dmul_rn(rinv, v) : v;
+        }
     }
 }
 
@@ -133,8 +139,9 @@ int launch_init_pick(akm_handle h, const RowStore &rs, const double *cost, int64
 int launch_gather_rows(akm_handle h, const RowStore &rs, const int64_t *rows_sorted_dev, int m, double *out_dev) {
     if (rs.n <= 0 || m <= 0) return AKM_OK;
     const int32_t *orig = rs.reordered ? rs.orig : nullptr;
-    if (rs.store == 4) gather_rows_kernel<float><<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, rs.x32, h->d, orig, rows_sorted_dev, m, out_dev);
-    else gather_rows_kernel<double><<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, rs.x64, h->d, orig, rows_sorted_dev, m, out_dev);
+    const double *xnorm = (h->metric == AKM_COSINE && rs.store == 4) ? rs.xlabel : nullptr;
+    if (rs.store == 4) gather_rows_kernel<float><<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, rs.x32, xnorm, h->d, orig, rows_sorted_dev, m, out_dev);
+    else gather_rows_kernel<double><<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, rs.x64, nullptr, h->d, orig, rows_sorted_dev, m, out_dev);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     return AKM_OK;

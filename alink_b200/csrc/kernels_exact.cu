@@ -83,8 +83,9 @@ prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, f
         // CosineDistance.updateLabel :60-65: norm = sqrt(dot); if (norm > 0) x *= 1.0 / norm
         const double nrm = sqrt(s);
         inv_s[tid] = (nrm > 0.0) ? (1.0 / nrm) : -1.0;   // -1 == leave untouched
-        if (myrow < n) xlabel[row0 + myrow] = nrm;          // |x_raw|: not a distance label, kept for EvalCluster's silhouette
+        if (myrow < n) xlabel[row0 + myrow] = nrm;          // |x_raw|: not a distance label; scales fp32-stored rows
         __syncthreads();
+        // fp32 store: raw rows (the scaling happens where they are read); fp64 store: normalised rows
         for (int c0 = 0; c0 < d; c0 += PREP_COLS) {
 #pragma unroll 8
             for (int it = 0; it < PREP_ROWS / (PREP_ROWS / PREP_COLS); ++it) {
@@ -93,9 +94,15 @@ prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, f
                 const int col = c0 + lc;
                 if (row < n && col < d) {
                     double v = (double)src[row * d + col];
-                    const double inv = inv_s[r];
-                    if (inv >= 0.0) v = DMUL(inv, v);
-                    x64[(row0 + row) * d + col] = v;   // normalised values are never fp32-exact
+                    if (STORE == 4) {
+                        const float f = (float)v;
+                        if (!((double)f == v)) inexact = true;
+                        x32[(row0 + row) * d + col] = f;
+                    } else {
+                        const double inv = inv_s[r];
+                        if (inv >= 0.0) v = DMUL(inv, v);
+                        x64[(row0 + row) * d + col] = v;
+                    }
                 }
             }
         }
@@ -115,7 +122,8 @@ int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f3
         if (rs.store == 4) { if (src_is_f32) PREP_LAUNCH(float, AKM_EUCLIDEAN, 4); else PREP_LAUNCH(double, AKM_EUCLIDEAN, 4); }
         else               { if (src_is_f32) PREP_LAUNCH(float, AKM_EUCLIDEAN, 8); else PREP_LAUNCH(double, AKM_EUCLIDEAN, 8); }
     } else {
-        if (src_is_f32) PREP_LAUNCH(float, AKM_COSINE, 8); else PREP_LAUNCH(double, AKM_COSINE, 8);
+        if (rs.store == 4) { if (src_is_f32) PREP_LAUNCH(float, AKM_COSINE, 4); else PREP_LAUNCH(double, AKM_COSINE, 4); }
+        else               { if (src_is_f32) PREP_LAUNCH(float, AKM_COSINE, 8); else PREP_LAUNCH(double, AKM_COSINE, 8); }
     }
 #undef PREP_LAUNCH
     h->stats.kernel_launches++;
@@ -123,15 +131,23 @@ int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f3
     return AKM_OK;
 }
 
-__global__ void widen_rows_kernel(const float *__restrict__ a, double *__restrict__ b, int64_t count) {
+// fp32 -> fp64 storage migration.  EUCLIDEAN: plain widening.  COSINE (xlabel != nullptr): the fp64 store holds
+// the normalised rows, so the scaling a raw fp32 store defers is applied here.
+__global__ void widen_rows_kernel(const float *__restrict__ a, const double *__restrict__ xlabel, int d,
+                                  double *__restrict__ b, int64_t count) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; i < count; i += stride) b[i] = (double)a[i];
+    for (; i < count; i += stride) {
+        double v = (double)a[i];
+        if (xlabel != nullptr) { const double nrm = xlabel[i / d]; if (nrm > 0.0) v = DMUL(1.0 / nrm, v); }
+        b[i] = v;
+    }
 }
 
-int launch_widen_rows(akm_handle h, const float *x32, double *x64, int64_t count) {
-    if (count <= 0) return AKM_OK;
-    widen_rows_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(x32, x64, count);
+int launch_widen_rows(akm_handle h, const float *x32, const double *xlabel, double *x64, int64_t n) {
+    if (n <= 0) return AKM_OK;
+    widen_rows_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(x32, h->metric == AKM_COSINE ? xlabel : nullptr, h->d, x64,
+                                                           n * (int64_t)h->d);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     return AKM_OK;
@@ -232,7 +248,10 @@ assign_exact_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, 
                 const int col = i0 + lcol;
                 const int64_t row = srow[r];
                 double xv = 0.0, cv = 0.0;
-                if (row >= 0 && col < d) xv = (double)X[row * d + col];
+                if (row >= 0 && col < d) {
+                    xv = (double)X[row * d + col];
+                    if (RawCosine<T, METRIC>::value) xv = DMUL(cos_inv(xlabel[row]), xv);
+                }
                 const int cj = c0 + r;
                 if (cj < k && col < d) cv = C[(size_t)cj * d + col];
                 xs[lcol][r] = xv;
@@ -321,7 +340,8 @@ int launch_assign_exact(akm_handle h, const RowStore &rs, const int32_t *rowlist
         if (rs.store == 4) { if (ind) AE_LAUNCH(float, rs.x32, AKM_EUCLIDEAN, true); else AE_LAUNCH(float, rs.x32, AKM_EUCLIDEAN, false); }
         else               { if (ind) AE_LAUNCH(double, rs.x64, AKM_EUCLIDEAN, true); else AE_LAUNCH(double, rs.x64, AKM_EUCLIDEAN, false); }
     } else {
-        if (ind) AE_LAUNCH(double, rs.x64, AKM_COSINE, true); else AE_LAUNCH(double, rs.x64, AKM_COSINE, false);
+        if (rs.store == 4) { if (ind) AE_LAUNCH(float, rs.x32, AKM_COSINE, true); else AE_LAUNCH(float, rs.x32, AKM_COSINE, false); }
+        else               { if (ind) AE_LAUNCH(double, rs.x64, AKM_COSINE, true); else AE_LAUNCH(double, rs.x64, AKM_COSINE, false); }
     }
 #undef AE_LAUNCH
     h->stats.kernel_launches++;
@@ -340,7 +360,7 @@ int launch_assign_exact_list(akm_handle h, const RowStore &rs, const int32_t *ro
     assign_exact_kernel<T, M, true><<<grid, 256, 0, h->stream>>>(PTR, rs.xlabel, rowlist, 0, count_dev, h->d, C, clabel, k, \
                                                                  labels, nullptr, nullptr, k, err)
     if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) AEL_LAUNCH(float, rs.x32, AKM_EUCLIDEAN); else AEL_LAUNCH(double, rs.x64, AKM_EUCLIDEAN); }
-    else AEL_LAUNCH(double, rs.x64, AKM_COSINE);
+    else { if (rs.store == 4) AEL_LAUNCH(float, rs.x32, AKM_COSINE); else AEL_LAUNCH(double, rs.x64, AKM_COSINE); }
 #undef AEL_LAUNCH
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
@@ -455,9 +475,12 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
             for (; p + U * SUB <= e; p += U * SUB) {
                 using RawT = typename std::conditional<VEC, typename Vec16<T>::type, T>::type;
                 RawT raw[U][DC];                      // loads stay in their storage type until they are consumed
+                double rsc[U];                        // COSINE rows stored raw: 1 / |x| per row
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
-                    const T *row = X + (base + sorted[p + u * SUB + sub]) * (int64_t)d + cb0;
+                    const int64_t ridx = base + sorted[p + u * SUB + sub];
+                    const T *row = X + ridx * (int64_t)d + cb0;
+                    rsc[u] = RawCosine<T, METRIC>::value ? cos_inv(xlabel[ridx]) : 1.0;
 #pragma unroll
                     for (int m = 0; m < DC; ++m) {
                         const int c0 = (cl + L * m) * VN;
@@ -473,17 +496,20 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
                         if constexpr (VEC) Vec16<T>::unpack(raw[u][m], val);
                         else val[0] = (double)raw[u][m];
 #pragma unroll
-                        for (int v = 0; v < VN; ++v) acc[m][v] += val[v];
+                        for (int v = 0; v < VN; ++v) acc[m][v] += RawCosine<T, METRIC>::value ? DMUL(rsc[u], val[v]) : val[v];
                     }
             }
             if (p < e) {                              // last, partial batch: same loads, predicated per row
                 using RawT = typename std::conditional<VEC, typename Vec16<T>::type, T>::type;
                 RawT raw[U][DC];
+                double rsc[U];
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
                     const int q = p + u * SUB + sub;
                     const bool ok = q < e;
-                    const T *row = X + (base + sorted[ok ? q : s]) * (int64_t)d + cb0;
+                    const int64_t ridx = base + sorted[ok ? q : s];
+                    const T *row = X + ridx * (int64_t)d + cb0;
+                    rsc[u] = RawCosine<T, METRIC>::value ? cos_inv(xlabel[ridx]) : 1.0;
 #pragma unroll
                     for (int m = 0; m < DC; ++m) {
                         const int c0 = (cl + L * m) * VN;
@@ -499,7 +525,7 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
                         if constexpr (VEC) Vec16<T>::unpack(raw[u][m], val);
                         else val[0] = (double)raw[u][m];
 #pragma unroll
-                        for (int v = 0; v < VN; ++v) acc[m][v] += val[v];
+                        for (int v = 0; v < VN; ++v) acc[m][v] += RawCosine<T, METRIC>::value ? DMUL(rsc[u], val[v]) : val[v];
                     }
             }
             p = e;
@@ -563,7 +589,7 @@ accumulate_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, i
 template <typename T, int METRIC>
 __global__ void accumulate_atomic_kernel(const T *__restrict__ X, const int32_t *__restrict__ labels, int64_t n, int d,
                                          int k0, const double *__restrict__ C, double *__restrict__ sum,
-                                         double *__restrict__ objective) {
+                                         double *__restrict__ objective, const double *__restrict__ xlabel) {
     const int lane = threadIdx.x & 31;
     int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -574,7 +600,8 @@ __global__ void accumulate_atomic_kernel(const T *__restrict__ X, const int32_t 
         double *out = sum + (size_t)lab * (d + 1);
         const double *c = C + (size_t)lab * d;
         for (int col = lane; col < d; col += 32) {
-            const double v = (double)X[row * d + col];
+            double v = (double)X[row * d + col];
+            if (RawCosine<T, METRIC>::value) v = DMUL(cos_inv(xlabel[row]), v);
             atomicAdd(out + col, v);
             if (METRIC == AKM_EUCLIDEAN) { const double df = v - c[col]; obj = fma(df, df, obj); }
             else obj -= c[col] * v;
@@ -595,7 +622,7 @@ static int accumulate_dispatch(akm_handle h, const T *X, int64_t n, const int32_
     const size_t budget = h->smem_optin > 8192 ? h->smem_optin - 8192 : 0;
     if (fixed + 2048 * 2 > budget) {
         const int blocks = h->num_sms * 8;
-        accumulate_atomic_kernel<T, METRIC><<<blocks, 256, 0, h->stream>>>(X, labels, n, d, k0, C, sum, objective);
+        accumulate_atomic_kernel<T, METRIC><<<blocks, 256, 0, h->stream>>>(X, labels, n, d, k0, C, sum, objective, xlabel);
         h->stats.kernel_launches++;
         AKM_CUDA(h, cudaGetLastError());
         return AKM_OK;
@@ -668,6 +695,7 @@ int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, c
         if (rs.store == 4) return accumulate_dispatch<float, AKM_EUCLIDEAN>(h, rs.x32, rs.n, labels, C, k0, sum, objective, rs.xlabel, clabel);
         return accumulate_dispatch<double, AKM_EUCLIDEAN>(h, rs.x64, rs.n, labels, C, k0, sum, objective, rs.xlabel, clabel);
     }
+    if (rs.store == 4) return accumulate_dispatch<float, AKM_COSINE>(h, rs.x32, rs.n, labels, C, k0, sum, objective, rs.xlabel, clabel);
     return accumulate_dispatch<double, AKM_COSINE>(h, rs.x64, rs.n, labels, C, k0, sum, objective, rs.xlabel, clabel);
 }
 

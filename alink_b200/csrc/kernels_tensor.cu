@@ -585,19 +585,22 @@ __global__ void absmax_kernel_f64(const double *__restrict__ x, int64_t count, u
 }
 
 // one warp per row: x16 = fp16(x * 2^sx), xerr = {||x||, ||x - x16 * 2^-sx||} (rounded up)
+// (xnorm != nullptr: COSINE rows stored raw, the operand is built from x * (1.0 / |x|))
 template <typename T>
-__global__ void x16_build_kernel(const T *__restrict__ X, int64_t n, int d, int d16, int sx, __half *__restrict__ x16,
-                                 float2 *__restrict__ xerr) {
+__global__ void x16_build_kernel(const T *__restrict__ X, const double *__restrict__ xnorm, int64_t n, int d, int d16, int sx,
+                                 __half *__restrict__ x16, float2 *__restrict__ xerr) {
     const int lane = threadIdx.x & 31;
     int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const double up = ldexp(1.0, sx), down = ldexp(1.0, -sx);
     for (; row < n; row += stride) {
         double s2 = 0.0, e2 = 0.0;
+        const double rinv = xnorm ? cos_inv(xnorm[row]) : 1.0;
         for (int c = lane; c < d16; c += 32) {
             __half hv = __float2half_rn(0.f);
             if (c < d) {
-                const double v = (double)X[row * d + c];
+                double v = (double)X[row * d + c];
+                if (xnorm) v = __dmul_rn(rinv, v);
                 hv = __double2half(v * up);
                 const double back = (double)__half2float(hv) * down;
                 const double dl = v - back;
@@ -733,6 +736,7 @@ refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xla
 #pragma unroll
             for (int i = 0; i < WL_CAND; ++i) acc[i] = 0.0;
             const bool wide = nc > 3;
+            const double rinv = RawCosine<T, METRIC>::value ? cos_inv(xlabel[row]) : 1.0;
             // one full 32-byte sector of the sample row per step (each sector is fetched exactly once even when
             // the L1 cannot hold the lines of all resident warps)
             constexpr int STEP = 32 / (int)sizeof(T);
@@ -755,6 +759,10 @@ refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xla
                 } else {
 #pragma unroll
                     for (int u = 0; u < STEP; ++u) xv[u] = (c + u < d) ? (double)x[c + u] : 0.0;
+                }
+                if (RawCosine<T, METRIC>::value) {
+#pragma unroll
+                    for (int u = 0; u < STEP; ++u) xv[u] = __dmul_rn(rinv, xv[u]);
                 }
 #pragma unroll
                 for (int i = 0; i < WL_CAND; ++i) {
@@ -810,7 +818,12 @@ __global__ void winner_distance_kernel(const T *__restrict__ X, const double *__
         const T *x = X + row * d;
         const double *c = C + (size_t)j * d;
         double t = 0.0;
-        for (int i = 0; i < d; ++i) t = __dadd_rn(t, __dmul_rn(c[i], (double)x[i]));
+        if (RawCosine<T, METRIC>::value) {
+            const double rinv = cos_inv(xlabel[row]);
+            for (int i = 0; i < d; ++i) t = __dadd_rn(t, __dmul_rn(c[i], __dmul_rn(rinv, (double)x[i])));
+        } else {
+            for (int i = 0; i < d; ++i) t = __dadd_rn(t, __dmul_rn(c[i], (double)x[i]));
+        }
         double D;
         if (METRIC == AKM_EUCLIDEAN) {
             const double y = __dadd_rn(0.0, __dmul_rn(-2.0, t));
@@ -895,6 +908,8 @@ int tensor_prepare_x16(akm_handle h, RowStore &rs) {
     float mx;
     memcpy(&mx, &bits, sizeof(float));
     if (!(mx < 3.0e38f)) { rs.x16_shift = INT_MIN; rs.x16_valid = true; return AKM_OK; }   // non-finite data: exact engine only
+    const bool raw_cosine = h->metric == AKM_COSINE && rs.store == 4;
+    if (raw_cosine && mx > 0.f) mx = 1.0f;               // the operand is built from the normalised values, |x_hat_i| <= 1
     int e = 0;
     if (mx > 0.f) frexpf(mx, &e);
     rs.x16_shift = (mx > 0.f) ? 14 - e : 0;
@@ -910,8 +925,9 @@ int tensor_prepare_x16(akm_handle h, RowStore &rs) {
         rs.want16 = true;
     }
     const int blocks = (int)std::min<int64_t>((rs.n + 7) / 8, (int64_t)h->num_sms * 32);
-    if (rs.store == 4) x16_build_kernel<float><<<blocks, 256, 0, h->stream>>>(rs.x32, rs.n, d, d16, rs.x16_shift, rs.x16, rs.xerr);
-    else x16_build_kernel<double><<<blocks, 256, 0, h->stream>>>(rs.x64, rs.n, d, d16, rs.x16_shift, rs.x16, rs.xerr);
+    if (rs.store == 4) x16_build_kernel<float><<<blocks, 256, 0, h->stream>>>(rs.x32, raw_cosine ? rs.xlabel : nullptr, rs.n, d, d16,
+                                                                               rs.x16_shift, rs.x16, rs.xerr);
+    else x16_build_kernel<double><<<blocks, 256, 0, h->stream>>>(rs.x64, nullptr, rs.n, d, d16, rs.x16_shift, rs.x16, rs.xerr);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     rs.x16_valid = true;
@@ -1085,7 +1101,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     refine_candidates_kernel<T, M><<<rblocks, 128, 0, h->stream>>>(PTR, rs.xlabel, d, C, clabel, k, c->wl_rows, \
                                                                    c->wl_cand, c->counters, labels, c->exact_rows, c->counters + 1)
     if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) REFINE(float, rs.x32, AKM_EUCLIDEAN); else REFINE(double, rs.x64, AKM_EUCLIDEAN); }
-    else REFINE(double, rs.x64, AKM_COSINE);
+    else { if (rs.store == 4) REFINE(float, rs.x32, AKM_COSINE); else REFINE(double, rs.x64, AKM_COSINE); }
 #undef REFINE
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
@@ -1096,7 +1112,8 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
             if (rs.store == 4) winner_distance_kernel<float, AKM_EUCLIDEAN><<<wb, 256, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, d, C, clabel, labels, mind);
             else winner_distance_kernel<double, AKM_EUCLIDEAN><<<wb, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
         } else {
-            winner_distance_kernel<double, AKM_COSINE><<<wb, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+            if (rs.store == 4) winner_distance_kernel<float, AKM_COSINE><<<wb, 256, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+            else winner_distance_kernel<double, AKM_COSINE><<<wb, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
         }
         h->stats.kernel_launches++;
         AKM_CUDA(h, cudaGetLastError());
