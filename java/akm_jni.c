@@ -98,3 +98,99 @@ JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_
     if (p) (*env)->ReleaseDoubleArrayElements(env, probs, p, 0);
     return rc;
 }
+
+/* ---- device-resident loop ---------------------------------------------------------------------- */
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_setCentroids(JNIEnv *env, jclass cls, jlong h, jdoubleArray c0, jint k0) {
+    jdouble *c = (*env)->GetDoubleArrayElements(env, c0, NULL);
+    int rc = akm_set_centroids(H(h), c, k0);
+    (*env)->ReleaseDoubleArrayElements(env, c0, c, JNI_ABORT);
+    return rc;
+}
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_step(JNIEnv *env, jclass cls, jlong h, jdouble tol, jintArray conv, jintArray k,
+                                 jdoubleArray obj) {
+    int cv = 0, kk = 0;
+    double o = 0.0;
+    int rc = akm_step(H(h), tol, &cv, &kk, &o);
+    jint jc = cv, jk = kk;
+    (*env)->SetIntArrayRegion(env, conv, 0, 1, &jc);
+    (*env)->SetIntArrayRegion(env, k, 0, 1, &jk);
+    (*env)->SetDoubleArrayRegion(env, obj, 0, 1, &o);
+    return rc;
+}
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_getModel(JNIEnv *env, jclass cls, jlong h, jdoubleArray cOut, jintArray kOut,
+                                     jdoubleArray wOut, jintArray stepsOut) {
+    jdouble *c = (*env)->GetDoubleArrayElements(env, cOut, NULL);
+    jdouble *w = (*env)->GetDoubleArrayElements(env, wOut, NULL);
+    int kk = 0, st = 0;
+    int rc = akm_get_model(H(h), c, &kk, w, &st);
+    jint jk = kk, js = st;
+    (*env)->SetIntArrayRegion(env, kOut, 0, 1, &jk);
+    (*env)->SetIntArrayRegion(env, stepsOut, 0, 1, &js);
+    (*env)->ReleaseDoubleArrayElements(env, cOut, c, 0);
+    (*env)->ReleaseDoubleArrayElements(env, wOut, w, 0);
+    return rc;
+}
+
+/* ---- initial centroids -------------------------------------------------------------------------- */
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_initReset(JNIEnv *env, jclass cls, jlong h) { return akm_init_reset(H(h)); }
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_initUpdate(JNIEnv *env, jclass cls, jlong h, jdoubleArray centers, jint m, jint idBase,
+                                       jdoubleArray sumOut) {
+    jdouble *c = (*env)->GetDoubleArrayElements(env, centers, NULL);
+    double s = 0.0;
+    int rc = akm_init_update(H(h), c, m, idBase, &s);
+    (*env)->ReleaseDoubleArrayElements(env, centers, c, JNI_ABORT);
+    (*env)->SetDoubleArrayRegion(env, sumOut, 0, 1, &s);
+    return rc;
+}
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_initPick(JNIEnv *env, jclass cls, jlong h, jdouble scale, jlong seed, jint round,
+                                     jlong rowBase, jint cap, jlongArray rowsOut, jintArray countOut) {
+    jlong *r = (*env)->GetLongArrayElements(env, rowsOut, NULL);
+    int cnt = 0;
+    int rc = akm_init_pick(H(h), scale, (uint64_t)seed, round, rowBase, cap, (int64_t *)r, &cnt);
+    jint jc = cnt;
+    (*env)->SetIntArrayRegion(env, countOut, 0, 1, &jc);
+    (*env)->ReleaseLongArrayElements(env, rowsOut, r, 0);
+    return rc;
+}
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_initCounts(JNIEnv *env, jclass cls, jlong h, jint mTotal, jdoubleArray countsOut) {
+    jdouble *c = (*env)->GetDoubleArrayElements(env, countsOut, NULL);
+    int rc = akm_init_counts(H(h), mTotal, c);
+    (*env)->ReleaseDoubleArrayElements(env, countsOut, c, 0);
+    return rc;
+}
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_getRows(JNIEnv *env, jclass cls, jlong h, jlongArray rows, jint m, jdoubleArray out) {
+    jlong *r = (*env)->GetLongArrayElements(env, rows, NULL);
+    jdouble *o = (*env)->GetDoubleArrayElements(env, out, NULL);
+    int rc = akm_get_rows(H(h), (const int64_t *)r, m, o);
+    (*env)->ReleaseLongArrayElements(env, rows, r, JNI_ABORT);
+    (*env)->ReleaseDoubleArrayElements(env, out, o, 0);
+    return rc;
+}
+
+/* ---- cluster evaluation ------------------------------------------------------------------------- */
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_evalClusters(JNIEnv *env, jclass cls, jlong h, jintArray labels, jint k,
+                                         jdoubleArray cnt, jdoubleArray mean, jdoubleArray dsum, jdoubleArray dsq,
+                                         jdoubleArray nsq, jdoubleArray sil) {
+    jint *l = (*env)->GetIntArrayElements(env, labels, NULL);
+    jdouble *a = (*env)->GetDoubleArrayElements(env, cnt, NULL);
+    jdouble *b = (*env)->GetDoubleArrayElements(env, mean, NULL);
+    jdouble *c = (*env)->GetDoubleArrayElements(env, dsum, NULL);
+    jdouble *d = (*env)->GetDoubleArrayElements(env, dsq, NULL);
+    jdouble *e = (*env)->GetDoubleArrayElements(env, nsq, NULL);
+    double s = 0.0;
+    int rc = akm_eval_clusters(H(h), (const int32_t *)l, k, a, b, c, d, e, &s);
+    (*env)->ReleaseIntArrayElements(env, labels, l, JNI_ABORT);
+    (*env)->ReleaseDoubleArrayElements(env, cnt, a, 0);
+    (*env)->ReleaseDoubleArrayElements(env, mean, b, 0);
+    (*env)->ReleaseDoubleArrayElements(env, dsum, c, 0);
+    (*env)->ReleaseDoubleArrayElements(env, dsq, d, 0);
+    (*env)->ReleaseDoubleArrayElements(env, nsq, e, 0);
+    (*env)->SetDoubleArrayRegion(env, sil, 0, 1, &s);
+    return rc;
+}

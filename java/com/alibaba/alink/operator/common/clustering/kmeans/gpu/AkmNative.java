@@ -30,6 +30,24 @@ public final class AkmNative {
     public static native int predict(long handle, double[] rows, long n, double[] centroids, int k,
                                      long[] idxOut, double[] distOut, double[] probsOut);
 
+    // device-resident superstep loop (the whole queue of KMeansTrainBatchOp.iterateICQ on the GPU)
+    public static native int setCentroids(long handle, double[] c0, int k0);
+    public static native int step(long handle, double tol, int[] convergedOut, int[] kOut, double[] objectiveOut);
+    public static native int getModel(long handle, double[] cOut, int[] kOut, double[] weightsOut, int[] stepsOut);
+
+    // KMeansInitCentroids.kMeansPlusPlusInit passes (include/akm.h, "Initial centroids on the device")
+    public static native int initReset(long handle);
+    public static native int initUpdate(long handle, double[] centers, int m, int idBase, double[] sumCostOut);
+    public static native int initPick(long handle, double scale, long seed, int round, long rowBase, int cap,
+                                      long[] rowsOut, int[] countOut);
+    public static native int initCounts(long handle, int mTotal, double[] countsOut);
+    public static native int getRows(long handle, long[] rowsSorted, int m, double[] out);
+
+    // EvalClusterBatchOp: per-cluster statistics + silhouette sum of the cached rows
+    public static native int evalClusters(long handle, int[] labels, int k, double[] countOut, double[] meanOut,
+                                          double[] distSumOut, double[] distSqSumOut, double[] normSqSumOut,
+                                          double[] silhouetteSumOut);
+
     public static void check(long handle, int rc) {
         if (rc != 0) {
             throw new RuntimeException("akm error " + rc + ": " + lastError(handle));
