@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <thread>
 
 #include "akm_internal.cuh"
 
@@ -91,13 +92,45 @@ static int rowstore_widen(akm_handle h, RowStore &rs) {
     return AKM_OK;
 }
 
-static int ensure_stage(akm_handle h, size_t bytes) {
+// Upload pipeline: the caller's (pageable) rows are copied into one half of a pinned buffer by a few host threads
+// while the other half is on its way to the device and through prepareVectorData, so the host copy, the DMA and
+// the kernel overlap.  (A cudaMemcpyAsync straight from pageable memory is staged by the driver at ~11 GB/s and
+// serialises with everything else.)
+constexpr size_t UPLOAD_HALF_BYTES = (size_t)64 << 20;
+constexpr int UPLOAD_THREADS = 4;
+
+static int ensure_dev_stage(akm_handle h, size_t bytes) {
     if (h->stage_bytes >= bytes) return AKM_OK;
     if (h->stage) cudaFree(h->stage);
     h->stage = nullptr; h->stage_bytes = 0;
     AKM_CUDA(h, cudaMalloc(&h->stage, bytes));
     h->stage_bytes = bytes;
     return AKM_OK;
+}
+
+static int ensure_upload_stage(akm_handle h, size_t half_bytes) {
+    AKM_TRY(ensure_dev_stage(h, 2 * half_bytes));
+    if (h->hstage_bytes < 2 * half_bytes) {
+        if (h->hstage) cudaFreeHost(h->hstage);
+        h->hstage = nullptr; h->hstage_bytes = 0;
+        AKM_CUDA(h, cudaHostAlloc(&h->hstage, 2 * half_bytes, cudaHostAllocDefault));
+        h->hstage_bytes = 2 * half_bytes;
+    }
+    for (int i = 0; i < 2; ++i)
+        if (!h->stage_free[i]) AKM_CUDA(h, cudaEventCreateWithFlags(&h->stage_free[i], cudaEventDisableTiming));
+    return AKM_OK;
+}
+
+static void host_copy_parallel(void *dst, const void *src, size_t bytes) {
+    if (bytes < ((size_t)4 << 20)) { memcpy(dst, src, bytes); return; }
+    std::thread workers[UPLOAD_THREADS - 1];
+    const size_t part = ((bytes / UPLOAD_THREADS) + 4095) & ~(size_t)4095;
+    for (int t = 1; t < UPLOAD_THREADS; ++t) {
+        const size_t off = std::min(bytes, part * t), len = std::min(bytes - off, part);
+        workers[t - 1] = std::thread([=]() { if (len) memcpy((char *)dst + off, (const char *)src + off, len); });
+    }
+    memcpy(dst, src, std::min(bytes, part));
+    for (int t = 1; t < UPLOAD_THREADS; ++t) workers[t - 1].join();
 }
 
 enum SrcKind { SRC_HOST_F64, SRC_HOST_F32, SRC_DEV_F32 };
@@ -107,14 +140,22 @@ static int upload_pass(akm_handle h, RowStore &rs, const void *src, SrcKind kind
     if (kind == SRC_DEV_F32) return launch_prep_rows(h, rs, src, true, rs.n, n);
     const size_t elt = kind == SRC_HOST_F64 ? 8 : 4;
     const size_t row_bytes = d * elt;
-    int64_t chunk = (int64_t)std::max<size_t>(1, ((size_t)64 << 20) / row_bytes);
+    int64_t chunk = (int64_t)std::max<size_t>(1, UPLOAD_HALF_BYTES / row_bytes);
     chunk = std::min<int64_t>(chunk, n);
-    AKM_TRY(ensure_stage(h, (size_t)chunk * row_bytes));
-    for (int64_t off = 0; off < n; off += chunk) {
+    const size_t half = (size_t)chunk * row_bytes;
+    AKM_TRY(ensure_upload_stage(h, half));
+    int slot = 0;
+    bool used[2] = {false, false};
+    for (int64_t off = 0; off < n; off += chunk, slot ^= 1) {
         const int64_t m = std::min<int64_t>(chunk, n - off);
-        AKM_CUDA(h, cudaMemcpyAsync(h->stage, (const char *)src + (size_t)off * row_bytes, (size_t)m * row_bytes,
-                                    cudaMemcpyHostToDevice, h->stream));
-        AKM_TRY(launch_prep_rows(h, rs, h->stage, kind == SRC_HOST_F32, rs.n + off, m));
+        char *hbuf = (char *)h->hstage + (size_t)slot * half;
+        char *dbuf = (char *)h->stage + (size_t)slot * half;
+        if (used[slot]) AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot]));     // DMA + kernel of two chunks ago are done
+        host_copy_parallel(hbuf, (const char *)src + (size_t)off * row_bytes, (size_t)m * row_bytes);
+        AKM_CUDA(h, cudaMemcpyAsync(dbuf, hbuf, (size_t)m * row_bytes, cudaMemcpyHostToDevice, h->stream));
+        AKM_TRY(launch_prep_rows(h, rs, dbuf, kind == SRC_HOST_F32, rs.n + off, m));
+        AKM_CUDA(h, cudaEventRecord(h->stage_free[slot], h->stream));
+        used[slot] = true;
     }
     return AKM_OK;
 }
@@ -357,6 +398,7 @@ int akm_destroy(akm_handle h) {
     if (h->h_iscal) cudaFreeHost(h->h_iscal);
     if (h->stage) cudaFree(h->stage);
     if (h->hstage) cudaFreeHost(h->hstage);
+    for (int i = 0; i < 2; ++i) if (h->stage_free[i]) cudaEventDestroy(h->stage_free[i]);
     if (h->reorder_scratch) cudaFree(h->reorder_scratch);
     if (h->reorder_dest) cudaFree(h->reorder_dest);
     if (h->reorder_hist) cudaFree(h->reorder_hist);
@@ -920,7 +962,7 @@ extern "C" int akm_blobs_append(akm_handle h, uint64_t seed, int k_true, double 
     if (n == 0) return AKM_OK;
     AKM_TRY(rowstore_reserve(h, h->rows, h->rows.n + n));
     const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n, ((int64_t)512 << 20) / ((int64_t)h->d * 4)));
-    AKM_TRY(ensure_stage(h, (size_t)chunk * h->d * 4));
+    AKM_TRY(ensure_dev_stage(h, (size_t)chunk * h->d * 4));
     for (int64_t off = 0; off < n; off += chunk) {
         const int64_t m = std::min<int64_t>(chunk, n - off);
         AKM_TRY(launch_blobs(h, seed, k_true, spread, sigma, nullptr, row0 + off, m, (float *)h->stage));

@@ -70,8 +70,9 @@ struct akm_handle_s {
     double *h_dscal = nullptr; int *h_iscal = nullptr;   // pinned mirrors
 
     // staging for uploads
-    void *stage = nullptr; size_t stage_bytes = 0;
-    void *hstage = nullptr; size_t hstage_bytes = 0;     // pinned
+    void *stage = nullptr; size_t stage_bytes = 0;       // device staging (two halves, used alternately)
+    void *hstage = nullptr; size_t hstage_bytes = 0;     // pinned host staging (two halves)
+    cudaEvent_t stage_free[2] = {nullptr, nullptr};      // half i of both buffers may be refilled
 
     // tensor path scratch (kernels_tensor.cu)
     void *tc = nullptr;

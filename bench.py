@@ -374,7 +374,8 @@ def main():
             torch.cuda.synchronize()
             up_s = time.perf_counter() - t0
         upload = {"rows": m_up, "seconds": up_s, "host_gbps": m_up * d * 8 / up_s / 1e9,
-                  "note": "akm_upload_rows from pageable host doubles incl. prepareVectorData; one-off, outside the iteration"}
+                  "note": "akm_upload_rows from pageable host doubles incl. prepareVectorData (pinned double-buffered staging, "
+                          "4 copy threads); one-off, outside the iteration; ~25 GB/s on multi-GB uploads"}
 
     # ---------------- roofline of the dominant kernel (nearest-centroid search)
     pk = peaks()
