@@ -133,6 +133,37 @@ static void host_copy_parallel(void *dst, const void *src, size_t bytes) {
     for (int t = 1; t < UPLOAD_THREADS; ++t) workers[t - 1].join();
 }
 
+// Device -> pageable host memory through the same pinned halves: the DMA of chunk i+1 overlaps the host copy of
+// chunk i.  Returns with the data in `host` (the stream is synchronised).
+int download_pipelined(akm_handle h, const void *dev, void *host, size_t bytes) {
+    if (bytes == 0) return AKM_OK;
+    if (bytes < ((size_t)8 << 20)) {
+        AKM_CUDA(h, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, h->stream));
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+        return AKM_OK;
+    }
+    const size_t half = (size_t)32 << 20;
+    AKM_TRY(ensure_upload_stage(h, half));
+    const size_t hh = h->hstage_bytes / 2;
+    size_t prev_off = 0, prev_len = 0;
+    int slot = 0;
+    for (size_t off = 0; off < bytes; off += half, slot ^= 1) {
+        const size_t len = std::min(half, bytes - off);
+        char *hbuf = (char *)h->hstage + (size_t)slot * hh;
+        AKM_CUDA(h, cudaMemcpyAsync(hbuf, (const char *)dev + off, len, cudaMemcpyDeviceToHost, h->stream));
+        AKM_CUDA(h, cudaEventRecord(h->stage_free[slot], h->stream));
+        if (prev_len) {
+            AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot ^ 1]));
+            host_copy_parallel((char *)host + prev_off, (char *)h->hstage + (size_t)(slot ^ 1) * hh, prev_len);
+        }
+        prev_off = off; prev_len = len;
+    }
+    slot ^= 1;                                            // the slot of the last chunk
+    AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot]));
+    host_copy_parallel((char *)host + prev_off, (char *)h->hstage + (size_t)slot * hh, prev_len);
+    return AKM_OK;
+}
+
 enum SrcKind { SRC_HOST_F64, SRC_HOST_F32, SRC_DEV_F32 };
 
 static int upload_pass(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n) {

@@ -125,6 +125,10 @@ int akm_fail(akm_handle h, int code, const std::string &msg);
         if (rc__ != AKM_OK) return rc__; \
     } while (0)
 
+// ---------------------------------------------------------------- akm_api.cu
+// device -> pageable host copy through the pinned staging halves (synchronises the handle's stream)
+int download_pipelined(akm_handle h, const void *dev, void *host, size_t bytes);
+
 // ---------------------------------------------------------------- kernels_exact.cu
 // prepareVectorData over `n` staged rows (src: double or float, row-major) appended at row `row0`.
 int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n);

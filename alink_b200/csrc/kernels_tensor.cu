@@ -805,24 +805,52 @@ refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xla
     }
 }
 
-// distance of each row to its final centroid in the exact Java order (predictionDistanceCol)
+// distance of each row to its final centroid in the exact Java order (predictionDistanceCol).  One thread per
+// row; the dot product is summed strictly in index order (separate multiply and add, like F2J dgemv), but the
+// operands arrive 32 bytes at a time with 128-bit loads (a thread-per-row kernel is bound by the number of load
+// instructions, not by bytes).  Neighbouring rows of a cluster-ordered partition share the centroid row.
 template <typename T, int METRIC>
-__global__ void winner_distance_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int64_t n, int d,
-                                       const double *__restrict__ C, const double *__restrict__ clabel,
-                                       const int32_t *__restrict__ labels, double *__restrict__ mind) {
+__global__ void __launch_bounds__(128)
+winner_distance_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int64_t n, int d,
+                       const double *__restrict__ C, const double *__restrict__ clabel,
+                       const int32_t *__restrict__ labels, double *__restrict__ mind) {
     int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    constexpr int STEP = 32 / (int)sizeof(T);
+    const bool vec = (d % STEP) == 0;                    // rows 32-byte aligned, centroid rows 16-byte aligned
     for (; row < n; row += stride) {
         const int j = labels[row];
         if (j < 0) { mind[row] = nan(""); continue; }
         const T *x = X + row * d;
         const double *c = C + (size_t)j * d;
+        const double rinv = RawCosine<T, METRIC>::value ? cos_inv(xlabel[row]) : 1.0;
         double t = 0.0;
-        if (RawCosine<T, METRIC>::value) {
-            const double rinv = cos_inv(xlabel[row]);
-            for (int i = 0; i < d; ++i) t = __dadd_rn(t, __dmul_rn(c[i], __dmul_rn(rinv, (double)x[i])));
+        if (vec) {
+            for (int i = 0; i < d; i += STEP) {
+                const int4 r0 = reinterpret_cast<const int4 *>(x + i)[0], r1 = reinterpret_cast<const int4 *>(x + i)[1];
+                double xv[STEP];
+                if (sizeof(T) == 4) {
+                    xv[0] = __int_as_float(r0.x); xv[1] = __int_as_float(r0.y); xv[2] = __int_as_float(r0.z); xv[3] = __int_as_float(r0.w);
+                    xv[4 % STEP] = __int_as_float(r1.x); xv[5 % STEP] = __int_as_float(r1.y);
+                    xv[6 % STEP] = __int_as_float(r1.z); xv[7 % STEP] = __int_as_float(r1.w);
+                } else {
+                    xv[0] = __hiloint2double(r0.y, r0.x); xv[1] = __hiloint2double(r0.w, r0.z);
+                    xv[2 % STEP] = __hiloint2double(r1.y, r1.x); xv[3 % STEP] = __hiloint2double(r1.w, r1.z);
+                }
+#pragma unroll
+                for (int u = 0; u < STEP; u += 2) {
+                    const double2 cv = *reinterpret_cast<const double2 *>(c + i + u);
+                    const double a0 = RawCosine<T, METRIC>::value ? __dmul_rn(rinv, xv[u]) : xv[u];
+                    const double a1 = RawCosine<T, METRIC>::value ? __dmul_rn(rinv, xv[u + 1]) : xv[u + 1];
+                    t = __dadd_rn(t, __dmul_rn(cv.x, a0));
+                    t = __dadd_rn(t, __dmul_rn(cv.y, a1));
+                }
+            }
         } else {
-            for (int i = 0; i < d; ++i) t = __dadd_rn(t, __dmul_rn(c[i], (double)x[i]));
+            for (int i = 0; i < d; ++i) {
+                const double a = RawCosine<T, METRIC>::value ? __dmul_rn(rinv, (double)x[i]) : (double)x[i];
+                t = __dadd_rn(t, __dmul_rn(c[i], a));
+            }
         }
         double D;
         if (METRIC == AKM_EUCLIDEAN) {
@@ -1107,13 +1135,13 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     AKM_CUDA(h, cudaGetLastError());
     AKM_TRY(launch_assign_exact_list(h, rs, c->exact_rows, c->counters + 1, C, clabel, k0, k, labels));
     if (mind) {
-        const int wb = h->num_sms * 8;
+        const int wb = h->num_sms * 16;
         if (h->metric == AKM_EUCLIDEAN) {
-            if (rs.store == 4) winner_distance_kernel<float, AKM_EUCLIDEAN><<<wb, 256, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, d, C, clabel, labels, mind);
-            else winner_distance_kernel<double, AKM_EUCLIDEAN><<<wb, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+            if (rs.store == 4) winner_distance_kernel<float, AKM_EUCLIDEAN><<<wb, 128, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+            else winner_distance_kernel<double, AKM_EUCLIDEAN><<<wb, 128, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
         } else {
-            if (rs.store == 4) winner_distance_kernel<float, AKM_COSINE><<<wb, 256, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, d, C, clabel, labels, mind);
-            else winner_distance_kernel<double, AKM_COSINE><<<wb, 256, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+            if (rs.store == 4) winner_distance_kernel<float, AKM_COSINE><<<wb, 128, 0, h->stream>>>(rs.x32, rs.xlabel, rs.n, d, C, clabel, labels, mind);
+            else winner_distance_kernel<double, AKM_COSINE><<<wb, 128, 0, h->stream>>>(rs.x64, rs.xlabel, rs.n, d, C, clabel, labels, mind);
         }
         h->stats.kernel_launches++;
         AKM_CUDA(h, cudaGetLastError());

@@ -224,11 +224,8 @@ int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *us
 template <typename V>
 static int copy_out_impl(akm_handle h, const RowStore &rs, const V *dev, V *host, int64_t n) {
     if (n <= 0) return AKM_OK;
-    if (!rs.reordered || !rs.orig) {
-        AKM_CUDA(h, cudaMemcpyAsync(host, dev, sizeof(V) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
-        return AKM_OK;
-    }
     const size_t need = sizeof(V) * (size_t)n;
+    if (!rs.reordered || !rs.orig) return download_pipelined(h, dev, host, need);
     if (h->reorder_scratch_bytes < need) {
         if (h->reorder_scratch) cudaFree(h->reorder_scratch);
         h->reorder_scratch = nullptr; h->reorder_scratch_bytes = 0;
@@ -238,8 +235,7 @@ static int copy_out_impl(akm_handle h, const RowStore &rs, const V *dev, V *host
     unpermute_kernel<V><<<h->num_sms * 8, 256, 0, h->stream>>>(dev, rs.orig, n, (V *)h->reorder_scratch);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
-    AKM_CUDA(h, cudaMemcpyAsync(host, h->reorder_scratch, need, cudaMemcpyDeviceToHost, h->stream));
-    return AKM_OK;
+    return download_pipelined(h, h->reorder_scratch, host, need);
 }
 
 int copy_rows_out_i32(akm_handle h, const RowStore &rs, const int32_t *dev, int32_t *host, int64_t n) {
