@@ -90,7 +90,10 @@ int akm_reserve_rows(akm_handle h, int64_t n_total);
  * (EuclideanDistance.java:59-65), COSINE x <- x * (1/||x||) when ||x|| > 0 (CosineDistance.java:60-65).
  * Replaces the List<FastDistanceVectorData> "trainData" cached by the ComQueue
  * (BaseComQueue.java:497-527).  Rows whose values are all exactly representable in fp32 are kept
- * as fp32 (4 B/value); the first value that is not switches the partition to fp64 losslessly. */
+ * as fp32 (4 B/value); the first value that is not switches the partition to fp64 losslessly.  (A COSINE
+ * fp32 partition keeps the raw values and forms x * (1/||x||) wherever it reads them, which is the same
+ * double Java stores.)  The host rows are staged through a pinned double buffer; the call returns when
+ * they are resident. */
 int akm_upload_rows(akm_handle h, const double *x_host, int64_t n);
 
 /* Same for fp32 host rows (values widened exactly). */
