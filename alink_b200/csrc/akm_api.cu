@@ -112,6 +112,7 @@ static int ensure_upload_stage(akm_handle h, size_t half_bytes) {
     AKM_TRY(ensure_dev_stage(h, 2 * half_bytes));
     if (h->hstage_bytes < 2 * half_bytes) {
         if (h->hstage) cudaFreeHost(h->hstage);
+    if (h->pin) cudaFreeHost(h->pin);
         h->hstage = nullptr; h->hstage_bytes = 0;
         AKM_CUDA(h, cudaHostAlloc(&h->hstage, 2 * half_bytes, cudaHostAllocDefault));
         h->hstage_bytes = 2 * half_bytes;
@@ -162,6 +163,45 @@ int download_pipelined(akm_handle h, const void *dev, void *host, size_t bytes) 
     AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot]));
     host_copy_parallel((char *)host + prev_off, (char *)h->hstage + (size_t)slot * hh, prev_len);
     return AKM_OK;
+}
+
+// ---- small host buffers of the per-superstep calls go through a pinned arena: every copy is truly asynchronous
+// and the call synchronises once; results reach the caller's memory in pin_finish().
+static int pin_begin(akm_handle h, size_t total_bytes) {
+    h->pin_off = 0;
+    h->pin_out.clear();
+    total_bytes += 1024;
+    if (h->pin_bytes >= total_bytes) return AKM_OK;
+    if (h->pin) cudaFreeHost(h->pin);
+    h->pin = nullptr; h->pin_bytes = 0;
+    AKM_CUDA(h, cudaHostAlloc((void **)&h->pin, total_bytes, cudaHostAllocDefault));
+    h->pin_bytes = total_bytes;
+    return AKM_OK;
+}
+static char *pin_take(akm_handle h, size_t bytes) {
+    const size_t off = (h->pin_off + 63) & ~(size_t)63;
+    if (off + bytes > h->pin_bytes) return nullptr;
+    h->pin_off = off + bytes;
+    return h->pin + off;
+}
+static int pin_h2d(akm_handle h, void *dev, const void *host, size_t bytes) {
+    char *b = pin_take(h, bytes);
+    if (!b) { AKM_CUDA(h, cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, h->stream)); return AKM_OK; }
+    memcpy(b, host, bytes);
+    AKM_CUDA(h, cudaMemcpyAsync(dev, b, bytes, cudaMemcpyHostToDevice, h->stream));
+    return AKM_OK;
+}
+static int pin_d2h(akm_handle h, void *host, const void *dev, size_t bytes) {
+    char *b = pin_take(h, bytes);
+    if (!b) { AKM_CUDA(h, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, h->stream)); return AKM_OK; }
+    AKM_CUDA(h, cudaMemcpyAsync(b, dev, bytes, cudaMemcpyDeviceToHost, h->stream));
+    h->pin_out.push_back({host, b, bytes});
+    return AKM_OK;
+}
+// after the stream has been synchronised
+static void pin_finish(akm_handle h) {
+    for (const auto &o : h->pin_out) memcpy(o.dst, o.src, o.bytes);
+    h->pin_out.clear();
 }
 
 enum SrcKind { SRC_HOST_F64, SRC_HOST_F32, SRC_DEV_F32 };
@@ -429,6 +469,7 @@ int akm_destroy(akm_handle h) {
     if (h->h_iscal) cudaFreeHost(h->h_iscal);
     if (h->stage) cudaFree(h->stage);
     if (h->hstage) cudaFreeHost(h->hstage);
+    if (h->pin) cudaFreeHost(h->pin);
     for (int i = 0; i < 2; ++i) if (h->stage_free[i]) cudaEventDestroy(h->stage_free[i]);
     if (h->reorder_scratch) cudaFree(h->reorder_scratch);
     if (h->reorder_dest) cudaFree(h->reorder_dest);
@@ -515,15 +556,17 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
         return AKM_OK;
     }
     AKM_TRY(ensure_labels(h, h->rows.n));
-    AKM_CUDA(h, cudaMemcpyAsync(s->c[0], centroids, sizeof(double) * (size_t)k0 * d, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(pin_begin(h, sizeof(double) * ((size_t)k0 * d + L)));
+    AKM_TRY(pin_h2d(h, s->c[0], centroids, sizeof(double) * (size_t)k0 * d));
     AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, /*cos_normalise=*/false));
     AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], k0, k, h->labels, nullptr, /*chain=*/2, nullptr));
     AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], s->l[0], k0, s->sum, s->sum + L));
-    AKM_CUDA(h, cudaMemcpyAsync(sum_out, s->sum, sizeof(double) * L, cudaMemcpyDeviceToHost, h->stream));
+    AKM_TRY(pin_d2h(h, sum_out, s->sum, sizeof(double) * L));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 5 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     if (labels_out) AKM_TRY(copy_rows_out_i32(h, h->rows, h->labels, labels_out, h->rows.n));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    pin_finish(h);
     absorb_tensor_stats(h);
     if (objective_out) *objective_out = h->h_dscal[0];
     AKM_TRY(check_error_flag(h));
@@ -539,21 +582,28 @@ int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int ste
     const size_t L = (size_t)k0 * (size_t)(d + 1);
     AKM_TRY(ensure_scratch(h, k0));
     Scratch *s = scratch_of(h);
-    AKM_CUDA(h, cudaMemcpyAsync(s->sum, sum, sizeof(double) * L, cudaMemcpyHostToDevice, h->stream));
+    AKM_TRY(pin_begin(h, sizeof(double) * (L + 2 * (size_t)k0 * d + (size_t)k0)));
+    AKM_TRY(pin_h2d(h, s->sum, sum, sizeof(double) * L));
     const double *dprev = nullptr, *lprev = nullptr;
     if (prev) {
-        AKM_CUDA(h, cudaMemcpyAsync(s->c[0], prev, sizeof(double) * (size_t)k0 * d, cudaMemcpyHostToDevice, h->stream));
+        AKM_TRY(pin_h2d(h, s->c[0], prev, sizeof(double) * (size_t)k0 * d));
         AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, false));
         dprev = s->c[0]; lprev = s->l[0];
     }
     // the buffer written at step s is CENTROID1 when s is odd (KMeansUpdateCentroids.java:38-42)
     AKM_TRY(launch_update(h, s->sum, k, k0, s->c[1], s->l[1], dprev, lprev, (step_no % 2) != 0, 0.0, h->shift, h->iscal));
-    AKM_CUDA(h, cudaMemcpyAsync(c_out, s->c[1], sizeof(double) * (size_t)k0 * d, cudaMemcpyDeviceToHost, h->stream));
+    AKM_TRY(pin_d2h(h, c_out, s->c[1], sizeof(double) * (size_t)k0 * d));
+    // the first *k_out entries of shift are meaningful; k_out is not known before the sync, so fetch k entries
+    // (k_out <= k) into the arena and hand over the valid prefix afterwards
+    char *shift_pin = (shift_out && prev && k > 0) ? pin_take(h, sizeof(double) * (size_t)k) : nullptr;
+    if (shift_pin) AKM_CUDA(h, cudaMemcpyAsync(shift_pin, h->shift, sizeof(double) * (size_t)k, cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    pin_finish(h);
     *k_out = h->h_iscal[0];
     if (shift_out && prev && *k_out > 0) {
-        AKM_CUDA(h, cudaMemcpy(shift_out, h->shift, sizeof(double) * (size_t)(*k_out), cudaMemcpyDeviceToHost));
+        if (shift_pin) memcpy(shift_out, shift_pin, sizeof(double) * (size_t)(*k_out));
+        else AKM_CUDA(h, cudaMemcpy(shift_out, h->shift, sizeof(double) * (size_t)(*k_out), cudaMemcpyDeviceToHost));
     }
     return AKM_OK;
 }

@@ -73,6 +73,11 @@ struct akm_handle_s {
     void *stage = nullptr; size_t stage_bytes = 0;       // device staging (two halves, used alternately)
     void *hstage = nullptr; size_t hstage_bytes = 0;     // pinned host staging (two halves)
     cudaEvent_t stage_free[2] = {nullptr, nullptr};      // half i of both buffers may be refilled
+    // pinned bounce arena for the few-MB host buffers of the per-superstep calls (centroids, accumulator):
+    // copies from/to pageable memory would be staged by the driver and block the calling thread one by one
+    char *pin = nullptr; size_t pin_bytes = 0, pin_off = 0;
+    struct PendingOut { void *dst; const void *src; size_t bytes; };
+    std::vector<PendingOut> pin_out;
 
     // tensor path scratch (kernels_tensor.cu)
     void *tc = nullptr;
