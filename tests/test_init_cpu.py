@@ -53,6 +53,21 @@ def test_pick_weight_matches_the_reference_loop():
         assert init_mod.pick_weight(w, c, a) == literal(w, c, b.next_double())
 
 
+def test_local_kmeans_reproduces_the_reference_junit_values():
+    # TEST/operator/common/clustering/kmeans/LocalKmeansFuncTest.java:19-34 (dense) and :36-54 (sparse): samples
+    # i * ones, weights i, k = 2 -> centroid norms.  Pins the weighted k-means++ picks (new Random(0)), pickWeight's
+    # off-by-one and the never-cleared sum matrix all at once.
+    w = np.arange(10, dtype=np.float64)
+    dense = np.array([[i, i] for i in range(10)], dtype=np.float64)
+    C = init_mod.local_kmeans(2, w, dense, orc.EUCLIDEAN)
+    assert abs(np.linalg.norm(C[0]) - 10.842) < 0.001 and abs(np.linalg.norm(C[1]) - 5.185) < 0.001
+    sparse = np.zeros((10, 20))
+    for i in range(10):
+        sparse[i, i] = sparse[i, i + 1] = i
+    C = init_mod.local_kmeans(2, w, sparse, orc.EUCLIDEAN)
+    assert abs(np.linalg.norm(C[0]) - 8.615) < 0.001 and abs(np.linalg.norm(C[1]) - 4.128) < 0.001
+
+
 @pytest.mark.parametrize("metric", [orc.EUCLIDEAN, orc.COSINE])
 def test_local_kmeans_finds_the_blobs(metric):
     k, d = 6, 8
