@@ -73,6 +73,18 @@ def test_model_wire_format_roundtrip_and_reference_fixture(golden):
     legacy = [rows[0], [1048576, '{"clusterId":0,"weight":3.0,"center":"{\\"data\\":[9.1,9.1,9.1]}"}'],
               [2097152, '{"clusterId":1,"weight":3.0,"center":"[0.1,0.1,0.1]"}']]
     assert model_io.load_model(legacy)["centroids"].tolist() == [[9.1, 9.1, 9.1], [0.1, 0.1, 0.1]]
+    # the literal fixtures of KMeansOldModelMapper1Test.java:19-26 and KMeansOldModelMapper2Test.java:19-25
+    old1 = [[0, '{"vectorCol":"\\"Y\\"","latitudeCol":null,"longitudeCol":null,"distanceType":"\\"EUCLIDEAN\\"","k":"2",'
+                '"modelSchema":"\\"model_id bigint,model_info string\\"","isNewFormat":"true","vectorSize":"3"}'],
+            [1048576, '{"center":"{\\"data\\":[9.1,9.1,9.1]}","clusterId":0,"weight":3.0}'],
+            [2097152, '{"center":"{\\"data\\":[0.1,0.1,0.1]}","clusterId":1,"weight":3.0}']]
+    old2 = [[0, '{"vectorCol":"\\"Y\\"","latitudeCol":null,"longitudeCol":null,"distanceType":"\\"EUCLIDEAN\\"","k":"2","vectorSize":"3"}'],
+            [1048576, '{"clusterId":0,"weight":3.0,"center":"[9.1, 9.1, 9.1]","vec":null}'],
+            [2097152, '{"clusterId":1,"weight":3.0,"center":"[0.1, 0.1, 0.1]","vec":null}']]
+    for fixture in (old1, old2):
+        m = model_io.load_model(fixture)
+        assert m["k"] == 2 and m["vectorSize"] == 3 and m["distanceType"] == "EUCLIDEAN" and m["vectorCol"] == "Y"
+        assert m["centroids"].tolist() == [[9.1, 9.1, 9.1], [0.1, 0.1, 0.1]] and m["clusterIds"].tolist() == [0, 1]
     # long vectors are sliced at 32 KiB and reassembled by model_id
     big = np.arange(6000, dtype=np.float64)[None, :] + 0.5
     sl = model_io.save_model(big, [1.0], 1, 6000, "COSINE", "v")
