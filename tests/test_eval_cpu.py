@@ -55,3 +55,27 @@ def test_host_remainder_matches_the_oracle():
                      ("daviesBouldin", "davies_bouldin"), ("calinskiHarabaz", "calinski_harabaz"),
                      ("silhouetteCoefficient", "silhouette")):
             assert abs(m[a] - r[b]) <= 1e-10 * max(1.0, abs(r[b])), (a, m[a], r[b])
+
+
+def test_cluster_statistics_junit_values():
+    # TEST/operator/common/evaluation/ClusterEvaluationUtilTest.java:36-76
+    r = orc.eval_clusters(orc.EUCLIDEAN, POINTS[:3], np.zeros(3, dtype=int), 1)
+    assert r["count"][0] == 3 and abs(r["compactness"][0] - 0.115) < 0.001
+    assert abs(r["dist_sq_sum"][0] - 0.06) < 0.01 and abs(r["norm_sq_sum"][0] - 0.15) < 0.01
+    np.testing.assert_allclose(r["mean"][0], [0.1, 0.1, 0.1], rtol=0, atol=1e-15)
+    r = orc.eval_clusters(orc.COSINE, POINTS[3:], np.zeros(3, dtype=int), 1)
+    assert r["count"][0] == 3 and abs(r["compactness"][0]) < 0.001 and abs(r["dist_sq_sum"][0]) < 0.01
+    assert abs(r["norm_sq_sum"][0] - 3.0) < 0.01 and abs((r["mean"][0] ** 2).sum() - 1.0) < 0.01
+
+
+def test_confusion_matrix_junit_values():
+    # ClusterEvaluationUtilTest.java:104-114: matrix {{5,1,2},{1,4,0},{0,1,3}}, rows = predictions, columns = labels
+    mat = [[5, 1, 2], [1, 4, 0], [0, 1, 3]]
+    act, pred = [], []
+    for i, row in enumerate(mat):
+        for j, c in enumerate(row):
+            act += ["a%d" % j] * c
+            pred += ["p%d" % i] * c
+    m = label_metrics(act, pred)
+    assert abs(m["NMI"] - 0.364) < 0.001 and abs(m["purity"] - 0.705) < 0.001
+    assert abs(m["RI"] - 0.68) < 0.01 and abs(m["ARI"] - 0.24) < 0.01
