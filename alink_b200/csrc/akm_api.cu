@@ -365,6 +365,9 @@ static void absorb_tensor_stats(akm_handle h) {
         h->stats.rows_refined = h->h_iscal[4];
         h->stats.rows_certified = h->stats.rows - h->h_iscal[4];
         h->stats.rows_exact_all = h->h_iscal[5];
+        h->stats.tiles_computed = h->h_iscal[7];
+    } else {
+        h->stats.tiles_total = h->stats.tiles_computed = 0;
     }
 }
 
@@ -563,7 +566,7 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
     AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], s->l[0], k0, s->sum, s->sum + L));
     AKM_TRY(pin_d2h(h, sum_out, s->sum, sizeof(double) * L));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 5 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 6 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     if (labels_out) AKM_TRY(copy_rows_out_i32(h, h->rows, h->labels, labels_out, h->rows.n));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     pin_finish(h);
@@ -648,7 +651,7 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     AKM_TRY(launch_update(h, h->sum, h->k, k0, h->cent[wr], h->clabel[wr], h->cent[rd], h->clabel[rd],
                           /*new_is_c1=*/wr == 0, tol, h->shift, h->iscal));
     if (prof) cudaEventRecord(h->pev[3], h->stream);
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 7 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 8 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     absorb_tensor_stats(h);
@@ -746,7 +749,7 @@ static int predict_store(akm_handle h, RowStore &rs, const double *dC, const dou
     AKM_TRY(launch_labels_to_i64(h, h->labels, n, s->idx64));
     AKM_TRY(copy_rows_out_i64(h, rs, s->idx64, idx_out, n));
     if (dist_out) AKM_TRY(copy_rows_out_f64(h, rs, h->mind, dist_out, n));
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 6 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     if (!probs_out) absorb_tensor_stats(h);
     if (h->h_iscal[2] != 0) {
@@ -846,7 +849,7 @@ int akm_init_update(akm_handle h, const double *centers, int m, int id_base, dou
     }
     AKM_TRY(launch_init_merge(h, n, h->labels, h->mind, id_base, h->init_cost, h->init_near, h->dscal));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->dscal, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 6 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     absorb_tensor_stats(h);
     AKM_TRY(check_error_flag(h));
@@ -1076,5 +1079,6 @@ extern "C" int akm_blobs_rows(akm_handle h, uint64_t seed, int k_true, double sp
 extern "C" int akm_set_option(akm_handle h, const char *name, double value) {
     if (!h || !name) return akm_fail(h, AKM_ERR_BADARG, "null argument");
     if (strcmp(name, "reorder_min_rows") == 0) { h->reorder_min_rows = (int64_t)value; return AKM_OK; }
+    if (strcmp(name, "tile_pruning") == 0) { h->tile_pruning = value != 0.0; return AKM_OK; }
     return akm_fail(h, AKM_ERR_BADARG, std::string("unknown option: ") + name);
 }

@@ -99,6 +99,7 @@ struct akm_handle_s {
     int reorders = 0;
     double reorder_ms = 0;
     int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
+    bool tile_pruning = true;             // skip (row group, centroid tile) pairs the triangle inequality rules out
 
     // optional per-phase profiling of akm_step
     bool profiling = false;

@@ -115,13 +115,14 @@ struct SearchParams {
     int32_t *labels;
     int32_t *wl_rows;       // worklist: rows that need exact work
     int32_t *wl_cand;       // WL_CAND candidates per entry (-1 = unused, first == -2: all centroids)
-    int *counters;          // [0] reserved worklist slots, [2] labels changed, [3] worklist entries used
+    int *counters;          // [0] reserved worklist slots, [2] labels changed, [3] worklist entries used, [4] tiles produced
     float eta;              // accumulation error factor
     // seeds: a rigorous upper bound of this pass's minimum score per row, derived from the previous pass
     float *useed;           // in: previous pass min score + its error bound; out: same for this pass (nullable)
     const float *sig_old;   // per OLD label: distance its centroid moved (INF if the cluster was dropped)
     int k_prev;             // 0: no seeds this pass
     const float2 *wm;       // per row {window W, seeded upper bound of the minimum score (INF: none)} from rowprep_kernel
+    const uint32_t *gmask;  // per 256-row group: bit t set = centroid tile t must be evaluated (nullptr: all tiles)
 };
 
 // ------------------------------------------------------------------------------------------ per-row window / seed
@@ -131,43 +132,102 @@ struct SearchParams {
 //   W  = 2.004 * B + 2 * eps_J   (NaN when the centroids are not finite -> every row goes exact)
 //   m0 = rigorous upper bound of this pass's minimum approximate score (INF when there is no seed):
 //        the previous winner a had true score <= useed; its centroid moved by sig_old[a].
-__global__ void rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restrict__ pc,
-                               const float2 *__restrict__ xerr, int32_t *__restrict__ labels,
-                               const float *__restrict__ useed, const float *__restrict__ sig_old, int k_prev,
-                               const int *__restrict__ remap, float2 *__restrict__ wm) {
+//
+// Tile pruning (Elkan's lemma at the granularity the tensor cores work at).  With a seed, ub bounds the distance
+// of the row to its previous centroid a at its new position; every centroid j of a 256-centroid tile T is at
+// least dmin[a][T] away from c_a, hence at least dmin - ub away from the row.  If
+//     dmin * (dmin - 2 ub) > 2 B + W            (EUCLIDEAN; twice that for COSINE, whose score is half the
+//                                                squared chord between unit vectors)
+// no score of the tile can come within the window of the row's minimum, so the tile holds neither the argmin nor
+// a candidate.  A tile is skipped for a 256-row group when that holds for every row of the group; rows of a
+// cluster-ordered partition share their previous centroid, so whole groups agree.  gmask[g] = OR of the rows' masks.
+__global__ void __launch_bounds__(256)
+rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restrict__ pc,
+               const float2 *__restrict__ xerr, int32_t *__restrict__ labels,
+               const float *__restrict__ useed, const float *__restrict__ sig_old, int k_prev,
+               const int *__restrict__ remap, float2 *__restrict__ wm,
+               const float *__restrict__ dmin, int ntiles, int k, uint32_t *__restrict__ gmask) {
     const float c16_max = pc->c16_max, dc_max = pc->dc_max, c_max = pc->c_max;
     const bool bad = pc->bad != 0;
-    int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; row < n; row += stride) {
-        const float2 xe = xerr[row];
-        const float r = xe.x, er = xe.y;
-        const float rc = r + c_max;
-        // |S - true| <= 2(|dx||c16| + |x||dc|) + 2 eta |x16||c16| + fp32 epilogue rounding
-        const float B = 2.f * (er * c16_max + r * dc_max) + 2.f * eta * (r + er) * c16_max + 4.8e-7f * rc * rc;
-        const float epsJ = (float)(d + 16) * 4.5e-16f * rc * rc;    // Java's own fp64 rounding
-        float W = 2.004f * B + 2.f * epsJ + 1e-30f;
-        if (bad) W = NAN;
-        float m0 = INFINITY;
-        if (k_prev > 0) {
-            const int a = labels[row];
-            if (a >= 0 && a < k_prev) {
-                const float sg_a = sig_old[a], u0 = useed[row];
-                float u;
-                if (metric == AKM_EUCLIDEAN) {
-                    const float r2 = r * r;
-                    const float t = sqrtf(fmaxf(u0 + r2 * 1.000001f, 0.f)) * 1.000001f + sg_a;
-                    u = t * t * 1.000001f - r2 * 0.999998f + 0.5f * W + 1e-5f * (t * t + r2);
-                } else {
-                    u = u0 + sg_a * (r + er) * 1.000001f + 0.5f * W + 1e-6f;
+    const int64_t ngroups = (n + 255) / 256;
+    const uint32_t all_tiles = ntiles >= 32 ? 0xFFFFFFFFu : ((1u << ntiles) - 1u);
+    for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
+        const int64_t row = g * 256 + threadIdx.x;
+        uint32_t mask = 0;
+        if (row < n) {
+            const float2 xe = xerr[row];
+            const float r = xe.x, er = xe.y;
+            const float rc = r + c_max;
+            // |S - true| <= 2(|dx||c16| + |x||dc|) + 2 eta |x16||c16| + fp32 epilogue rounding
+            const float B = 2.f * (er * c16_max + r * dc_max) + 2.f * eta * (r + er) * c16_max + 4.8e-7f * rc * rc;
+            const float epsJ = (float)(d + 16) * 4.5e-16f * rc * rc;    // Java's own fp64 rounding
+            float W = 2.004f * B + 2.f * epsJ + 1e-30f;
+            if (bad) W = NAN;
+            float m0 = INFINITY;
+            mask = all_tiles;
+            if (k_prev > 0) {
+                const int a = labels[row];
+                if (a >= 0 && a < k_prev) {
+                    const float sg_a = sig_old[a], u0 = useed[row];
+                    float u, ub;                                    // ub: distance (COSINE: chord) to c_a, rounded up
+                    if (metric == AKM_EUCLIDEAN) {
+                        const float r2 = r * r;
+                        const float t = sqrtf(fmaxf(u0 + r2 * 1.000001f, 0.f)) * 1.000001f + sg_a;
+                        u = t * t * 1.000001f - r2 * 0.999998f + 0.5f * W + 1e-5f * (t * t + r2);
+                        ub = t;
+                    } else {
+                        u = u0 + sg_a * (r + er) * 1.000001f + 0.5f * W + 1e-6f;
+                        ub = sqrtf(fmaxf(2.f + 2.f * u, 0.f)) * 1.000001f + 1e-6f;
+                        if (!(fabsf(r - 1.f) < 1e-5f)) ub = INFINITY;   // not a unit vector (zero row): no pruning
+                    }
+                    if (u == u) m0 = u;                                 // NaN: no seed
+                    const int ja = remap ? remap[a] : a;                // this pass's numbering (-1: cluster dropped)
+                    if (dmin != nullptr && ja >= 0 && ja < k && u == u && ub < 3.0e37f && W == W) {
+                        const float rhs = ((metric == AKM_EUCLIDEAN) ? 2.f : 4.f) * W * 1.01f + 1e-30f;
+                        mask = 1u << (ja / 256);                       // its own tile is always evaluated
+                        for (int t = 0; t < ntiles; ++t) {
+                            const float dm = dmin[(size_t)ja * ntiles + t];
+                            const float lhs = dm * (dm - 2.f * ub) * 0.999999f;
+                            if (!(dm > 2.f * ub && lhs > rhs)) mask |= 1u << t;
+                        }
+                    }
+                    // express the old label in this pass's cluster numbering (empty clusters were compacted away),
+                    // so the search kernel can tell which rows really changed cluster
+                    if (remap) labels[row] = remap[a];
                 }
-                if (u == u) m0 = u;                                 // NaN: no seed
-                // express the old label in this pass's cluster numbering (empty clusters were compacted away),
-                // so the search kernel can tell which rows really changed cluster
-                if (remap) labels[row] = remap[a];
             }
+            wm[row] = make_float2(W, m0);
         }
-        wm[row] = make_float2(W, m0);
+        if (gmask != nullptr) {
+            mask = __reduce_or_sync(0xffffffffu, mask);
+            if ((threadIdx.x & 31) == 0 && mask) atomicOr(gmask + g, mask);
+        }
+    }
+}
+
+// dmin[a][T] = min over the centroids j != a of tile T of |c_a - c_j| (COSINE: C holds unit vectors, so this is
+// the chord), rounded down.  One warp per centroid a; k*k*d flops, done once per pass.
+__global__ void __launch_bounds__(256)
+centroid_tile_dist_kernel(const double *__restrict__ C, int k, int d, int ntiles, float *__restrict__ dmin) {
+    const int lane = threadIdx.x & 31;
+    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (a >= k) return;
+    const double *ca = C + (size_t)a * d;
+    for (int t = 0; t < ntiles; ++t) {
+        double best = INFINITY;
+        const int j1 = min(k, (t + 1) * 256);
+        for (int j = t * 256; j < j1; ++j) {
+            if (j == a) continue;
+            const double *cj = C + (size_t)j * d;
+            double s2 = 0.0;
+            for (int i = lane; i < d; i += 32) { const double df = ca[i] - cj[i]; s2 = fma(df, df, s2); }
+            for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            best = fmin(best, s2);
+        }
+        if (lane == 0) {
+            float f = (best == best && best < 1e300) ? __double2float_rd(sqrt(best) * (1.0 - 1e-9)) : ((best == best) ? 3.0e38f : 0.f);
+            dmin[(size_t)a * ntiles + t] = f;
+        }
     }
 }
 
@@ -282,8 +342,9 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 int s_i = 0, ph = 0;
                 for (int g = pair_id; g < ngroups; g += npairs) {
                     const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
+                    const uint32_t gm = p.gmask ? p.gmask[g] : 0xFFFFFFFFu;
                     for (int t = 0; t < nt; ++t)
-                        for (int kb = 0; kb < nkb; ++kb) {
+                        for (int kb = 0; kb < nkb && ((gm >> t) & 1u); ++kb) {
                             mbar_wait(smem_u32(a_empty + s_i), ph ^ 1);
                             if (leader) mbar_expect_tx(smem_u32(a_full + s_i), 2u * A_STAGE);
                             const uint32_t full_leader = smem_u32(a_full + s_i) & PEER_BIT_MASK;
@@ -321,9 +382,12 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             if constexpr (STREAM) {
                 int s_i = 0, ph = 0, t_it = 0;
                 for (int g = pair_id; g < ngroups; g += npairs) {
-                    for (int t = 0; t < nt; ++t, ++t_it) {
+                    const uint32_t gm = p.gmask ? p.gmask[g] : 0xFFFFFFFFu;
+                    for (int t = 0; t < nt; ++t) {
+                        if (!((gm >> t) & 1u)) continue;            // pruned for this group (rowprep_kernel)
                         const int tb = t_it & 1;
                         mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
+                        ++t_it;
                         tc_fence_after();
                         const uint32_t d0 = tmem_base + (uint32_t)(tb * PAIR_N);
                         for (int kb = 0; kb < nkb; ++kb) {
@@ -343,16 +407,22 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                         }
                     }
                 }
+                if (lane == 0 && t_it) atomicAdd(p.counters + 4, t_it);   // accumulator tiles produced by this pair
             } else {
                 const uint32_t b_lo0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) | (1u << 16);
                 mbar_wait(smem_u32(b_full), 0);
                 int it = 0, t_it = 0;
+                uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
                 for (int g = pair_id; g < ngroups; g += npairs, ++it) {
                     const int as = it & 1;
+                    const uint32_t gm = gm_next;
+                    if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
                     mbar_wait(smem_u32(a_full + as), (it >> 1) & 1);
-                    for (int t = 0; t < nt; ++t, ++t_it) {
+                    for (int t = 0; t < nt; ++t) {
+                        if (!((gm >> t) & 1u)) continue;            // pruned for this group (rowprep_kernel)
                         const int tb = t_it & 1;
                         mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
+                        ++t_it;
                         tc_fence_after();
                         if (lane == 0) {
                             const uint32_t a_lo = a_lo0 + (uint32_t)as * (A_STAGE >> 4);
@@ -372,6 +442,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     if (lane == 0) umma_commit_2sm(smem_u32(a_empty + as), 3);
                     __syncwarp();
                 }
+                if (lane == 0 && t_it) atomicAdd(p.counters + 4, t_it);   // accumulator tiles produced by this pair
             }
         }
     } else {
@@ -391,6 +462,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         int wl_pos = 0, wl_end = 0, wl_used = 0;
         float2 wm_next = make_float2(0.f, INFINITY);
         int a_next = -1;
+        uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
         {
             const int64_t row0 = (int64_t)pair_id * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
             if (pair_id < ngroups && row0 < p.n) { wm_next = p.wm[row0]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[row0] : -1; }
@@ -400,6 +472,8 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             const bool valid = row < p.n;
             const float2 wm = wm_next;
             const int a_old = a_next;
+            const uint32_t gm = gm_next;
+            if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
             {   // prefetch the next group's two floats (and old label) while this group is processed
                 const int64_t rown = (int64_t)(g + npairs) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
                 if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[rown] : -1; }
@@ -410,9 +484,11 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             int ncand = 0;
             float dropped = INFINITY;
 
-            for (int t = 0; t < nt; ++t, ++t_it) {
+            for (int t = 0; t < nt; ++t) {
+                if (!((gm >> t) & 1u)) continue;                    // pruned for this group: no accumulator was produced
                 const int tb = t_it & 1;
                 mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
+                ++t_it;
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * PAIR_N + quarter * 64);
                 // columns at or beyond k are padding (score offset PAD_SCORE): a quarter or chunk that holds nothing
@@ -876,6 +952,9 @@ struct TensorCtx {
     int *counters = nullptr;     // [0] worklist, [1] exact list
     unsigned *absmax = nullptr;
     float2 *wm = nullptr; int64_t wm_cap = 0;
+    // tile pruning: per-centroid distance to the nearest other centroid of every tile, per-group tile masks
+    float *dmin = nullptr; size_t dmin_cap = 0;
+    uint32_t *gmask = nullptr; int64_t gmask_cap = 0;
     // seeds (only for the cached training partition)
     float *useed = nullptr; int64_t useed_cap = 0;
     double *Cprev = nullptr; float *sig_old = nullptr; int prev_cap = 0;
@@ -893,7 +972,7 @@ void tensor_free(akm_handle h) {
     if (!c) return;
     cudaFree(c->c16); cudaFree(c->cn); cudaFree(c->pc); cudaFree(c->wl_rows); cudaFree(c->wl_cand);
     cudaFree(c->exact_rows); cudaFree(c->counters); cudaFree(c->absmax);
-    cudaFree(c->useed); cudaFree(c->Cprev); cudaFree(c->sig_old); cudaFree(c->wm);
+    cudaFree(c->useed); cudaFree(c->Cprev); cudaFree(c->sig_old); cudaFree(c->wm); cudaFree(c->dmin); cudaFree(c->gmask);
     delete c;
     h->tc = nullptr;
 }
@@ -1039,7 +1118,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
         c->kpad_cap = kpad;
     }
     if (!c->pc) AKM_CUDA(h, cudaMalloc((void **)&c->pc, sizeof(PassConst)));
-    if (!c->counters) AKM_CUDA(h, cudaMalloc((void **)&c->counters, 4 * sizeof(int)));
+    if (!c->counters) AKM_CUDA(h, cudaMalloc((void **)&c->counters, 8 * sizeof(int)));
     if (c->wl_cap < rs.n) {
         cudaFree(c->wl_rows); cudaFree(c->wl_cand); cudaFree(c->exact_rows);
         c->wl_rows = c->wl_cand = c->exact_rows = nullptr;
@@ -1074,7 +1153,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     static const bool no_seed_env = getenv("AKM_NOSEED") != nullptr;      // debugging aid
     if (no_seed_env) use_seed = false;
     const int k_prev = use_seed ? c->k_prev : 0;
-    AKM_CUDA(h, cudaMemsetAsync(c->counters, 0, 4 * sizeof(int), h->stream));
+    AKM_CUDA(h, cudaMemsetAsync(c->counters, 0, 8 * sizeof(int), h->stream));
     AKM_CUDA(h, cudaMemsetAsync(c->pc, 0, sizeof(PassConst), h->stream));
     AKM_CUDA(h, cudaMemsetAsync(c->absmax, 0, sizeof(unsigned), h->stream));
     c16_max_kernel<<<std::min(h->num_sms, (k * d + 255) / 256), 256, 0, h->stream>>>(C, (size_t)k * d, c->absmax);
@@ -1104,12 +1183,34 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
         AKM_CUDA(h, cudaMalloc((void **)&c->wm, sizeof(float2) * (size_t)rs.n));
         c->wm_cap = rs.n;
     }
+    // tile pruning needs seeds (an upper bound of every row's distance to its previous centroid) and pays when a
+    // group's rows share that centroid, i.e. on a cluster-ordered partition; with a single tile there is nothing to skip
+    const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
+    const bool prune = k_prev > 0 && ntiles > 1 && h->tile_pruning;
+    if (prune) {
+        const size_t need = (size_t)k * ntiles;
+        if (c->dmin_cap < need) {
+            cudaFree(c->dmin); c->dmin = nullptr; c->dmin_cap = 0;
+            AKM_CUDA(h, cudaMalloc((void **)&c->dmin, sizeof(float) * need));
+            c->dmin_cap = need;
+        }
+        if (c->gmask_cap < ngroups2) {
+            cudaFree(c->gmask); c->gmask = nullptr; c->gmask_cap = 0;
+            AKM_CUDA(h, cudaMalloc((void **)&c->gmask, sizeof(uint32_t) * (size_t)ngroups2));
+            c->gmask_cap = ngroups2;
+        }
+        AKM_CUDA(h, cudaMemsetAsync(c->gmask, 0, sizeof(uint32_t) * (size_t)ngroups2, h->stream));
+        centroid_tile_dist_kernel<<<(k + 7) / 8, 256, 0, h->stream>>>(C, k, d, ntiles, c->dmin);
+        h->stats.kernel_launches++;
+    }
     rowprep_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,
-                                                          c->sig_old, k_prev, (chain == 1) ? remap : nullptr, c->wm);
+                                                          c->sig_old, k_prev, (chain == 1) ? remap : nullptr, c->wm,
+                                                          prune ? c->dmin : nullptr, ntiles, k, prune ? c->gmask : nullptr);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     sp.wm = c->wm;
-    const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
+    sp.gmask = prune ? c->gmask : nullptr;
+    h->stats.tiles_total = (int64_t)ngroups2 * ntiles;
     const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;
     const int rc = pair_stream ? launch_pair<0>(h, mapX, mapC, sp, pair_smem, pgrid)
                    : (KB == 1) ? launch_pair<1>(h, mapX, mapC, sp, pair_smem, pgrid)
@@ -1150,6 +1251,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     // iscal[4] = rows refined, [5] = rows evaluated against all k, [6] = labels changed
     AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 4, c->counters + 3, sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 5, c->counters + 1, 2 * sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->iscal + 7, c->counters + 4, sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
     h->stats.engine_used = AKM_ENGINE_TENSOR;
     return AKM_OK;
 }

@@ -31,7 +31,7 @@ class AkmError(RuntimeError):
 class Stats(ctypes.Structure):
     _fields_ = [("rows", ctypes.c_int64), ("rows_certified", ctypes.c_int64), ("rows_refined", ctypes.c_int64),
                 ("kernel_launches", ctypes.c_int64), ("engine_used", ctypes.c_int32), ("storage_bytes", ctypes.c_int32),
-                ("rows_exact_all", ctypes.c_int64)]
+                ("rows_exact_all", ctypes.c_int64), ("tiles_total", ctypes.c_int64), ("tiles_computed", ctypes.c_int64)]
 
 
 _lib = None

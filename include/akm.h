@@ -207,6 +207,8 @@ typedef struct {
     int32_t engine_used;      /* AKM_ENGINE_EXACT or AKM_ENGINE_TENSOR */
     int32_t storage_bytes;    /* 4 or 8 */
     int64_t rows_exact_all;   /* subset of rows_refined that was evaluated against all k centroids */
+    int64_t tiles_total;      /* tensor engine: (256-row groups) x (256-centroid tiles) of the last pass */
+    int64_t tiles_computed;   /* ... of which were evaluated; the rest were pruned by the triangle inequality */
 } akm_stats;
 int akm_get_stats(akm_handle h, akm_stats *out);
 
@@ -217,7 +219,10 @@ int akm_time_kernel(akm_handle h, const char *name, int reps, double *ms_out);
 
 /* Tuning options (no reference counterpart).  "reorder_min_rows": partitions with at least this many rows are
  * kept grouped by cluster inside the library (outputs are always returned in the caller's row order);
- * default 262144, a huge value disables it. */
+ * default 262144, a huge value disables it.  "tile_pruning" (default 1): from the second pass of a training
+ * sequence on, the tensor engine skips every (256-row group, 256-centroid tile) pair that the triangle
+ * inequality proves free of the argmin and of every near-tie candidate (bounds from the previous pass; results
+ * are unchanged, akm_stats.tiles_computed / tiles_total reports how much was evaluated); 0 evaluates everything. */
 int akm_set_option(akm_handle h, const char *name, double value);
 
 /* Per-phase device timing of akm_step with CUDA events on the handle's stream (off by default).

@@ -21,6 +21,6 @@ for s in range(steps):
     conv, kk, obj = h.step(0.0)
     p = h.get_profile()
     st = h.stats()
-    print("step %d: search %.2f refine %.2f acc %.2f upd %.2f ms | k=%d refined=%.2f%% exact_all=%.3f%% obj=%.6g" % (
+    print("step %d: search %.2f refine %.2f acc %.2f upd %.2f ms | k=%d refined=%.2f%% tiles=%.1f%% obj=%.6g" % (
         s + 1, p["search_ms"], p["refine_ms"], p["accumulate_ms"], p["update_ms"], kk,
-        100.0 * st["rows_refined"] / max(1, st["rows"]), 100.0 * st["rows_exact_all"] / max(1, st["rows"]), obj), flush=True)
+        100.0 * st["rows_refined"] / max(1, st["rows"]), 100.0 * st["tiles_computed"] / max(1, st["tiles_total"]), obj), flush=True)

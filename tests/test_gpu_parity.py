@@ -228,6 +228,31 @@ def test_wide_rows_training_loop_matches_oracle(metric):
     assert (m["weights"] == ref["weights"]).all()
 
 
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_tile_pruning_changes_nothing_but_the_work(metric):
+    # k > 256 so that there are several centroid tiles; a cluster-ordered partition so that groups agree
+    n, d, k = 60000, 32, 700
+    X = blobs(n, d, k, seed=41, spread=20.0)
+    C0 = X[np.random.default_rng(4).choice(n, k, replace=False)].copy()
+    ref = orc.train(metric, X, C0, max_iter=7, tol=0.0, threads=4)
+    out = {}
+    for prune in (1, 0):
+        with native.Handle(d, metric) as h:
+            h.set_engine(native.ENGINE_TENSOR)
+            h.set_option("reorder_min_rows", 1)
+            h.set_option("tile_pruning", prune)
+            h.upload_rows(X)
+            m = h.train(C0, max_iter=7, tol=0.0)
+            out[prune] = (h.get_labels(), m, h.stats())
+    for prune in (1, 0):
+        labels, m, st = out[prune]
+        assert (labels == ref["labels"]).all() and m["k"] == ref["k"]
+        np.testing.assert_allclose(m["C"][: m["k"]], ref["C"][: ref["k"]], rtol=1e-9, atol=1e-12)
+    assert out[0][2]["tiles_computed"] == out[0][2]["tiles_total"] > 0
+    assert 0 < out[1][2]["tiles_computed"] < out[1][2]["tiles_total"]      # something was skipped
+    assert (out[1][1]["C"] == out[0][1]["C"]).all() or metric == native.COSINE
+
+
 def test_only_the_first_k_centroids_are_candidates():
     d = 8
     X = blobs(500, d, 3, seed=9)
@@ -363,7 +388,7 @@ def test_full_size_baseline_configs_tensor_engine_equals_exact_engine(cfg, n, d,
         pytest.skip("needs ~%d GB of free HBM" % need_gb)
     init_rows = (np.arange(k, dtype=np.int64) * n) // k
     out = {}
-    for name, engine, steps in (("tensor", native.ENGINE_TENSOR, 3), ("exact", native.ENGINE_EXACT, 2)):
+    for name, engine, steps in (("tensor", native.ENGINE_TENSOR, 3), ("exact", native.ENGINE_EXACT, 3)):
         with native.Handle(d, metric) as h:
             h.set_engine(engine)
             h.reserve_rows(n)
@@ -377,7 +402,7 @@ def test_full_size_baseline_configs_tensor_engine_equals_exact_engine(cfg, n, d,
                 if len(objs) == 2:
                     labels2 = h.get_labels()
                     model2 = h.get_model()
-            out[name] = dict(objs=objs, ks=ks, labels=labels2, model=model2)
+            out[name] = dict(objs=objs, ks=ks, labels=labels2, model=model2, labels3=h.get_labels(), stats=h.stats())
             if name == "tensor":
                 # the third pass runs on the cluster-ordered layout with seeded thresholds: invariants only
                 lab3 = h.get_labels()
@@ -387,9 +412,12 @@ def test_full_size_baseline_configs_tensor_engine_equals_exact_engine(cfg, n, d,
                 assert lab3.min() >= 0 and lab3.max() < ks[1]
                 assert (np.bincount(lab3, minlength=k) == m3["weights"]).all()   # model weights = counts of the last pass
     t, e = out["tensor"], out["exact"]
-    assert t["ks"][:2] == e["ks"]
+    assert t["ks"] == e["ks"]
     assert (t["labels"] == e["labels"]).all()
-    for a, b in zip(t["objs"][:2], e["objs"]):
+    assert (t["labels3"] == e["labels3"]).all()          # third pass: cluster-ordered rows, seeded windows, pruned tiles
+    if k > 256:
+        assert t["stats"]["tiles_computed"] <= t["stats"]["tiles_total"]
+    for a, b in zip(t["objs"], e["objs"]):
         assert abs(a - b) <= 1e-9 * abs(b)
     kk = e["ks"][1]
     np.testing.assert_allclose(t["model"]["C"][:kk], e["model"]["C"][:kk], rtol=1e-9, atol=1e-12)
