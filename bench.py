@@ -338,9 +338,33 @@ def main():
     st = h.stats()
     launches = st["kernel_launches"] - launches0
     prof = h.get_profile()
-    h.set_profiling(False)
     value = N * args.steps / (ms_total / 1e3)
     ms_per_step = ms_total / args.steps
+
+    # ---------------- the same supersteps with tile pruning switched off (every sample against every centroid on the
+    # tensor cores): reported beside `value` so that both readings of "one Lloyd iteration" are in the line
+    h.set_option("tile_pruning", 0)
+    h.get_profile(reset=True)
+    barrier()
+    ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        ev2.record(stream)
+        for _ in range(args.steps):
+            h.step(0.0)
+        ev3.record(stream)
+    barrier()
+    ms_full = max_over_ranks(ev2.elapsed_time(ev3))
+    prof_full = h.get_profile()
+    h.set_option("tile_pruning", 1)
+    h.set_profiling(False)
+    sf = max(1, prof_full["steps"])
+    full_eval = {"value": N * args.steps / (ms_full / 1e3), "ms_per_step": ms_full / args.steps,
+                 "phases_ms_per_step": {"search": prof_full["search_ms"] / sf, "refine": prof_full["refine_ms"] / sf,
+                                        "accumulate": prof_full["accumulate_ms"] / sf,
+                                        "allreduce_update": prof_full["update_ms"] / sf},
+                 "search_frac_of_peak": (2.0 * cnt * k * d / (prof_full["search_ms"] / sf / 1e3) / 1e12 / peaks()["tf_sust"])
+                 if prof_full["search_ms"] > 0 else None,
+                 "note": "tile_pruning = 0: same results, every (row group, centroid tile) pair evaluated"}
 
     # ---------------- e2e: host-buffer supersteps (what the Java ComputeFunctions would call)
     e2e = None
@@ -441,6 +465,7 @@ def main():
             "roofline": roofline, "roofline_accumulate": roofline_accumulate, "cpu_baseline": cpu,
             "phases_ms_per_step": {"search": search_ms, "refine": refine_ms, "accumulate": acc_ms,
                                    "allreduce_update": prof["update_ms"] / steps_p},
+            "full_evaluation": full_eval,
             "rows_certified_frac": certified / max(1.0, certified + refined),
             "objective_last": objective, "k_last": kk, "generate_s": gen_s, "upload": upload,
             "regroup": {"in_warmup": {"count": warm_prof["reorders"], "ms": warm_prof["reorder_ms"]},
