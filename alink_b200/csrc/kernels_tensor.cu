@@ -186,7 +186,7 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
                         const float rhs = ((metric == AKM_EUCLIDEAN) ? 2.f : 4.f) * W * 1.01f + 1e-30f;
                         mask = 1u << (ja / 256);                       // its own tile is always evaluated
                         for (int t = 0; t < ntiles; ++t) {
-                            const float dm = dmin[(size_t)ja * ntiles + t];
+                            const float dm = sqrtf(dmin[(size_t)ja * ntiles + t]) * 0.999999f;    // table holds squares
                             const float lhs = dm * (dm - 2.f * ub) * 0.999999f;
                             if (!(dm > 2.f * ub && lhs > rhs)) mask |= 1u << t;
                         }
@@ -205,28 +205,39 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
     }
 }
 
-// dmin[a][T] = min over the centroids j != a of tile T of |c_a - c_j| (COSINE: C holds unit vectors, so this is
-// the chord), rounded down.  One warp per centroid a; k*k*d flops, done once per pass.
+// dmin2[a][T] = min over the centroids j != a of tile T of |c_a - c_j|^2 (COSINE: C holds unit vectors, so this is
+// the squared chord), as float rounded down.  32 x 32 (a, j) pairs per CTA, operands staged through shared memory,
+// fp64 accumulation; the per-tile minimum is taken with an integer atomicMin on the bit pattern of the non-negative
+// float (the table is preset to a huge value).  k*k*d flops, once per pass.
 __global__ void __launch_bounds__(256)
-centroid_tile_dist_kernel(const double *__restrict__ C, int k, int d, int ntiles, float *__restrict__ dmin) {
-    const int lane = threadIdx.x & 31;
-    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (a >= k) return;
-    const double *ca = C + (size_t)a * d;
-    for (int t = 0; t < ntiles; ++t) {
-        double best = INFINITY;
-        const int j1 = min(k, (t + 1) * 256);
-        for (int j = t * 256; j < j1; ++j) {
-            if (j == a) continue;
-            const double *cj = C + (size_t)j * d;
-            double s2 = 0.0;
-            for (int i = lane; i < d; i += 32) { const double df = ca[i] - cj[i]; s2 = fma(df, df, s2); }
-            for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-            best = fmin(best, s2);
+centroid_tile_dist_kernel(const double *__restrict__ C, int k, int d, int ntiles, unsigned *__restrict__ dmin2) {
+    __shared__ double sa[32][33], sb[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;          // 32 x 8
+    const int a0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int c0 = 0; c0 < d; c0 += 32) {
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = ty + 8 * i, col = c0 + tx;
+            sa[r][tx] = (a0 + r < k && col < d) ? C[(size_t)(a0 + r) * d + col] : 0.0;
+            sb[r][tx] = (j0 + r < k && col < d) ? C[(size_t)(j0 + r) * d + col] : 0.0;
         }
-        if (lane == 0) {
-            float f = (best == best && best < 1e300) ? __double2float_rd(sqrt(best) * (1.0 - 1e-9)) : ((best == best) ? 3.0e38f : 0.f);
-            dmin[(size_t)a * ntiles + t] = f;
+        __syncthreads();
+#pragma unroll 8
+        for (int c = 0; c < 32; ++c) {
+            const double bj = sb[tx][c];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const double df = sa[ty + 8 * i][c] - bj; acc[i] = fma(df, df, acc[i]); }
+        }
+    }
+    const int j = j0 + tx;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int a = a0 + ty + 8 * i;
+        if (a < k && j < k && a != j && acc[i] == acc[i]) {
+            const float f = __double2float_rd(acc[i] * (1.0 - 1e-9));
+            atomicMin(dmin2 + (size_t)a * ntiles + j / 256, __float_as_uint(fmaxf(f, 0.f)));
         }
     }
 }
@@ -1200,7 +1211,9 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
             c->gmask_cap = ngroups2;
         }
         AKM_CUDA(h, cudaMemsetAsync(c->gmask, 0, sizeof(uint32_t) * (size_t)ngroups2, h->stream));
-        centroid_tile_dist_kernel<<<(k + 7) / 8, 256, 0, h->stream>>>(C, k, d, ntiles, c->dmin);
+        AKM_CUDA(h, cudaMemsetAsync(c->dmin, 0x7F, sizeof(float) * need, h->stream));     // 3.4e38: "no other centroid in this tile"
+        centroid_tile_dist_kernel<<<dim3((k + 31) / 32, (k + 31) / 32), 256, 0, h->stream>>>(C, k, d, ntiles,
+                                                                                             reinterpret_cast<unsigned *>(c->dmin));
         h->stats.kernel_launches++;
     }
     rowprep_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,

@@ -11,6 +11,8 @@ metric = native.COSINE if (len(sys.argv) > 5 and sys.argv[5] == "cosine") else n
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 k = int(sys.argv[3]) if len(sys.argv) > 3 else 1000
 h = native.Handle(d, metric)
+if os.environ.get("AKM_PRUNE"):
+    h.set_option("tile_pruning", int(os.environ["AKM_PRUNE"]))
 h.reserve_rows(N)
 h.blobs_append(20260101, k, 0, N)
 C0 = h.blobs_rows(20260101, k, (np.arange(k, dtype=np.int64) * N) // k).astype(np.float64)
