@@ -95,9 +95,20 @@ static int rowstore_widen(akm_handle h, RowStore &rs) {
 // Upload pipeline: the caller's (pageable) rows are copied into one half of a pinned buffer by a few host threads
 // while the other half is on its way to the device and through prepareVectorData, so the host copy, the DMA and
 // the kernel overlap.  (A cudaMemcpyAsync straight from pageable memory is staged by the driver at ~11 GB/s and
-// serialises with everything else.)
+// serialises with everything else.)  The copy threads narrow a chunk of doubles to fp32 when every value of the
+// chunk survives the round trip -- the usual case for feature vectors -- so it crosses PCIe at 4 bytes per value;
+// a chunk with any other value is sent as doubles and switches the partition to fp64 storage.
 constexpr size_t UPLOAD_HALF_BYTES = (size_t)64 << 20;
-constexpr int UPLOAD_THREADS = 4;
+constexpr int UPLOAD_MAX_THREADS = 8;
+
+static int upload_threads() {
+    static const int n = [] {
+        if (const char *e = getenv("AKM_UPLOAD_THREADS")) return std::max(1, std::min(UPLOAD_MAX_THREADS, atoi(e)));
+        const unsigned hc = std::thread::hardware_concurrency();
+        return (int)std::max(2u, std::min((unsigned)UPLOAD_MAX_THREADS, hc / 2));
+    }();
+    return n;
+}
 
 static int ensure_dev_stage(akm_handle h, size_t bytes) {
     if (h->stage_bytes >= bytes) return AKM_OK;
@@ -111,8 +122,9 @@ static int ensure_dev_stage(akm_handle h, size_t bytes) {
 static int ensure_upload_stage(akm_handle h, size_t half_bytes) {
     AKM_TRY(ensure_dev_stage(h, 2 * half_bytes));
     if (h->hstage_bytes < 2 * half_bytes) {
-        if (h->hstage) cudaFreeHost(h->hstage);
-    if (h->pin) cudaFreeHost(h->pin);
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));  // a chunk of an earlier upload may still be in flight
+        h->stage_used[0] = h->stage_used[1] = false;
+        if (h->hstage) cudaFreeHost(h->hstage);       // (the pin arena belongs to pin_begin / akm_destroy alone)
         h->hstage = nullptr; h->hstage_bytes = 0;
         AKM_CUDA(h, cudaHostAlloc(&h->hstage, 2 * half_bytes, cudaHostAllocDefault));
         h->hstage_bytes = 2 * half_bytes;
@@ -122,16 +134,45 @@ static int ensure_upload_stage(akm_handle h, size_t half_bytes) {
     return AKM_OK;
 }
 
-static void host_copy_parallel(void *dst, const void *src, size_t bytes) {
-    if (bytes < ((size_t)4 << 20)) { memcpy(dst, src, bytes); return; }
-    std::thread workers[UPLOAD_THREADS - 1];
-    const size_t part = ((bytes / UPLOAD_THREADS) + 4095) & ~(size_t)4095;
-    for (int t = 1; t < UPLOAD_THREADS; ++t) {
-        const size_t off = std::min(bytes, part * t), len = std::min(bytes - off, part);
-        workers[t - 1] = std::thread([=]() { if (len) memcpy((char *)dst + off, (const char *)src + off, len); });
+template <typename F>
+static void run_parts(size_t count, size_t align, size_t min_parallel, F &&fn) {     // fn(thread, begin, end)
+    const int T = upload_threads();
+    if (count < min_parallel || T == 1) { fn(0, (size_t)0, count); return; }
+    std::thread workers[UPLOAD_MAX_THREADS - 1];
+    const size_t part = ((count / T) + align - 1) / align * align;
+    for (int t = 1; t < T; ++t) {
+        const size_t lo = std::min(count, part * t), hi = std::min(count, lo + part);
+        workers[t - 1] = std::thread([&fn, t, lo, hi]() { if (hi > lo) fn(t, lo, hi); });
     }
-    memcpy(dst, src, std::min(bytes, part));
-    for (int t = 1; t < UPLOAD_THREADS; ++t) workers[t - 1].join();
+    fn(0, (size_t)0, std::min(count, part));
+    for (int t = 1; t < T; ++t) workers[t - 1].join();
+}
+
+static void host_copy_parallel(void *dst, const void *src, size_t bytes) {
+    run_parts(bytes, 4096, (size_t)4 << 20, [=](int, size_t lo, size_t hi) { memcpy((char *)dst + lo, (const char *)src + lo, hi - lo); });
+}
+
+// dst[i] = (float)src[i]; false when some value does not survive the round trip (NaN included): the caller then
+// sends the chunk as doubles
+static bool host_narrow_parallel(float *dst, const double *src, size_t count) {
+    bool ok[UPLOAD_MAX_THREADS];
+    for (bool &o : ok) o = true;
+    run_parts(count, 1024, (size_t)1 << 19, [&ok, dst, src](int t, size_t lo, size_t hi) {
+        bool good = true;
+        for (size_t i0 = lo; i0 < hi && good; i0 += 65536) {       // give up early on the first bad block
+            const size_t i1 = std::min(hi, i0 + 65536);
+            int bad = 0;
+            for (size_t i = i0; i < i1; ++i) {
+                const float f = (float)src[i];
+                dst[i] = f;
+                bad |= ((double)f != src[i]);
+            }
+            good = bad == 0;
+        }
+        ok[t] = good;
+    });
+    for (bool o : ok) if (!o) return false;
+    return true;
 }
 
 // Device -> pageable host memory through the same pinned halves: the DMA of chunk i+1 overlaps the host copy of
@@ -206,48 +247,46 @@ static void pin_finish(akm_handle h) {
 
 enum SrcKind { SRC_HOST_F64, SRC_HOST_F32, SRC_DEV_F32 };
 
-static int upload_pass(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n) {
-    const size_t d = (size_t)h->d;
-    if (kind == SRC_DEV_F32) return launch_prep_rows(h, rs, src, true, rs.n, n);
-    const size_t elt = kind == SRC_HOST_F64 ? 8 : 4;
-    const size_t row_bytes = d * elt;
-    int64_t chunk = (int64_t)std::max<size_t>(1, UPLOAD_HALF_BYTES / row_bytes);
-    chunk = std::min<int64_t>(chunk, n);
-    const size_t half = (size_t)chunk * row_bytes;
-    AKM_TRY(ensure_upload_stage(h, half));
-    int slot = 0;
-    bool used[2] = {false, false};
-    for (int64_t off = 0; off < n; off += chunk, slot ^= 1) {
-        const int64_t m = std::min<int64_t>(chunk, n - off);
-        char *hbuf = (char *)h->hstage + (size_t)slot * half;
-        char *dbuf = (char *)h->stage + (size_t)slot * half;
-        if (used[slot]) AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot]));     // DMA + kernel of two chunks ago are done
-        host_copy_parallel(hbuf, (const char *)src + (size_t)off * row_bytes, (size_t)m * row_bytes);
-        AKM_CUDA(h, cudaMemcpyAsync(dbuf, hbuf, (size_t)m * row_bytes, cudaMemcpyHostToDevice, h->stream));
-        AKM_TRY(launch_prep_rows(h, rs, dbuf, kind == SRC_HOST_F32, rs.n + off, m));
-        AKM_CUDA(h, cudaEventRecord(h->stage_free[slot], h->stream));
-        used[slot] = true;
-    }
-    return AKM_OK;
-}
-
-static int upload_rows(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n) {
+// Appends the rows; returns when the last chunk is staged (copies and kernels still in flight on h->stream).
+static int upload_rows(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n, bool prepared = false) {
     if (n == 0) return AKM_OK;
+    // COSINE rows the caller has already normalised are kept as the doubles they are (an fp32 store would hold raw
+    // rows and scale them wherever they are read)
+    if (prepared && h->metric == AKM_COSINE && rs.store == 4) AKM_TRY(rowstore_widen(h, rs));
     AKM_TRY(rowstore_reserve(h, rs, rs.n + n));
-    AKM_CUDA(h, cudaMemsetAsync(h->iscal + 3, 0, sizeof(int), h->stream));
-    AKM_TRY(upload_pass(h, rs, src, kind, n));
-    if (rs.store == 4) {
-        AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 3, h->iscal + 3, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
-        if (h->h_iscal[3] != 0) {
-            // some value of this batch is not fp32-representable: keep doubles from now on
-            AKM_TRY(rowstore_widen(h, rs));
-            AKM_TRY(upload_pass(h, rs, src, kind, n));
+    if (&rs == &h->rows) { h->xl_total_valid = false; h->acc_valid = false; h->last_changed = -1; }
+    rs.x16_valid = false;
+    const size_t d = (size_t)h->d;
+    if (kind == SRC_DEV_F32) {
+        AKM_TRY(launch_prep_rows(h, rs, src, true, rs.n, n, prepared));
+        rs.n += n;
+    } else {
+        const size_t elt = kind == SRC_HOST_F64 ? 8 : 4;
+        const size_t row_bytes = d * elt;
+        int64_t chunk = (int64_t)std::max<size_t>(1, UPLOAD_HALF_BYTES / row_bytes);
+        chunk = std::min<int64_t>(chunk, n);
+        const size_t half = (size_t)chunk * row_bytes;
+        AKM_TRY(ensure_upload_stage(h, half));
+        const size_t hhalf = h->hstage_bytes / 2, dhalf = h->stage_bytes / 2;
+        for (int64_t off = 0; off < n; off += chunk) {
+            const int slot = h->stage_slot;
+            h->stage_slot ^= 1;
+            const int64_t m = std::min<int64_t>(chunk, n - off);
+            char *hbuf = (char *)h->hstage + (size_t)slot * hhalf;
+            char *dbuf = (char *)h->stage + (size_t)slot * dhalf;
+            if (h->stage_used[slot]) AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot]));   // DMA + kernel of two chunks ago are done
+            const char *sp = (const char *)src + (size_t)off * row_bytes;
+            bool as_f32 = kind == SRC_HOST_F32;
+            if (kind == SRC_HOST_F64 && host_narrow_parallel((float *)hbuf, (const double *)sp, (size_t)m * d)) as_f32 = true;
+            else host_copy_parallel(hbuf, sp, (size_t)m * row_bytes);
+            if (!as_f32 && rs.store == 4) AKM_TRY(rowstore_widen(h, rs));      // first value that is not an fp32 value
+            AKM_CUDA(h, cudaMemcpyAsync(dbuf, hbuf, (size_t)m * d * (as_f32 ? 4 : 8), cudaMemcpyHostToDevice, h->stream));
+            AKM_TRY(launch_prep_rows(h, rs, dbuf, as_f32, rs.n, m, prepared));
+            AKM_CUDA(h, cudaEventRecord(h->stage_free[slot], h->stream));
+            h->stage_used[slot] = true;
+            rs.n += m;
         }
     }
-    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
-    rs.n += n;
-    rs.x16_valid = false;
     if (rs.reordered) AKM_TRY(ensure_orig(h, rs));   // appended rows keep their own index
     return AKM_OK;
 }
@@ -301,6 +340,7 @@ struct Scratch {
     double *c[2] = {nullptr, nullptr};
     double *l[2] = {nullptr, nullptr};
     double *sum = nullptr;
+    int *cmap = nullptr, *inv = nullptr;    // compaction maps of akm_update_centroids / akm_superstep (not the loop's)
     int cap = 0;
     double *dist_all = nullptr; size_t dist_all_count = 0;
     double *probs = nullptr; size_t probs_count = 0;
@@ -316,6 +356,7 @@ static void scratch_free(akm_handle h) {
     Scratch *e = h->sc;
     if (!e) return;
     for (int i = 0; i < 2; ++i) { dev_free(e->c[i]); dev_free(e->l[i]); }
+    dev_free(e->cmap); dev_free(e->inv);
     dev_free(e->sum); dev_free(e->dist_all); dev_free(e->probs); dev_free(e->idx64);
     delete e;
     h->sc = nullptr;
@@ -325,15 +366,25 @@ static int ensure_scratch(akm_handle h, int k0) {
     Scratch *s = scratch_of(h);
     if (s->cap >= k0) return AKM_OK;
     for (int i = 0; i < 2; ++i) { dev_free(s->c[i]); dev_free(s->l[i]); }
-    dev_free(s->sum);
+    dev_free(s->sum); dev_free(s->cmap); dev_free(s->inv);
     const size_t kd = (size_t)k0 * (size_t)h->d;
     for (int i = 0; i < 2; ++i) {
         AKM_TRY(dev_alloc(h, &s->c[i], kd));
         AKM_TRY(dev_alloc(h, &s->l[i], (size_t)k0));
     }
     AKM_TRY(dev_alloc(h, &s->sum, (size_t)k0 * (size_t)(h->d + 1) + 2));
+    AKM_TRY(dev_alloc(h, &s->cmap, (size_t)k0));
+    AKM_TRY(dev_alloc(h, &s->inv, (size_t)k0));
     s->cap = k0;
     return ensure_kvec(h, k0);
+}
+
+// h->labels is about to hold something other than the last training assignment of h->rows (prediction labels,
+// caller-provided ids, ...): neither the search seeds nor the incremental sums describe it any more
+static void invalidate_label_state(akm_handle h) {
+    tensor_invalidate_seeds(h);
+    h->acc_valid = false;
+    h->last_changed = -1;
 }
 
 // ------------------------------------------------------------------ assignment dispatch
@@ -379,11 +430,14 @@ static int maybe_reorder(akm_handle h, int k) {
     if (env == 0) return AKM_OK;
     if (h->stats.engine_used != AKM_ENGINE_TENSOR || h->rows.n < h->reorder_min_rows) return AKM_OK;
     h->changed_since_reorder++;                       // tensor passes since the last regrouping (or since upload)
-    bool go = !h->rows.reordered && h->changed_since_reorder >= 2;   // labels of the very first pass still move a lot
+    bool go = !h->rows.reordered && h->changed_since_reorder >= h->regroup_after;
     if (!go && h->rows.reordered && (int64_t)h->h_iscal[6] * 4 > h->rows.n) go = true;
     if (!go) return AKM_OK;
     if (h->profiling) cudaEventRecord(h->pev[3], h->stream);
     AKM_TRY(reorder_rows_by_label(h, h->rows, h->labels, tensor_useed(h), k));
+    // the incremental sums were formed from these very labels: their record moves with the rows
+    if (h->acc_valid && h->labels_acc && h->labels_acc_cap >= h->rows.n)
+        AKM_CUDA(h, cudaMemcpyAsync(h->labels_acc, h->labels, sizeof(int32_t) * (size_t)h->rows.n, cudaMemcpyDeviceToDevice, h->stream));
     if (h->profiling) {
         cudaEventRecord(h->pev[4], h->stream);
         cudaEventSynchronize(h->pev[4]);
@@ -464,7 +518,7 @@ int akm_destroy(akm_handle h) {
     scratch_free(h);
     rowstore_free(h->rows);
     rowstore_free(h->batch);
-    dev_free(h->labels); dev_free(h->mind);
+    dev_free(h->labels); dev_free(h->mind); dev_free(h->labels_acc); dev_free(h->sum_local);
     for (int i = 0; i < 2; ++i) { dev_free(h->cent[i]); dev_free(h->clabel[i]); }
     dev_free(h->sum); dev_free(h->cmap); dev_free(h->inv); dev_free(h->shift); dev_free(h->dscal); dev_free(h->iscal);
     dev_free(h->init_cost); dev_free(h->init_near); dev_free(h->init_rows); dev_free(h->init_out);
@@ -501,7 +555,10 @@ int akm_set_engine(akm_handle h, int engine) {
 int akm_reserve_rows(akm_handle h, int64_t n_total) {
     AKM_TRY(bind_device(h));
     REQUIRE(h, n_total >= 0, "negative row count");
-    return rowstore_reserve(h, h->rows, n_total);
+    AKM_TRY(rowstore_reserve(h, h->rows, n_total));
+    // everything else whose size follows from the row count, so that the supersteps allocate nothing
+    if (n_total >= h->reorder_min_rows && h->engine != AKM_ENGINE_EXACT) AKM_TRY(reorder_reserve(h, h->rows, n_total));
+    return AKM_OK;
 }
 
 int akm_upload_rows(akm_handle h, const double *x_host, int64_t n) {
@@ -509,6 +566,19 @@ int akm_upload_rows(akm_handle h, const double *x_host, int64_t n) {
     REQUIRE(h, n >= 0, "negative row count");
     REQUIRE(h, n == 0 || x_host, "rows pointer is null");
     return upload_rows(h, h->rows, x_host, SRC_HOST_F64, n);
+}
+
+int akm_upload_rows_prepared(akm_handle h, const double *x_host, int64_t n) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, n >= 0, "negative row count");
+    REQUIRE(h, n == 0 || x_host, "rows pointer is null");
+    return upload_rows(h, h->rows, x_host, SRC_HOST_F64, n, /*prepared=*/true);
+}
+
+int akm_upload_wait(akm_handle h) {
+    AKM_TRY(bind_device(h));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AKM_OK;
 }
 
 int akm_upload_rows_f32(akm_handle h, const float *x_host, int64_t n) {
@@ -530,7 +600,8 @@ int akm_clear_rows(akm_handle h) {
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     rowstore_free(h->rows);
     h->rows.store = 4;
-    tensor_invalidate_seeds(h);
+    invalidate_label_state(h);
+    h->xl_total_valid = false;
     dev_free(h->init_cost); dev_free(h->init_near);
     h->init_cap = 0;
     return AKM_OK;
@@ -563,14 +634,16 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
     AKM_TRY(pin_h2d(h, s->c[0], centroids, sizeof(double) * (size_t)k0 * d));
     AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, /*cos_normalise=*/false));
     AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], k0, k, h->labels, nullptr, /*chain=*/2, nullptr));
-    AKM_TRY(launch_accumulate(h, h->rows, h->labels, s->c[0], s->l[0], k0, s->sum, s->sum + L));
+    AKM_TRY(accumulate_step(h, s->c[0], s->l[0], k0, s->sum));
     AKM_TRY(pin_d2h(h, sum_out, s->sum, sizeof(double) * L));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 6 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 2, h->iscal + 2, 7 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     if (labels_out) AKM_TRY(copy_rows_out_i32(h, h->rows, h->labels, labels_out, h->rows.n));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     pin_finish(h);
     absorb_tensor_stats(h);
+    accumulate_absorb(h);
+    h->sum_dev_is_local = true;                      // s->sum holds this partition's sums (akm_allreduce_sum may use them)
     if (objective_out) *objective_out = h->h_dscal[0];
     AKM_TRY(check_error_flag(h));
     return maybe_reorder(h, k);
@@ -585,6 +658,7 @@ int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int ste
     const size_t L = (size_t)k0 * (size_t)(d + 1);
     AKM_TRY(ensure_scratch(h, k0));
     Scratch *s = scratch_of(h);
+    h->sum_dev_is_local = false;
     AKM_TRY(pin_begin(h, sizeof(double) * (L + 2 * (size_t)k0 * d + (size_t)k0)));
     AKM_TRY(pin_h2d(h, s->sum, sum, sizeof(double) * L));
     const double *dprev = nullptr, *lprev = nullptr;
@@ -594,7 +668,8 @@ int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int ste
         dprev = s->c[0]; lprev = s->l[0];
     }
     // the buffer written at step s is CENTROID1 when s is odd (KMeansUpdateCentroids.java:38-42)
-    AKM_TRY(launch_update(h, s->sum, k, k0, s->c[1], s->l[1], dprev, lprev, (step_no % 2) != 0, 0.0, h->shift, h->iscal));
+    AKM_TRY(launch_update(h, s->sum, k, k0, s->c[1], s->l[1], dprev, lprev, (step_no % 2) != 0, 0.0, h->shift, h->iscal,
+                          s->cmap, s->inv));
     AKM_TRY(pin_d2h(h, c_out, s->c[1], sizeof(double) * (size_t)k0 * d));
     // the first *k_out entries of shift are meaningful; k_out is not known before the sync, so fetch k entries
     // (k_out <= k) into the arena and hand over the valid prefix afterwards
@@ -609,6 +684,52 @@ int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int ste
         else AKM_CUDA(h, cudaMemcpy(shift_out, h->shift, sizeof(double) * (size_t)(*k_out), cudaMemcpyDeviceToHost));
     }
     return AKM_OK;
+}
+
+// The three stages above in one call: one host->device copy (centroids), one device->host batch, one
+// synchronisation; the accumulator never leaves the device between the stages.
+int akm_superstep(akm_handle h, const double *centroids, int k0, int k, int step_no, double tol, double *c_out,
+                  int *k_out, int *converged_out, double *sum_out, double *shift_out, double *objective_out) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, centroids && c_out && k_out, "centroids / c_out / k_out is null");
+    REQUIRE(h, k0 > 0 && k >= 0 && k <= k0, "need 0 <= k <= k0 and k0 > 0");
+    const int d = h->d;
+    const size_t L = (size_t)k0 * (size_t)(d + 1), kd = (size_t)k0 * d;
+    AKM_TRY(ensure_scratch(h, k0));
+    Scratch *s = scratch_of(h);
+    h->sum_dev_is_local = false;
+    AKM_TRY(ensure_labels(h, std::max<int64_t>(h->rows.n, 1)));
+    AKM_TRY(pin_begin(h, sizeof(double) * (2 * kd + L + (size_t)k0 + 64)));
+    AKM_TRY(pin_h2d(h, s->c[0], centroids, sizeof(double) * kd));
+    AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], k0, /*cos_normalise=*/false));
+    if (h->rows.n > 0) AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], k0, k, h->labels, nullptr, /*chain=*/2, nullptr));
+    AKM_TRY(accumulate_step(h, s->c[0], s->l[0], k0, s->sum));
+    if (h->comm) {
+        AKM_TRY(nccl_allreduce_device(h, s->sum, (int64_t)L + 2));
+        AKM_TRY(launch_flag_from_sum(h, s->sum + L + 1));
+    }
+    AKM_TRY(launch_update(h, s->sum, k, k0, s->c[1], s->l[1], s->c[0], s->l[0], (step_no % 2) != 0, tol, h->shift, h->iscal,
+                          s->cmap, s->inv));
+    AKM_TRY(pin_d2h(h, c_out, s->c[1], sizeof(double) * kd));
+    if (sum_out) AKM_TRY(pin_d2h(h, sum_out, s->sum, sizeof(double) * L));
+    char *shift_pin = (shift_out && k > 0) ? pin_take(h, sizeof(double) * (size_t)k) : nullptr;
+    if (shift_pin) AKM_CUDA(h, cudaMemcpyAsync(shift_pin, h->shift, sizeof(double) * (size_t)k, cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 9 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, s->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    pin_finish(h);
+    if (h->rows.n > 0) absorb_tensor_stats(h);
+    accumulate_absorb(h);
+    *k_out = h->h_iscal[0];
+    if (converged_out) *converged_out = h->h_iscal[1];
+    if (objective_out) *objective_out = h->h_dscal[0];
+    if (shift_out && *k_out > 0) {
+        if (shift_pin) memcpy(shift_out, shift_pin, sizeof(double) * (size_t)(*k_out));
+        else AKM_CUDA(h, cudaMemcpy(shift_out, h->shift, sizeof(double) * (size_t)(*k_out), cudaMemcpyDeviceToHost));
+    }
+    AKM_TRY(check_error_flag(h));
+    if (h->rows.n == 0) return AKM_OK;
+    return maybe_reorder(h, k);
 }
 
 int akm_set_centroids(akm_handle h, const double *c0, int k0) {
@@ -626,6 +747,7 @@ int akm_set_centroids(akm_handle h, const double *c0, int k0) {
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     h->k0 = k0; h->k = k0; h->step = 0;
     tensor_invalidate_seeds(h);
+    h->last_changed = -1;                            // new centroids: expect most rows to move (full accumulation)
     return AKM_OK;
 }
 
@@ -642,19 +764,25 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     const bool prof = h->profiling;
     h->mid_recorded = false;
     if (prof) cudaEventRecord(h->pev[0], h->stream);
-    AKM_TRY(run_assign(h, h->rows, h->cent[rd], h->clabel[rd], k0, h->k, h->labels, nullptr, /*chain=*/1,
-                       s > 1 ? h->cmap : nullptr));
+    if (h->rows.n > 0)
+        AKM_TRY(run_assign(h, h->rows, h->cent[rd], h->clabel[rd], k0, h->k, h->labels, nullptr, /*chain=*/1,
+                           s > 1 ? h->cmap : nullptr));
     if (prof) cudaEventRecord(h->pev[1], h->stream);
-    AKM_TRY(launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->clabel[rd], k0, h->sum, h->sum + L));
+    AKM_TRY(accumulate_step(h, h->cent[rd], h->clabel[rd], k0, h->sum));
     if (prof) cudaEventRecord(h->pev[2], h->stream);
-    if (h->comm) AKM_TRY(nccl_allreduce_device(h, h->sum, (int64_t)L + 1));
+    if (h->comm) {
+        // sums, objective and the no-finite-distance flag travel together: every rank sees the same error
+        AKM_TRY(nccl_allreduce_device(h, h->sum, (int64_t)L + 2));
+        AKM_TRY(launch_flag_from_sum(h, h->sum + L + 1));
+    }
     AKM_TRY(launch_update(h, h->sum, h->k, k0, h->cent[wr], h->clabel[wr], h->cent[rd], h->clabel[rd],
-                          /*new_is_c1=*/wr == 0, tol, h->shift, h->iscal));
+                          /*new_is_c1=*/wr == 0, tol, h->shift, h->iscal, h->cmap, h->inv_cap >= k0 ? h->inv : nullptr));
     if (prof) cudaEventRecord(h->pev[3], h->stream);
-    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 8 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal, h->iscal, 9 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->h_dscal, h->sum + L, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
-    absorb_tensor_stats(h);
+    if (h->rows.n > 0) absorb_tensor_stats(h);
+    accumulate_absorb(h);
     h->k = h->h_iscal[0];
     if (prof) {
         float a = 0.f, b = 0.f, c = 0.f, m1 = 0.f;
@@ -676,6 +804,7 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     if (k_out) *k_out = h->k;
     if (objective_out) *objective_out = h->h_dscal[0];
     AKM_TRY(check_error_flag(h));
+    if (h->rows.n == 0) return AKM_OK;
     // labels index the centroids this step assigned against (k_before clusters)
     return maybe_reorder(h, k_before);
 }
@@ -714,7 +843,7 @@ static int predict_store(akm_handle h, RowStore &rs, const double *dC, const dou
     Scratch *s = scratch_of(h);
     const int64_t n = rs.n;
     if (n == 0) return AKM_OK;
-    tensor_invalidate_seeds(h);                      // h->labels is about to hold prediction labels
+    invalidate_label_state(h);                       // h->labels is about to hold prediction labels
     AKM_TRY(ensure_labels(h, n));
     AKM_TRY(ensure_mind(h, n));
     if (s->idx64_cap < n) {
@@ -842,7 +971,7 @@ int akm_init_update(akm_handle h, const double *centers, int m, int id_base, dou
     // the centres are rows of the prepared partition: labels only, no second normalisation
     AKM_TRY(launch_prepare_centroids(h, s->c[0], s->l[0], m, /*cos_normalise=*/false));
     if (n > 0) {
-        tensor_invalidate_seeds(h);
+        invalidate_label_state(h);
         AKM_TRY(ensure_labels(h, n));
         AKM_TRY(ensure_mind(h, n));
         AKM_TRY(run_assign(h, h->rows, s->c[0], s->l[0], m, m, h->labels, h->mind));
@@ -923,7 +1052,7 @@ int akm_eval_clusters(akm_handle h, const int32_t *labels, int k, double *count_
     const size_t L = (size_t)k * (d + 1);
     std::vector<double> sums(L, 0.0);
     if (n > 0) {
-        tensor_invalidate_seeds(h);                      // h->labels is about to hold the caller's cluster ids
+        invalidate_label_state(h);                       // h->labels is about to hold the caller's cluster ids
         AKM_TRY(ensure_labels(h, n));
         AKM_TRY(ensure_init_lists(h, 1, (size_t)(n + 1) / 2 + 1));        // staging for the int32 labels
         int32_t *stage = reinterpret_cast<int32_t *>(h->init_out);
@@ -980,43 +1109,6 @@ int akm_get_stats(akm_handle h, akm_stats *out) {
 }
 
 }  // extern "C"
-
-// ---------------------------------------------------------------- kernel timing for the roofline object
-extern "C" int akm_time_kernel(akm_handle h, const char *name, int reps, double *ms_out) {
-    AKM_TRY(bind_device(h));
-    REQUIRE(h, name && ms_out && reps > 0, "bad argument");
-    if (h->k0 <= 0 || h->rows.n == 0) return akm_fail(h, AKM_ERR_STATE, "needs cached rows and centroids");
-    const int rd = ((h->step + 1) % 2 == 0) ? 0 : 1;
-    const size_t L = (size_t)h->k0 * (size_t)(h->d + 1);
-    AKM_TRY(ensure_labels(h, h->rows.n));
-    Scratch *s = scratch_of(h);
-    AKM_TRY(ensure_scratch(h, h->k0));
-    cudaEvent_t e0, e1;
-    AKM_CUDA(h, cudaEventCreate(&e0));
-    AKM_CUDA(h, cudaEventCreate(&e1));
-    const bool is_assign = strcmp(name, "assign") == 0;
-    const bool is_acc = strcmp(name, "accumulate") == 0;
-    if (!is_assign && !is_acc) return akm_fail(h, AKM_ERR_BADARG, "name must be assign | accumulate");
-    int rc = AKM_OK;
-    // one untimed launch, then `reps` timed ones (labels must exist before timing accumulate)
-    rc = run_assign(h, h->rows, h->cent[rd], h->clabel[rd], h->k0, h->k, h->labels, nullptr);
-    if (rc == AKM_OK && is_acc) rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->clabel[rd], h->k0, s->sum, s->sum + L);
-    if (rc == AKM_OK) {
-        cudaEventRecord(e0, h->stream);
-        for (int i = 0; i < reps && rc == AKM_OK; ++i) {
-            if (is_assign) rc = run_assign(h, h->rows, h->cent[rd], h->clabel[rd], h->k0, h->k, h->labels, nullptr);
-            else rc = launch_accumulate(h, h->rows, h->labels, h->cent[rd], h->clabel[rd], h->k0, s->sum, s->sum + L);
-        }
-        cudaEventRecord(e1, h->stream);
-        if (cudaEventSynchronize(e1) != cudaSuccess) rc = akm_fail(h, AKM_ERR_CUDA, "event sync failed");
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, e0, e1);
-        *ms_out = (double)ms / reps;
-    }
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    return rc;
-}
 
 extern "C" int akm_set_profiling(akm_handle h, int on) {
     AKM_TRY(bind_device(h));
@@ -1080,5 +1172,7 @@ extern "C" int akm_set_option(akm_handle h, const char *name, double value) {
     if (!h || !name) return akm_fail(h, AKM_ERR_BADARG, "null argument");
     if (strcmp(name, "reorder_min_rows") == 0) { h->reorder_min_rows = (int64_t)value; return AKM_OK; }
     if (strcmp(name, "tile_pruning") == 0) { h->tile_pruning = value != 0.0; return AKM_OK; }
+    if (strcmp(name, "delta_accumulate") == 0) { h->delta_accumulate = value != 0.0; h->acc_valid = false; h->last_changed = -1; return AKM_OK; }
+    if (strcmp(name, "regroup_after") == 0) { h->regroup_after = std::max(1, (int)value); return AKM_OK; }
     return akm_fail(h, AKM_ERR_BADARG, std::string("unknown option: ") + name);
 }

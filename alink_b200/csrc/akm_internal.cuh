@@ -59,7 +59,14 @@ struct akm_handle_s {
     double *cent[2] = {nullptr, nullptr};
     double *clabel[2] = {nullptr, nullptr};
     int cent_cap = 0;
-    double *sum = nullptr;    // k0*(d+1) + 2 : [L] = sum of xlabel / row count of this rank
+    double *sum = nullptr;    // k0*(d+1) + 2 : [L] = objective, [L+1] = no-finite-distance flag (both all-reduced)
+    // incremental accumulation (kernels_exact.cu, accumulate_step): sums of this partition and the label every
+    // row was added under
+    double *sum_local = nullptr; int sum_local_k0 = 0;
+    int32_t *labels_acc = nullptr; int64_t labels_acc_cap = 0;
+    bool acc_valid = false, acc_count_pending = false, xl_total_valid = false, delta_accumulate = true;
+    int acc_k0 = 0, acc_delta_passes = 0, acc_mode_last = 0;
+    int64_t acc_n = 0, acc_changed_total = 0, last_changed = -1;
     int *cmap = nullptr;      // k0 compaction map (old index -> new index)
     int *inv = nullptr; int inv_cap = 0;   // new index -> old index
     double *shift = nullptr;  // k0
@@ -73,6 +80,7 @@ struct akm_handle_s {
     void *stage = nullptr; size_t stage_bytes = 0;       // device staging (two halves, used alternately)
     void *hstage = nullptr; size_t hstage_bytes = 0;     // pinned host staging (two halves)
     cudaEvent_t stage_free[2] = {nullptr, nullptr};      // half i of both buffers may be refilled
+    bool stage_used[2] = {false, false}; int stage_slot = 0;
     // pinned bounce arena for the few-MB host buffers of the per-superstep calls (centroids, accumulator):
     // copies from/to pageable memory would be staged by the driver and block the calling thread one by one
     char *pin = nullptr; size_t pin_bytes = 0, pin_off = 0;
@@ -99,6 +107,8 @@ struct akm_handle_s {
     int reorders = 0;
     double reorder_ms = 0;
     int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
+    int regroup_after = 1;                // regroup once this many tensor-engine passes have produced labels
+    bool sum_dev_is_local = false;        // Scratch::sum still holds what akm_assign_accumulate returned
     bool tile_pruning = true;             // skip (row group, centroid tile) pairs the triangle inequality rules out
 
     // optional per-phase profiling of akm_step
@@ -137,7 +147,9 @@ int download_pipelined(akm_handle h, const void *dev, void *host, size_t bytes);
 
 // ---------------------------------------------------------------- kernels_exact.cu
 // prepareVectorData over `n` staged rows (src: double or float, row-major) appended at row `row0`.
-int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n);
+// prepared: the caller already ran prepareVectorData (COSINE rows are stored as given, not normalised again)
+int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n,
+                     bool prepared = false);
 // widen rows [0,n) of x32 into x64 (storage migration)
 int launch_widen_rows(akm_handle h, const float *x32, const double *xlabel, double *x64, int64_t n);
 // updateLabel on k0 centroids in place (EUCL: labels; COS: normalise rows unless cos_normalise == false,
@@ -153,9 +165,16 @@ int launch_assign_exact_list(akm_handle h, const RowStore &rs, const int32_t *ro
 int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, const double *C, const double *clabel,
                       int k0, double *sum, double *objective);
 // KMeansUpdateCentroids + KMeansIterTermination diag
+// cmap / inv: k0 ints each owned by the caller's state (the device-resident loop and the host-buffer calls keep
+// separate maps: the loop's map feeds the next pass's seeds); inv == nullptr selects the single-CTA kernel
 int launch_update(akm_handle h, const double *sum, int k, int k0, double *Cnew, double *clnew,
                   const double *Cprev, const double *clprev, bool new_is_c1, double tol,
-                  double *shift, int *iscal);
+                  double *shift, int *iscal, int *cmap, int *inv);
+// accumulation half of a superstep over h->rows / h->labels (full pass or moved rows only); sum_out: k0*(d+1)+2
+// doubles = sums, objective of this partition, no-finite-distance flag.  accumulate_absorb() after h_iscal[8] is back.
+int accumulate_step(akm_handle h, const double *C, const double *clabel, int k0, double *sum_out);
+void accumulate_absorb(akm_handle h);
+int launch_flag_from_sum(akm_handle h, const double *flag);
 // probs from all distances (getProbArrayFromDistanceArray)
 int launch_probs(akm_handle h, const double *dist_all, int64_t n, int k, double *probs);
 int launch_labels_to_i64(akm_handle h, const int32_t *labels, int64_t n, int64_t *out);
@@ -175,6 +194,7 @@ void nccl_destroy(akm_handle h);
 
 // ---------------------------------------------------------------- reorder.cu
 int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *useed, int k);
+int reorder_reserve(akm_handle h, const RowStore &rs, int64_t n);
 int ensure_orig(akm_handle h, RowStore &rs);
 int copy_rows_out_i32(akm_handle h, const RowStore &rs, const int32_t *dev, int32_t *host, int64_t n);
 int copy_rows_out_i64(akm_handle h, const RowStore &rs, const int64_t *dev, int64_t *host, int64_t n);

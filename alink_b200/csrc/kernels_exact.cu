@@ -27,7 +27,7 @@ template <typename SrcT, int METRIC, int STORE>
 __global__ void __launch_bounds__(PREP_ROWS)
 prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, float *__restrict__ x32,
                  double *__restrict__ x64, double *__restrict__ xlabel, double *__restrict__ sum_xlabel,
-                 int *__restrict__ inexact_flag) {
+                 int *__restrict__ inexact_flag, int prepared) {
     __shared__ double tile[PREP_ROWS][PREP_COLS + 1];
     __shared__ double inv_s[PREP_ROWS];
     __shared__ double red[PREP_ROWS / 32];
@@ -82,7 +82,7 @@ prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, f
     } else {
         // CosineDistance.updateLabel :60-65: norm = sqrt(dot); if (norm > 0) x *= 1.0 / norm
         const double nrm = sqrt(s);
-        inv_s[tid] = (nrm > 0.0) ? (1.0 / nrm) : -1.0;   // -1 == leave untouched
+        inv_s[tid] = (nrm > 0.0 && !prepared) ? (1.0 / nrm) : -1.0;   // -1 == leave untouched
         if (myrow < n) xlabel[row0 + myrow] = nrm;          // |x_raw|: not a distance label; scales fp32-stored rows
         __syncthreads();
         // fp32 store: raw rows (the scaling happens where they are read); fp64 store: normalised rows
@@ -110,14 +110,14 @@ prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, f
     if (STORE == 4 && inexact) atomicExch(inexact_flag, 1);
 }
 
-int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n) {
+int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n, bool prepared) {
     if (n <= 0) return AKM_OK;
     const unsigned grid = (unsigned)ceil_div64(n, PREP_ROWS);
     double *sx = h->dscal + 1;
     int *flag = h->iscal + 3;
 #define PREP_LAUNCH(SRC, M, ST)                                                              \
     prep_rows_kernel<SRC, M, ST><<<grid, PREP_ROWS, 0, h->stream>>>((const SRC *)src, n, h->d, row0, rs.x32, \
-                                                                    rs.x64, rs.xlabel, sx, flag)
+                                                                    rs.x64, rs.xlabel, sx, flag, prepared ? 1 : 0)
     if (h->metric == AKM_EUCLIDEAN) {
         if (rs.store == 4) { if (src_is_f32) PREP_LAUNCH(float, AKM_EUCLIDEAN, 4); else PREP_LAUNCH(double, AKM_EUCLIDEAN, 4); }
         else               { if (src_is_f32) PREP_LAUNCH(float, AKM_EUCLIDEAN, 8); else PREP_LAUNCH(double, AKM_EUCLIDEAN, 8); }
@@ -700,6 +700,215 @@ int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, c
 }
 
 // =====================================================================================
+// Incremental accumulation.  The reference refills the k x (d+1) accumulator from every sample in every
+// superstep (KMeansAssignCluster.java:59-63).  From the third pass of a run on, only a small share of
+// the samples changes cluster, so the handle keeps the sums of its partition (sum_local) together with
+// the label each row was added under (labels_acc) and moves just the rows whose label changed:
+//     S[old] -= x,  S[new] += x,  count[old] -= 1,  count[new] += 1.
+// Counts stay exact.  The sums pick up one fp64 rounding per moved value, so the policy in
+// accumulate_step() falls back to a full pass when many rows move, every 16 passes, and when the moved
+// rows since the last full pass exceed a quarter of the partition (drift stays many orders below the
+// 1e-6 parity bar; clusters that end up empty are reset to exact zeros).
+// =====================================================================================
+template <typename T, int METRIC>
+__global__ void __launch_bounds__(256)
+accumulate_delta_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, const int32_t *__restrict__ labels,
+                        int32_t *__restrict__ labels_acc, int64_t n, int d, int k0, double *__restrict__ sum,
+                        int *__restrict__ changed_out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nblk = (n + 31) / 32;
+    int64_t blk = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    int moved = 0;
+    for (; blk < nblk; blk += stride) {
+        const int64_t r = blk * 32 + lane;
+        int lb = -1, la = -1;
+        if (r < n) { lb = labels[r]; la = labels_acc[r]; }
+        if (lb < 0 || lb >= k0) lb = -1;
+        if (la < 0 || la >= k0) la = -1;
+        unsigned m = __ballot_sync(0xffffffffu, la != lb);
+        if (m == 0) continue;
+        moved += __popc(m);
+        if (la != lb) labels_acc[r] = lb;
+        while (m) {
+            const int i = __ffs(m) - 1;
+            m &= m - 1;
+            const int64_t row = blk * 32 + i;
+            const int from = __shfl_sync(0xffffffffu, la, i), to = __shfl_sync(0xffffffffu, lb, i);
+            const T *x = X + row * (int64_t)d;
+            const double rinv = RawCosine<T, METRIC>::value ? cos_inv(xlabel[row]) : 1.0;
+            double *sf = sum + (size_t)(from < 0 ? 0 : from) * (d + 1);
+            double *st = sum + (size_t)(to < 0 ? 0 : to) * (d + 1);
+            for (int c = lane; c < d; c += 32) {
+                double v = (double)x[c];
+                if (RawCosine<T, METRIC>::value) v = DMUL(rinv, v);
+                if (from >= 0) atomicAdd(sf + c, -v);
+                if (to >= 0) atomicAdd(st + c, v);
+            }
+            if (lane == 0) {
+                if (from >= 0) atomicAdd(sf + d, -1.0);
+                if (to >= 0) atomicAdd(st + d, 1.0);
+            }
+        }
+    }
+    if (lane == 0 && moved) atomicAdd(changed_out, moved);
+}
+
+// labels_acc <- labels; *changed_out += number of rows whose label differs from the one recorded before
+__global__ void labels_sync_kernel(const int32_t *__restrict__ labels, int32_t *__restrict__ labels_acc, int64_t n,
+                                   int *__restrict__ changed_out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int moved = 0;
+    for (; i < n; i += stride) {
+        const int lb = labels[i];
+        if (labels_acc[i] != lb) { ++moved; labels_acc[i] = lb; }
+    }
+    for (int o = 16; o > 0; o >>= 1) moved += __shfl_xor_sync(0xffffffffu, moved, o);
+    if ((threadIdx.x & 31) == 0 && moved) atomicAdd(changed_out, moved);
+}
+
+__global__ void sum_f64_kernel(const double *__restrict__ a, int64_t n, double *__restrict__ out) {
+    __shared__ double red[8];
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    double s = 0.0;
+    for (; i < n; i += stride) s += a[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        atomicAdd(out, t);
+    }
+}
+
+// sum_out[0..L) <- sum_local (rows of empty clusters as exact zeros, in both buffers); sum_out[L] += objective of the
+// partition put together the way Java's distance is:  EUCL  sum ||x||^2 - 2 c.S + n ||c||^2,  COS  n - c.S
+// (sum_out[L] was zeroed by the caller); sum_out[L+1] = the no-finite-distance flag of this pass (all-reduced with
+// the sums so that every rank of a multi-GPU step fails together).  One warp per cluster.
+__global__ void __launch_bounds__(256)
+finish_sums_kernel(int metric, double *__restrict__ sum_local, const double *__restrict__ C,
+                   const double *__restrict__ clabel, int k0, int d, const double *__restrict__ xl_total,
+                   const int *__restrict__ err_flag, double *__restrict__ sum_out) {
+    const int lane = threadIdx.x & 31;
+    const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const size_t L = (size_t)k0 * (d + 1);
+    if (j == 0 && lane == 0) {
+        if (metric == AKM_EUCLIDEAN) atomicAdd(sum_out + L, *xl_total);
+        sum_out[L + 1] = (*err_flag != 0) ? 1.0 : 0.0;
+    }
+    if (j >= k0) return;
+    double *row = sum_local + (size_t)j * (d + 1);
+    double *out = sum_out + (size_t)j * (d + 1);
+    const double cnt = row[d];
+    double dot = 0.0;
+    if (cnt == 0.0) {
+        for (int c = lane; c <= d; c += 32) { row[c] = 0.0; out[c] = 0.0; }
+        return;
+    }
+    for (int c = lane; c < d; c += 32) {
+        const double v = row[c];
+        out[c] = v;
+        dot = fma(C[(size_t)j * d + c], v, dot);
+    }
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if (lane == 0) {
+        out[d] = cnt;
+        const double part = (metric == AKM_EUCLIDEAN) ? (cnt * clabel[j] - 2.0 * dot) : (cnt - dot);
+        atomicAdd(sum_out + L, part);
+    }
+}
+
+// The accumulation half of one superstep over the cached partition and h->labels.  sum_out has k0*(d+1)+2 slots.
+int accumulate_step(akm_handle h, const double *C, const double *clabel, int k0, double *sum_out) {
+    RowStore &rs = h->rows;
+    const int d = h->d;
+    const int64_t n = rs.n;
+    const size_t L = (size_t)k0 * (size_t)(d + 1);
+    AKM_CUDA(h, cudaMemsetAsync(sum_out + L, 0, 2 * sizeof(double), h->stream));
+    AKM_CUDA(h, cudaMemsetAsync(h->iscal + 8, 0, sizeof(int), h->stream));
+    if (n <= 0) {
+        AKM_CUDA(h, cudaMemsetAsync(sum_out, 0, sizeof(double) * L, h->stream));
+        return AKM_OK;
+    }
+    if (h->sum_local_k0 < k0) {
+        if (h->sum_local) cudaFree(h->sum_local);
+        h->sum_local = nullptr; h->sum_local_k0 = 0;
+        AKM_CUDA(h, cudaMalloc((void **)&h->sum_local, sizeof(double) * (L + 2)));
+        h->sum_local_k0 = k0;
+        h->acc_valid = false;
+    }
+    if (h->labels_acc_cap < n) {
+        if (h->labels_acc) cudaFree(h->labels_acc);
+        h->labels_acc = nullptr; h->labels_acc_cap = 0;
+        AKM_CUDA(h, cudaMalloc((void **)&h->labels_acc, sizeof(int32_t) * (size_t)std::max<int64_t>(rs.cap, n)));
+        h->labels_acc_cap = std::max<int64_t>(rs.cap, n);
+        h->acc_valid = false;
+    }
+    if (!h->xl_total_valid) {
+        AKM_CUDA(h, cudaMemsetAsync(h->dscal + 2, 0, sizeof(double), h->stream));
+        if (h->metric == AKM_EUCLIDEAN) {
+            sum_f64_kernel<<<h->num_sms * 4, 256, 0, h->stream>>>(rs.xlabel, n, h->dscal + 2);
+            h->stats.kernel_launches++;
+        }
+        h->xl_total_valid = true;
+    }
+    const bool known = h->acc_valid && h->acc_n == n && h->acc_k0 == k0;
+    const bool delta = known && h->delta_accumulate && h->last_changed >= 0 && h->last_changed * 16 <= n &&
+                       h->acc_delta_passes < 16 && h->acc_changed_total * 4 <= n;
+    if (delta) {
+        const int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)h->num_sms * 16);
+#define DELTA(T, PTR, M) accumulate_delta_kernel<T, M><<<blocks, 256, 0, h->stream>>>(PTR, rs.xlabel, h->labels, h->labels_acc, n, d, k0, h->sum_local, h->iscal + 8)
+        if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) DELTA(float, rs.x32, AKM_EUCLIDEAN); else DELTA(double, rs.x64, AKM_EUCLIDEAN); }
+        else { if (rs.store == 4) DELTA(float, rs.x32, AKM_COSINE); else DELTA(double, rs.x64, AKM_COSINE); }
+#undef DELTA
+        h->stats.kernel_launches++;
+        AKM_CUDA(h, cudaGetLastError());
+        h->acc_delta_passes++;
+        h->acc_mode_last = 1;
+        h->acc_count_pending = true;
+    } else {
+        // full pass; the label copy doubles as the count of rows that moved since the previous pass
+        labels_sync_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(h->labels, h->labels_acc, n, h->iscal + 8);
+        h->stats.kernel_launches++;
+        AKM_CUDA(h, cudaGetLastError());
+        AKM_TRY(launch_accumulate(h, rs, h->labels, C, clabel, k0, h->sum_local, nullptr));
+        h->acc_delta_passes = 0;
+        h->acc_changed_total = 0;
+        h->acc_mode_last = 0;
+        h->acc_count_pending = known;       // without a previous record the count means nothing
+        if (!known) h->last_changed = -1;
+    }
+    finish_sums_kernel<<<(k0 + 7) / 8, 256, 0, h->stream>>>(h->metric, h->sum_local, C, clabel, k0, d, h->dscal + 2,
+                                                          h->iscal + 2, sum_out);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    h->acc_valid = true; h->acc_n = n; h->acc_k0 = k0;
+    return AKM_OK;
+}
+
+// after the caller copied iscal[8] back (h_iscal[8] = rows moved in the pass accumulate_step just ran)
+void accumulate_absorb(akm_handle h) {
+    if (!h->acc_count_pending) return;
+    h->acc_count_pending = false;
+    h->last_changed = h->h_iscal[8];
+    if (h->acc_mode_last == 1) h->acc_changed_total += h->h_iscal[8];
+}
+
+// if some rank flagged a row without a finite distance, every rank raises the error (sum[L+1] was all-reduced)
+__global__ void flag_from_sum_kernel(const double *__restrict__ flag, int *__restrict__ err_flag) {
+    if (*flag != 0.0) *err_flag = 1;
+}
+int launch_flag_from_sum(akm_handle h, const double *flag) {
+    flag_from_sum_kernel<<<1, 1, 0, h->stream>>>(flag, h->iscal + 2);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
+// =====================================================================================
 // KMeansUpdateCentroids.updateCentroids (:52-69) + KMeansIterTermination diagonal (:28-44)
 // Single CTA: k0*d is at most a few hundred thousand values.
 //   iscal[0] = new k, iscal[1] = converged
@@ -872,17 +1081,17 @@ update_rows_kernel(int metric, const double *__restrict__ sum, int k0, int d, do
 }
 
 int launch_update(akm_handle h, const double *sum, int k, int k0, double *Cnew, double *clnew, const double *Cprev,
-                  const double *clprev, bool new_is_c1, double tol, double *shift, int *iscal) {
+                  const double *clprev, bool new_is_c1, double tol, double *shift, int *iscal, int *cmap, int *inv) {
     const size_t smem = (size_t)8 * 2 * h->d * sizeof(double);
-    if (smem > 96 * 1024 || h->inv_cap < k0) {
+    if (smem > 96 * 1024 || inv == nullptr) {
         update_kernel<<<1, UPD_THREADS, 0, h->stream>>>(h->metric, sum, k, k0, h->d, Cnew, clnew, Cprev, clprev,
-                                                        new_is_c1 ? 1 : 0, tol, shift, h->cmap, iscal);
+                                                        new_is_c1 ? 1 : 0, tol, shift, cmap, iscal);
     } else {
-        update_map_kernel<<<1, UPD_THREADS, 0, h->stream>>>(sum, k, k0, h->d, h->cmap, h->inv, iscal);
+        update_map_kernel<<<1, UPD_THREADS, 0, h->stream>>>(sum, k, k0, h->d, cmap, inv, iscal);
         if (smem > 48 * 1024)
             AKM_CUDA(h, cudaFuncSetAttribute(update_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         update_rows_kernel<<<(k0 + 7) / 8, 256, smem, h->stream>>>(h->metric, sum, k0, h->d, Cnew, clnew, Cprev, clprev,
-                                                                  new_is_c1 ? 1 : 0, tol, shift, h->inv, iscal);
+                                                                  new_is_c1 ? 1 : 0, tol, shift, inv, iscal);
         h->stats.kernel_launches++;
     }
     h->stats.kernel_launches++;

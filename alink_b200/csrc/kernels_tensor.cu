@@ -115,6 +115,9 @@ struct SearchParams {
     int32_t *labels;
     int32_t *wl_rows;       // worklist: rows that need exact work
     int32_t *wl_cand;       // WL_CAND candidates per entry (-1 = unused, first == -2: all centroids)
+    int wl_cap;             // worklist slots allocated (a multiple of WL_BLOCK)
+    int32_t *exact_rows;    // exact list: direct destination of rows when the worklist is full
+    int *exact_count;
     int *counters;          // [0] reserved worklist slots, [2] labels changed, [3] worklist entries used, [4] tiles produced
     float eta;              // accumulation error factor
     // seeds: a rigorous upper bound of this pass's minimum score per row, derived from the previous pass
@@ -471,6 +474,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         const int bar_id = 1 + q;
         int t_it = 0;
         int wl_pos = 0, wl_end = 0, wl_used = 0;
+        bool wl_full = false;
         float2 wm_next = make_float2(0.f, INFINITY);
         int a_next = -1;
         uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
@@ -617,22 +621,29 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
                 if (mask) {
                     const int cnt = __popc(mask);
-                    if (wl_pos + cnt > wl_end) {
+                    if (!wl_full && wl_pos + cnt > wl_end) {
                         for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
                         int base = 0;
                         if (lane == 0) base = atomicAdd(p.counters, WL_BLOCK);
                         wl_pos = __shfl_sync(0xffffffffu, base, 0);
                         wl_end = wl_pos + WL_BLOCK;
+                        // the allocation is sized for the worst case (tensor_assign), so this never triggers; if it
+                        // ever did, the rows go straight to the exact list (one slot per row of the partition)
+                        if (wl_end > p.wl_cap) { wl_full = true; wl_pos = wl_end = 0; }
                     }
-                    const int base = wl_pos;
-                    wl_pos += cnt;
                     wl_used += cnt;
-                    if (need_exact) {
-                        const int pos = base + __popc(mask & ((1u << lane) - 1));
-                        p.wl_rows[pos] = (int32_t)row;
-                        int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
-                        dst[0] = *reinterpret_cast<const int4 *>(stage);
-                        dst[1] = *reinterpret_cast<const int4 *>(stage + 4);
+                    if (wl_full) {
+                        if (need_exact) p.exact_rows[atomicAdd(p.exact_count, 1)] = (int32_t)row;
+                    } else {
+                        const int base = wl_pos;
+                        wl_pos += cnt;
+                        if (need_exact) {
+                            const int pos = base + __popc(mask & ((1u << lane) - 1));
+                            p.wl_rows[pos] = (int32_t)row;
+                            int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
+                            dst[0] = *reinterpret_cast<const int4 *>(stage);
+                            dst[1] = *reinterpret_cast<const int4 *>(stage + 4);
+                        }
                     }
                 }
             }
@@ -801,9 +812,9 @@ __global__ void __launch_bounds__(128, RF_MINB)
 refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, int d,
                          const double *__restrict__ C, const double *__restrict__ clabel, int k,
                          const int32_t *__restrict__ wl_rows, const int32_t *__restrict__ wl_cand,
-                         const int *__restrict__ counters, int32_t *__restrict__ labels,
+                         const int *__restrict__ counters, int wl_cap, int32_t *__restrict__ labels,
                          int32_t *__restrict__ exact_rows, int *__restrict__ exact_count) {
-    const int nwl = counters[0];
+    const int nwl = min(counters[0], wl_cap);             // blocks reserved past the capacity were never written
     int e = blockIdx.x * blockDim.x + threadIdx.x;
     const int stride = gridDim.x * blockDim.x;
     for (; e < nwl; e += stride) {
@@ -959,7 +970,7 @@ struct TensorCtx {
     EncodeTiledFn encode = nullptr;
     __half *c16 = nullptr; float *cn = nullptr; int kpad_cap = 0;
     PassConst *pc = nullptr;
-    int32_t *wl_rows = nullptr, *wl_cand = nullptr, *exact_rows = nullptr; int64_t wl_cap = 0;
+    int32_t *wl_rows = nullptr, *wl_cand = nullptr, *exact_rows = nullptr; int64_t wl_cap = 0, wl_slots = 0;
     int *counters = nullptr;     // [0] worklist, [1] exact list
     unsigned *absmax = nullptr;
     float2 *wm = nullptr; int64_t wm_cap = 0;
@@ -1133,7 +1144,12 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     if (c->wl_cap < rs.n) {
         cudaFree(c->wl_rows); cudaFree(c->wl_cand); cudaFree(c->exact_rows);
         c->wl_rows = c->wl_cand = c->exact_rows = nullptr;
-        const size_t slots = (size_t)rs.n + (size_t)h->num_sms * 8 * WL_BLOCK;   // + one partial block per epilogue warp
+        // worst case: every row needs exact work; a warp abandons up to 31 slots of each 2048-slot block (a ballot that
+        // does not fit starts a new block) and leaves one partial block at the end (4 reserving warps per CTA)
+        size_t slots = (size_t)rs.n + (size_t)rs.n / 64 + (size_t)h->num_sms * 8 * WL_BLOCK;
+        slots = (slots + WL_BLOCK - 1) / WL_BLOCK * WL_BLOCK;
+        c->wl_slots = (int64_t)std::min<size_t>(slots, (((size_t)1 << 31) - ((size_t)1 << 23)) / WL_BLOCK * WL_BLOCK);   // int counter, + slack for one last reservation per warp
+        slots = (size_t)c->wl_slots;
         AKM_CUDA(h, cudaMalloc((void **)&c->wl_rows, sizeof(int32_t) * slots));
         AKM_CUDA(h, cudaMalloc((void **)&c->wl_cand, sizeof(int32_t) * slots * WL_CAND));
         AKM_CUDA(h, cudaMalloc((void **)&c->exact_rows, sizeof(int32_t) * (size_t)rs.n));
@@ -1185,6 +1201,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     sp.d = d; sp.metric = h->metric; sp.k = k;
     sp.cn = c->cn; sp.pc = c->pc; sp.xerr = rs.xerr; sp.labels = labels;
     sp.wl_rows = c->wl_rows; sp.wl_cand = c->wl_cand; sp.counters = c->counters;
+    sp.wl_cap = (int)c->wl_slots; sp.exact_rows = c->exact_rows; sp.exact_count = c->counters + 1;
     sp.eta = (float)(KB * KBLK + 32) * 2.3841858e-7f;       // (d16 + 32) * 2^-22
     sp.useed = train_rows ? c->useed : nullptr;
     sp.sig_old = c->sig_old;
@@ -1241,7 +1258,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     const int rblocks = h->num_sms * 32;
 #define REFINE(T, PTR, M)                                                                                         \
     refine_candidates_kernel<T, M><<<rblocks, 128, 0, h->stream>>>(PTR, rs.xlabel, d, C, clabel, k, c->wl_rows, \
-                                                                   c->wl_cand, c->counters, labels, c->exact_rows, c->counters + 1)
+                                                                   c->wl_cand, c->counters, (int)c->wl_slots, labels, c->exact_rows, c->counters + 1)
     if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) REFINE(float, rs.x32, AKM_EUCLIDEAN); else REFINE(double, rs.x64, AKM_EUCLIDEAN); }
     else { if (rs.store == 4) REFINE(float, rs.x32, AKM_COSINE); else REFINE(double, rs.x64, AKM_COSINE); }
 #undef REFINE

@@ -155,21 +155,16 @@ int ensure_orig(akm_handle h, RowStore &rs) {
     return AKM_OK;
 }
 
-// Regroup the rows of `rs` by `labels` inside chunks.  labels / useed are permuted with the rows.
-int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *useed, int k) {
-    const int64_t n = rs.n;
+// Scratch of the regrouping for a partition of n rows: one wave of rows (as many 32K-row chunks as fit 4 GB) and the
+// destination index of every row.  akm_reserve_rows calls this up front so that no cudaMalloc (which stalls the
+// device) lands inside the first supersteps of a training run.
+int reorder_reserve(akm_handle h, const RowStore &rs, int64_t n) {
     if (n <= 0 || n >= ((int64_t)1 << 31)) return AKM_OK;
-    if ((size_t)(k + 3) * sizeof(int) > 160 * 1024) return AKM_OK;       // bucket counters live in shared memory
-    AKM_TRY(ensure_orig(h, rs));
-    const int d = h->d;
-    const size_t xbytes = (size_t)d * (rs.store == 4 ? 4 : 8);
-    const size_t x16bytes = (rs.x16 && rs.x16_valid && rs.x16_cap >= n) ? (size_t)rs.d16 * 2 : 0;
-    const size_t max_row = std::max(xbytes, std::max<size_t>(x16bytes, 8));
-    // wave = as many chunks as fit a bounded scratch buffer
+    const size_t xbytes = (size_t)h->d * (rs.store == 4 ? 4 : 8);
+    const size_t max_row = std::max(xbytes, std::max<size_t>((size_t)((h->d + 7) / 8) * 16, 8));   // rows, fp16 copy, side arrays
     const size_t budget = (size_t)4 << 30;
-    int64_t wave_chunks = std::max<int64_t>(1, (int64_t)(budget / (max_row * REORDER_CHUNK)));
     const int64_t nchunks = ceil_div64(n, REORDER_CHUNK);
-    wave_chunks = std::min(wave_chunks, nchunks);
+    const int64_t wave_chunks = std::min<int64_t>(std::max<int64_t>(1, (int64_t)(budget / (max_row * REORDER_CHUNK))), nchunks);
     const size_t need = (size_t)wave_chunks * REORDER_CHUNK * max_row;
     if (h->reorder_scratch_bytes < need) {
         if (h->reorder_scratch) cudaFree(h->reorder_scratch);
@@ -183,6 +178,23 @@ int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *us
         AKM_CUDA(h, cudaMalloc((void **)&h->reorder_dest, sizeof(int32_t) * (size_t)n));
         h->reorder_dest_cap = n;
     }
+    return AKM_OK;
+}
+
+// Regroup the rows of `rs` by `labels` inside chunks.  labels / useed are permuted with the rows.
+int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *useed, int k) {
+    const int64_t n = rs.n;
+    if (n <= 0 || n >= ((int64_t)1 << 31)) return AKM_OK;
+    if ((size_t)(k + 3) * sizeof(int) > 160 * 1024) return AKM_OK;       // bucket counters live in shared memory
+    AKM_TRY(ensure_orig(h, rs));
+    const int d = h->d;
+    const size_t xbytes = (size_t)d * (rs.store == 4 ? 4 : 8);
+    const size_t x16bytes = (rs.x16 && rs.x16_valid && rs.x16_cap >= n) ? (size_t)rs.d16 * 2 : 0;
+    const size_t max_row = std::max(xbytes, std::max<size_t>((size_t)((d + 7) / 8) * 16, 8));      // as in reorder_reserve
+    AKM_TRY(reorder_reserve(h, rs, n));
+    const size_t budget = (size_t)4 << 30;
+    const int64_t nchunks = ceil_div64(n, REORDER_CHUNK);
+    const int64_t wave_chunks = std::min<int64_t>(std::max<int64_t>(1, (int64_t)(budget / (max_row * REORDER_CHUNK))), nchunks);
     const size_t smem = (size_t)(k + 3) * sizeof(int);
     const int64_t nwaves = ceil_div64(nchunks, wave_chunks);
     const size_t hist_bytes = ((size_t)nchunks + (size_t)nwaves) * (size_t)(k + 1) * sizeof(int);

@@ -67,6 +67,10 @@ def lib():
         L.akm_reserve_rows.argtypes = [_H, ctypes.c_int64]
         L.akm_upload_rows.argtypes = [_H, _c_dp, ctypes.c_int64]
         L.akm_upload_rows_f32.argtypes = [_H, _c_fp, ctypes.c_int64]
+        L.akm_upload_rows_prepared.argtypes = [_H, _c_dp, ctypes.c_int64]
+        L.akm_upload_wait.argtypes = [_H]
+        L.akm_superstep.argtypes = [_H, _c_dp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, _c_dp,
+                                    ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), _c_dp, _c_dp, _c_dp]
         L.akm_upload_rows_device_f32.argtypes = [_H, ctypes.c_void_p, ctypes.c_int64]
         L.akm_clear_rows.argtypes = [_H]
         L.akm_num_rows.argtypes = [_H, _c_lp, ctypes.POINTER(ctypes.c_int)]
@@ -83,7 +87,6 @@ def lib():
         L.akm_predict.argtypes = [_H, _c_dp, ctypes.c_int64, _c_dp, ctypes.c_int, _c_lp, _c_dp, _c_dp]
         L.akm_predict_cached.argtypes = [_H, _c_dp, ctypes.c_int, _c_lp, _c_dp]
         L.akm_get_stats.argtypes = [_H, ctypes.POINTER(Stats)]
-        L.akm_time_kernel.argtypes = [_H, ctypes.c_char_p, ctypes.c_int, _c_dp]
         L.akm_set_option.argtypes = [_H, ctypes.c_char_p, ctypes.c_double]
         L.akm_init_reset.argtypes = [_H]
         L.akm_init_update.argtypes = [_H, _c_dp, ctypes.c_int, ctypes.c_int, _c_dp]
@@ -173,6 +176,16 @@ class Handle:
             X = _f64(X)
             self._ck(lib().akm_upload_rows(self._h, _dp(X), X.shape[0]))
 
+    def upload_rows_prepared(self, X):
+        """Rows that already went through prepareVectorData on the caller's side (COSINE: unit vectors, stored as given)."""
+        X = _f64(X)
+        if X.ndim != 2 or X.shape[1] != self.d:
+            raise ValueError("rows must be n x %d" % self.d)
+        self._ck(lib().akm_upload_rows_prepared(self._h, _dp(X), X.shape[0]))
+
+    def upload_wait(self):
+        self._ck(lib().akm_upload_wait(self._h))
+
     def upload_rows_device_f32(self, dev_ptr, n):
         self._ck(lib().akm_upload_rows_device_f32(self._h, ctypes.c_void_p(int(dev_ptr)), int(n)))
 
@@ -209,6 +222,21 @@ class Handle:
         self._ck(lib().akm_update_centroids(self._h, _dp(sum_), k0, int(k), int(step_no), _dp(prev), _dp(C),
                                             ctypes.byref(nk), _dp(shift)))
         return C, nk.value, (shift[:nk.value] if shift is not None else None)
+
+    def superstep(self, C, k=None, step_no=1, tol=0.0, want_sum=False, want_shift=False):
+        """akm_superstep: assign + all-reduce + update + criterion with host buffers.
+        Returns dict(C[k0,d], k, converged, objective, sum|None, shift|None)."""
+        C = _f64(C)
+        k0 = C.shape[0]
+        k = k0 if k is None else int(k)
+        Cn = np.empty((k0, self.d), dtype=np.float64)
+        nk, conv, obj = ctypes.c_int(), ctypes.c_int(), ctypes.c_double()
+        s = np.empty(k0 * (self.d + 1), dtype=np.float64) if want_sum else None
+        shift = np.zeros(k0, dtype=np.float64) if want_shift else None
+        self._ck(lib().akm_superstep(self._h, _dp(C), k0, k, int(step_no), float(tol), _dp(Cn), ctypes.byref(nk),
+                                     ctypes.byref(conv), _dp(s), _dp(shift), ctypes.byref(obj)))
+        return dict(C=Cn, k=nk.value, converged=bool(conv.value), objective=obj.value, sum=s,
+                    shift=(shift[:nk.value] if shift is not None else None))
 
     # ---- device-resident loop
     def set_centroids(self, C0):
@@ -284,11 +312,6 @@ class Handle:
         st = Stats()
         self._ck(lib().akm_get_stats(self._h, ctypes.byref(st)))
         return {f: getattr(st, f) for f, _ in Stats._fields_}
-
-    def time_kernel(self, name, reps=3):
-        ms = ctypes.c_double()
-        self._ck(lib().akm_time_kernel(self._h, name.encode(), int(reps), ctypes.byref(ms)))
-        return ms.value
 
     def set_option(self, name, value):
         self._ck(lib().akm_set_option(self._h, name.encode(), float(value)))

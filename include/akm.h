@@ -92,12 +92,27 @@ int akm_reserve_rows(akm_handle h, int64_t n_total);
  * (BaseComQueue.java:497-527).  Rows whose values are all exactly representable in fp32 are kept
  * as fp32 (4 B/value); the first value that is not switches the partition to fp64 losslessly.  (A COSINE
  * fp32 partition keeps the raw values and forms x * (1/||x||) wherever it reads them, which is the same
- * double Java stores.)  The host rows are staged through a pinned double buffer; the call returns when
- * they are resident. */
+ * double Java stores.)  The host rows are staged through a pinned double buffer by a few copy threads, which
+ * also narrow fp32-representable chunks to fp32 so that they cross PCIe at 4 bytes per value. */
 int akm_upload_rows(akm_handle h, const double *x_host, int64_t n);
 
 /* Same for fp32 host rows (values widened exactly). */
 int akm_upload_rows_f32(akm_handle h, const float *x_host, int64_t n);
+
+/* Appends n samples that ALREADY went through FastDistance.prepareVectorData on the Java side -- what the ComQueue
+ * hands a ComputeFunction as "trainData" (KMeansTrainBatchOp.java:95-101 ran CosineDistance.updateLabel :58-65 on
+ * every vector before the queue starts).  COSINE rows are stored exactly as given (no second normalisation, so the
+ * assignment is bit-identical to the one Java computes from the same FastDistanceVectorData); the partition is
+ * then held in fp64, since unit-length doubles are not fp32 values.  EUCLIDEAN: identical to akm_upload_rows
+ * (prepareVectorData leaves the vector untouched and the label is recomputed here).  Cluster evaluation under
+ * COSINE (akm_eval_clusters) wants the raw vectors: use akm_upload_rows for a partition that is evaluated. */
+int akm_upload_rows_prepared(akm_handle h, const double *x_host, int64_t n);
+
+/* The upload calls above return once the caller's rows sit in the library's pinned staging buffers: the host
+ * buffer may be refilled at once (KMeans' Java side fills its next chunk while this one is still crossing
+ * PCIe), and every later call on the handle is ordered behind the copies.  akm_upload_wait blocks until all
+ * uploaded rows are resident and reports any deferred CUDA error.  No reference counterpart. */
+int akm_upload_wait(akm_handle h);
 
 /* Same, but the source already lives in device memory on the handle's device (used to measure
  * the resident-data throughput and to feed data produced on the GPU). */
@@ -139,6 +154,23 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k,
  *   shift_out  nullable double[k0] (first *k_out entries valid) */
 int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int step_no, const double *prev,
                          double *c_out, int *k_out, double *shift_out);
+
+/* One whole superstep of KMeansTrainBatchOp.iterateICQ (KMeansTrainBatchOp.java:58-81) for hosts that keep the
+ * centroid buffers in Java between supersteps: KMeansAssignCluster.calc (KMeansAssignCluster.java:30-67) ->
+ * AllReduce(CENTROID_ALL_REDUCE) (AllReduce.java:85-120; ncclAllReduce on the device buffer when a communicator
+ * is attached, identity otherwise) -> KMeansUpdateCentroids.updateCentroids (KMeansUpdateCentroids.java:52-69) ->
+ * the diagonal of KMeansIterTermination.calc (KMeansIterTermination.java:28-44).  Same results as calling
+ * akm_assign_accumulate, akm_allreduce_sum and akm_update_centroids(prev = centroids) one after the other, with one
+ * host->device copy (the centroids), one device->host batch and one synchronisation; the accumulator stays on
+ * the device.
+ *   centroids      k0 x d as in akm_assign_accumulate (the buffer the assignment reads)
+ *   step_no, tol   as in akm_update_centroids / akm_step
+ *   c_out          k0 x d new centroid buffer;  k_out new cluster count;  converged_out nullable
+ *   sum_out        nullable double[k0*(d+1)]: the all-reduced accumulator ("centroidAllReduce", whose counts
+ *                  KMeansOutputModel reads)
+ *   shift_out      nullable double[k0] (first *k_out valid);  objective_out nullable, over all ranks */
+int akm_superstep(akm_handle h, const double *centroids, int k0, int k, int step_no, double tol, double *c_out,
+                  int *k_out, int *converged_out, double *sum_out, double *shift_out, double *objective_out);
 
 /* ------------------------------------------------------------------ device-resident iteration */
 
@@ -212,17 +244,20 @@ typedef struct {
 } akm_stats;
 int akm_get_stats(akm_handle h, akm_stats *out);
 
-/* Times `reps` back-to-back launches of one named kernel of the last configuration with CUDA events
- * on the handle's stream; returns the average milliseconds per launch.  Used by bench.py for the
- * roofline object. name: "assign" | "accumulate". */
-int akm_time_kernel(akm_handle h, const char *name, int reps, double *ms_out);
-
-/* Tuning options (no reference counterpart).  "reorder_min_rows": partitions with at least this many rows are
- * kept grouped by cluster inside the library (outputs are always returned in the caller's row order);
- * default 262144, a huge value disables it.  "tile_pruning" (default 1): from the second pass of a training
- * sequence on, the tensor engine skips every (256-row group, 256-centroid tile) pair that the triangle
- * inequality proves free of the argmin and of every near-tie candidate (bounds from the previous pass; results
- * are unchanged, akm_stats.tiles_computed / tiles_total reports how much was evaluated); 0 evaluates everything. */
+/* Tuning options (no reference counterpart).  None of them changes a result.
+ *   "reorder_min_rows"  partitions with at least this many rows are kept grouped by cluster inside the library
+ *                       (outputs are always returned in the caller's row order); default 262144, a huge value
+ *                       disables it.
+ *   "regroup_after"     regroup once this many tensor-engine passes have produced labels (default 1).
+ *   "tile_pruning"      (default 1) from the second pass of a training sequence on, the tensor engine skips every
+ *                       (256-row group, 256-centroid tile) pair that the triangle inequality proves free of the
+ *                       argmin and of every near-tie candidate (bounds from the previous pass;
+ *                       akm_stats.tiles_computed / tiles_total reports how much was evaluated); 0 evaluates all.
+ *   "delta_accumulate"  (default 1) once few rows change cluster per pass, the per-cluster sums are kept between
+ *                       supersteps and only the rows whose label changed are moved (counts stay exact, sums pick
+ *                       up one fp64 rounding per moved value; a full pass runs whenever more than 1/16 of the rows
+ *                       moved in the previous pass, every 16 passes, and after any call that rewrites the labels);
+ *                       0 refills the accumulator from every row in every superstep like the reference does. */
 int akm_set_option(akm_handle h, const char *name, double value);
 
 /* Per-phase device timing of akm_step with CUDA events on the handle's stream (off by default).

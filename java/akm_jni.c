@@ -29,6 +29,38 @@ JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_
     return rc;
 }
 
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_uploadRowsPrepared(
+    JNIEnv *env, jclass cls, jlong h, jdoubleArray rows, jlong n) {
+    jdouble *p = (*env)->GetPrimitiveArrayCritical(env, rows, NULL);
+    int rc = akm_upload_rows_prepared(H(h), p, n);       /* returns once the rows are staged: the array is free again */
+    (*env)->ReleasePrimitiveArrayCritical(env, rows, p, JNI_ABORT);
+    return rc;
+}
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_uploadWait(
+    JNIEnv *env, jclass cls, jlong h) { return akm_upload_wait(H(h)); }
+
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_superstep(
+    JNIEnv *env, jclass cls, jlong h, jdoubleArray cent, jint k0, jint k, jint step, jdouble tol, jdoubleArray cout,
+    jintArray kout, jintArray convout, jdoubleArray sumout, jdoubleArray shiftout, jdoubleArray objout) {
+    jdouble *c = (*env)->GetDoubleArrayElements(env, cent, NULL);
+    jdouble *co = (*env)->GetDoubleArrayElements(env, cout, NULL);
+    jdouble *so = sumout ? (*env)->GetDoubleArrayElements(env, sumout, NULL) : NULL;
+    jdouble *sh = shiftout ? (*env)->GetDoubleArrayElements(env, shiftout, NULL) : NULL;
+    int nk = 0, conv = 0;
+    double obj = 0.0;
+    int rc = akm_superstep(H(h), c, k0, k, step, tol, co, &nk, &conv, so, sh, &obj);
+    (*env)->ReleaseDoubleArrayElements(env, cent, c, JNI_ABORT);
+    (*env)->ReleaseDoubleArrayElements(env, cout, co, 0);
+    if (so) (*env)->ReleaseDoubleArrayElements(env, sumout, so, 0);
+    if (sh) (*env)->ReleaseDoubleArrayElements(env, shiftout, sh, 0);
+    jint v = nk, w = conv;
+    (*env)->SetIntArrayRegion(env, kout, 0, 1, &v);
+    if (convout) (*env)->SetIntArrayRegion(env, convout, 0, 1, &w);
+    if (objout) (*env)->SetDoubleArrayRegion(env, objout, 0, 1, &obj);
+    return rc;
+}
+
 JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_assignAccumulate(
     JNIEnv *env, jclass cls, jlong h, jdoubleArray cent, jint k0, jint k, jdoubleArray sum, jdoubleArray obj) {
     jdouble *c = (*env)->GetDoubleArrayElements(env, cent, NULL);

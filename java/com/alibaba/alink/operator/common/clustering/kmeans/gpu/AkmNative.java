@@ -20,6 +20,13 @@ public final class AkmNative {
     public static native int destroy(long handle);
     public static native String lastError(long handle);
     public static native int uploadRows(long handle, double[] rowsRowMajor, long n);
+    /** rows that already went through FastDistance.prepareVectorData (the ComQueue's "trainData") */
+    public static native int uploadRowsPrepared(long handle, double[] rowsRowMajor, long n);
+    public static native int uploadWait(long handle);
+    /** assign + all-reduce (NCCL) + update + criterion in one native call; out arrays may be null except cOut, kOut */
+    public static native int superstep(long handle, double[] centroids, int k0, int k, int stepNo, double tol,
+                                       double[] cOut, int[] kOut, int[] convergedOut, double[] sumOut,
+                                       double[] shiftOut, double[] objectiveOut);
     public static native int assignAccumulate(long handle, double[] centroids, int k0, int k,
                                               double[] sumOut, double[] objectiveOut);
     public static native int updateCentroids(long handle, double[] sum, int k0, int k, int stepNo,

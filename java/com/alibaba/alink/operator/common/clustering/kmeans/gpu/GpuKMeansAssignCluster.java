@@ -12,11 +12,10 @@ import org.apache.flink.api.java.tuple.Tuple2;
  * partition once (the GPU analogue of the JVM-heap cache of BaseComQueue.java:497-527); every superstep then
  * costs one k0 x d upload and one k0 x (d+1) download.
  *
- * Note: the cached samples were already label-updated by KMeansTrainBatchOp (prepareVectorData).  For
- * EUCLIDEAN the vectors are untouched, so uploading them reproduces the labels bit for bit; for COSINE the
- * vectors are already unit length and akm's normalisation (x * (1/||x||)) is applied to them once more, which
- * can move the last bit -- to stay bit-identical build the handle before prepareVectorData (or skip the Java
- * side normalisation when the GPU path is on).
+ * The cached samples were already label-updated by KMeansTrainBatchOp (prepareVectorData, :95-101): COSINE vectors
+ * arrive normalised.  They are uploaded with akm_upload_rows_prepared, which stores them as given, so the
+ * assignment is computed from exactly the doubles the stock KMeansAssignCluster would read.  The upload call
+ * returns as soon as a chunk is staged, so filling the next chunk overlaps the transfer of the previous one.
  */
 public class GpuKMeansAssignCluster extends ComputeFunction {
     static final String HANDLE = "akmHandle";
@@ -58,13 +57,14 @@ public class GpuKMeansAssignCluster extends ComputeFunction {
                 double[] v = ((com.alibaba.alink.common.linalg.DenseVector) sample.getVector()).getData();
                 System.arraycopy(v, 0, buf, filled * vectorSize, vectorSize);
                 if (++filled == chunk) {
-                    AkmNative.check(handle, AkmNative.uploadRows(handle, buf, filled));
+                    AkmNative.check(handle, AkmNative.uploadRowsPrepared(handle, buf, filled));
                     filled = 0;
                 }
             }
             if (filled > 0) {
-                AkmNative.check(handle, AkmNative.uploadRows(handle, buf, filled));
+                AkmNative.check(handle, AkmNative.uploadRowsPrepared(handle, buf, filled));
             }
+            AkmNative.check(handle, AkmNative.uploadWait(handle));
         }
         // DenseMatrix is column-major d x k0 == row-major k0 x d: pass the backing array as is
         AkmNative.check(handle, AkmNative.assignAccumulate(handle, centroids.f1.getVectors().getData(), k0, k,
