@@ -22,9 +22,12 @@ int akm_fail(akm_handle h, int code, const std::string &msg) {
 #define REQUIRE(h, cond, msg) \
     do { if (!(cond)) return akm_fail((h), AKM_ERR_BADARG, (msg)); } while (0)
 
-static int bind_device(akm_handle h) {
+static int upload_resolve(akm_handle h);
+static int bind_device(akm_handle h, bool uploading = false) {
     if (!h) return akm_fail(nullptr, AKM_ERR_BADARG, "null handle");
     AKM_CUDA(h, cudaSetDevice(h->device));
+    // anything but a further upload wants the rows as they will finally be stored
+    if (!uploading && (h->pend[0].active || h->pend[1].active)) return upload_resolve(h);
     return AKM_OK;
 }
 
@@ -43,10 +46,23 @@ static void dev_free(T *&p) {
 }
 
 static void rowstore_free(RowStore &rs) {
-    dev_free(rs.x32); dev_free(rs.x64); dev_free(rs.xlabel); dev_free(rs.x16); dev_free(rs.xerr); dev_free(rs.orig);
+    if (rs.x_alloc) cudaFree(rs.x_alloc);
+    if (rs.x16_alloc) cudaFree(rs.x16_alloc);
+    rs.x_alloc = nullptr; rs.x16_alloc = nullptr; rs.x32 = nullptr; rs.x64 = nullptr; rs.x16 = nullptr;
+    rs.x_head = rs.x_off = rs.x16_head = rs.x16_off = 0;
+    dev_free(rs.xlabel); dev_free(rs.xerr); dev_free(rs.orig);
     rs.n = rs.cap = 0;
     rs.x16_valid = false;
     rs.x16_cap = 0; rs.orig_cap = rs.orig_n = 0; rs.reordered = false;
+}
+
+// allocate the exact copy for `cap` rows of `store` bytes per value (+ regrouping headroom), data at offset 0
+static int rowstore_alloc_x(akm_handle h, RowStore &rs, int store, int64_t cap, void **out, int64_t *head_out) {
+    const int64_t head = reorder_head_rows(h, rs, store, cap);
+    *out = nullptr;
+    AKM_CUDA(h, cudaMalloc(out, std::max<size_t>(1, (size_t)(cap + head) * (size_t)h->d * (size_t)store)));
+    *head_out = head;
+    return AKM_OK;
 }
 
 // Grow (or create) the exact store so that `need` rows fit; keeps existing rows.
@@ -57,21 +73,15 @@ static int rowstore_reserve(akm_handle h, RowStore &rs, int64_t need) {
     double *nl = nullptr;
     AKM_TRY(dev_alloc(h, &nl, (size_t)cap));
     if (rs.n > 0) AKM_CUDA(h, cudaMemcpyAsync(nl, rs.xlabel, sizeof(double) * (size_t)rs.n, cudaMemcpyDeviceToDevice, h->stream));
-    if (rs.store == 4) {
-        float *nx = nullptr;
-        AKM_TRY(dev_alloc(h, &nx, (size_t)cap * d));
-        if (rs.n > 0) AKM_CUDA(h, cudaMemcpyAsync(nx, rs.x32, sizeof(float) * (size_t)rs.n * d, cudaMemcpyDeviceToDevice, h->stream));
-        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
-        dev_free(rs.x32);
-        rs.x32 = nx;
-    } else {
-        double *nx = nullptr;
-        AKM_TRY(dev_alloc(h, &nx, (size_t)cap * d));
-        if (rs.n > 0) AKM_CUDA(h, cudaMemcpyAsync(nx, rs.x64, sizeof(double) * (size_t)rs.n * d, cudaMemcpyDeviceToDevice, h->stream));
-        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
-        dev_free(rs.x64);
-        rs.x64 = nx;
-    }
+    void *nx = nullptr;
+    int64_t head = 0;
+    AKM_TRY(rowstore_alloc_x(h, rs, rs.store, cap, &nx, &head));
+    const void *old = rs.store == 4 ? (const void *)rs.x32 : (const void *)rs.x64;
+    if (rs.n > 0) AKM_CUDA(h, cudaMemcpyAsync(nx, old, (size_t)rs.store * (size_t)rs.n * d, cudaMemcpyDeviceToDevice, h->stream));
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (rs.x_alloc) cudaFree(rs.x_alloc);
+    rs.x_alloc = nx; rs.x_head = head; rs.x_off = 0;
+    if (rs.store == 4) { rs.x32 = (float *)nx; rs.x64 = nullptr; } else { rs.x64 = (double *)nx; rs.x32 = nullptr; }
     dev_free(rs.xlabel);
     rs.xlabel = nl;
     rs.cap = cap;
@@ -81,12 +91,15 @@ static int rowstore_reserve(akm_handle h, RowStore &rs, int64_t need) {
 
 // fp32 -> fp64 storage migration (lossless: every stored value was fp32-exact; COSINE rows get normalised here)
 static int rowstore_widen(akm_handle h, RowStore &rs) {
-    double *nx = nullptr;
-    AKM_TRY(dev_alloc(h, &nx, (size_t)rs.cap * (size_t)h->d));
-    AKM_TRY(launch_widen_rows(h, rs.x32, rs.xlabel, nx, rs.n));
+    void *nx = nullptr;
+    int64_t head = 0;
+    AKM_TRY(rowstore_alloc_x(h, rs, 8, rs.cap, &nx, &head));
+    AKM_TRY(launch_widen_rows(h, rs.x32, rs.xlabel, (double *)nx, rs.n));
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
-    dev_free(rs.x32);
-    rs.x64 = nx;
+    if (rs.x_alloc) cudaFree(rs.x_alloc);
+    rs.x_alloc = nx; rs.x_head = head; rs.x_off = 0;
+    rs.x32 = nullptr;
+    rs.x64 = (double *)nx;
     rs.store = 8;
     rs.x16_valid = false;
     return AKM_OK;
@@ -99,7 +112,7 @@ static int rowstore_widen(akm_handle h, RowStore &rs) {
 // chunk survives the round trip -- the usual case for feature vectors -- so it crosses PCIe at 4 bytes per value;
 // a chunk with any other value is sent as doubles and switches the partition to fp64 storage.
 constexpr size_t UPLOAD_HALF_BYTES = (size_t)64 << 20;
-constexpr int UPLOAD_MAX_THREADS = 8;
+constexpr int UPLOAD_MAX_THREADS = 32;
 
 static int upload_threads() {
     static const int n = [] {
@@ -247,6 +260,29 @@ static void pin_finish(akm_handle h) {
 
 enum SrcKind { SRC_HOST_F64, SRC_HOST_F32, SRC_DEV_F32 };
 
+// Chunks of doubles that went from page-locked caller memory straight into fp32 storage are checked after the fact
+// (the device flags values that are not fp32 values).  Their source doubles are still in the device staging halves,
+// so a misfit is repaired without the caller's buffer: the partition is widened and the chunk prepared again.
+static int upload_resolve(akm_handle h) {
+    if (!h->pend[0].active && !h->pend[1].active) return AKM_OK;
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+    const bool bad0 = h->pend[0].active && h->h_iscal[10] != 0, bad1 = h->pend[1].active && h->h_iscal[11] != 0;
+    if ((bad0 || bad1) && h->rows.store == 4) {
+        const size_t dhalf = h->stage_bytes / 2;
+        const int64_t n_keep = h->rows.n;
+        AKM_TRY(rowstore_widen(h, h->rows));
+        for (int slot = 0; slot < 2; ++slot) {
+            if (!((slot == 0) ? bad0 : bad1)) continue;
+            AKM_TRY(launch_prep_rows(h, h->rows, (char *)h->stage + (size_t)slot * dhalf, false, h->pend[slot].row0,
+                                     h->pend[slot].rows, h->pend[slot].prepared, h->iscal + 10 + slot));
+        }
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+        h->rows.n = n_keep;
+    }
+    h->pend[0].active = h->pend[1].active = false;
+    return AKM_OK;
+}
+
 // Appends the rows; returns when the last chunk is staged (copies and kernels still in flight on h->stream).
 static int upload_rows(akm_handle h, RowStore &rs, const void *src, SrcKind kind, int64_t n, bool prepared = false) {
     if (n == 0) return AKM_OK;
@@ -266,14 +302,45 @@ static int upload_rows(akm_handle h, RowStore &rs, const void *src, SrcKind kind
         int64_t chunk = (int64_t)std::max<size_t>(1, UPLOAD_HALF_BYTES / row_bytes);
         chunk = std::min<int64_t>(chunk, n);
         const size_t half = (size_t)chunk * row_bytes;
+        if (h->stage_bytes < 2 * half) AKM_TRY(upload_resolve(h));      // the halves are about to be reallocated
         AKM_TRY(ensure_upload_stage(h, half));
         const size_t hhalf = h->hstage_bytes / 2, dhalf = h->stage_bytes / 2;
-        for (int64_t off = 0; off < n; off += chunk) {
+        // a source in page-locked memory (akm_host_alloc, or registered by the caller) is read by the DMA engine
+        // directly: no staging copy, no narrowing -- PCIe, not the host's memory bandwidth, sets the rate
+        cudaPointerAttributes pa{};
+        const bool pinned_src = &rs == &h->rows && cudaPointerGetAttributes(&pa, src) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+        if (!pinned_src) cudaGetLastError();
+        for (int64_t off = 0; pinned_src && off < n; off += chunk) {
+            const int slot = h->stage_slot;
+            h->stage_slot ^= 1;
+            const int64_t m = std::min<int64_t>(chunk, n - off);
+            char *dbuf = (char *)h->stage + (size_t)slot * dhalf;
+            // the chunk that used this half two chunks ago: done by now -- was every value of it an fp32 value?
+            if (h->pend[slot].active) {
+                AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot]));
+                if (h->h_iscal[10 + slot] != 0) AKM_TRY(upload_resolve(h));
+                h->pend[slot].active = false;
+            }
+            const bool as_f32 = kind == SRC_HOST_F32;
+            const bool check = !as_f32 && rs.store == 4;     // doubles into fp32 storage: the device reports misfits
+            if (check) AKM_CUDA(h, cudaMemsetAsync(h->iscal + 10 + slot, 0, sizeof(int), h->stream));
+            AKM_CUDA(h, cudaMemcpyAsync(dbuf, (const char *)src + (size_t)off * row_bytes, (size_t)m * row_bytes, cudaMemcpyHostToDevice, h->stream));
+            AKM_TRY(launch_prep_rows(h, rs, dbuf, as_f32, rs.n, m, prepared, h->iscal + 10 + slot));
+            if (check) {
+                AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 10 + slot, h->iscal + 10 + slot, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+                h->pend[slot] = {true, prepared, rs.n, m};
+            }
+            AKM_CUDA(h, cudaEventRecord(h->stage_free[slot], h->stream));
+            h->stage_used[slot] = true;
+            rs.n += m;
+        }
+        for (int64_t off = 0; !pinned_src && off < n; off += chunk) {
             const int slot = h->stage_slot;
             h->stage_slot ^= 1;
             const int64_t m = std::min<int64_t>(chunk, n - off);
             char *hbuf = (char *)h->hstage + (size_t)slot * hhalf;
             char *dbuf = (char *)h->stage + (size_t)slot * dhalf;
+            if (h->pend[slot].active) AKM_TRY(upload_resolve(h));
             if (h->stage_used[slot]) AKM_CUDA(h, cudaEventSynchronize(h->stage_free[slot]));   // DMA + kernel of two chunks ago are done
             const char *sp = (const char *)src + (size_t)off * row_bytes;
             bool as_f32 = kind == SRC_HOST_F32;
@@ -430,7 +497,7 @@ static int maybe_reorder(akm_handle h, int k) {
     if (env == 0) return AKM_OK;
     if (h->stats.engine_used != AKM_ENGINE_TENSOR || h->rows.n < h->reorder_min_rows) return AKM_OK;
     h->changed_since_reorder++;                       // tensor passes since the last regrouping (or since upload)
-    bool go = !h->rows.reordered && h->changed_since_reorder >= h->regroup_after;
+    bool go = !h->rows.reordered && h->changed_since_reorder >= h->regroup_after;   // default 2: the first labels move a lot
     if (!go && h->rows.reordered && (int64_t)h->h_iscal[6] * 4 > h->rows.n) go = true;
     if (!go) return AKM_OK;
     if (h->profiling) cudaEventRecord(h->pev[3], h->stream);
@@ -518,7 +585,7 @@ int akm_destroy(akm_handle h) {
     scratch_free(h);
     rowstore_free(h->rows);
     rowstore_free(h->batch);
-    dev_free(h->labels); dev_free(h->mind); dev_free(h->labels_acc); dev_free(h->sum_local);
+    dev_free(h->labels); dev_free(h->mind); dev_free(h->labels_acc); dev_free(h->sum_local); dev_free(h->sum_tmp);
     for (int i = 0; i < 2; ++i) { dev_free(h->cent[i]); dev_free(h->clabel[i]); }
     dev_free(h->sum); dev_free(h->cmap); dev_free(h->inv); dev_free(h->shift); dev_free(h->dscal); dev_free(h->iscal);
     dev_free(h->init_cost); dev_free(h->init_near); dev_free(h->init_rows); dev_free(h->init_out);
@@ -562,17 +629,31 @@ int akm_reserve_rows(akm_handle h, int64_t n_total) {
 }
 
 int akm_upload_rows(akm_handle h, const double *x_host, int64_t n) {
-    AKM_TRY(bind_device(h));
+    AKM_TRY(bind_device(h, /*uploading=*/true));
     REQUIRE(h, n >= 0, "negative row count");
     REQUIRE(h, n == 0 || x_host, "rows pointer is null");
     return upload_rows(h, h->rows, x_host, SRC_HOST_F64, n);
 }
 
 int akm_upload_rows_prepared(akm_handle h, const double *x_host, int64_t n) {
-    AKM_TRY(bind_device(h));
+    AKM_TRY(bind_device(h, /*uploading=*/true));
     REQUIRE(h, n >= 0, "negative row count");
     REQUIRE(h, n == 0 || x_host, "rows pointer is null");
     return upload_rows(h, h->rows, x_host, SRC_HOST_F64, n, /*prepared=*/true);
+}
+
+int akm_host_alloc(size_t bytes, void **out) {
+    if (!out) return akm_fail(nullptr, AKM_ERR_BADARG, "out is null");
+    *out = nullptr;
+    cudaError_t e = cudaHostAlloc(out, std::max<size_t>(bytes, 1), cudaHostAllocPortable);
+    if (e != cudaSuccess) return akm_fail(nullptr, e == cudaErrorMemoryAllocation ? AKM_ERR_OOM : AKM_ERR_CUDA,
+                                          std::string("cudaHostAlloc: ") + cudaGetErrorString(e));
+    return AKM_OK;
+}
+
+int akm_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+    return AKM_OK;
 }
 
 int akm_upload_wait(akm_handle h) {
@@ -582,7 +663,7 @@ int akm_upload_wait(akm_handle h) {
 }
 
 int akm_upload_rows_f32(akm_handle h, const float *x_host, int64_t n) {
-    AKM_TRY(bind_device(h));
+    AKM_TRY(bind_device(h, /*uploading=*/true));
     REQUIRE(h, n >= 0, "negative row count");
     REQUIRE(h, n == 0 || x_host, "rows pointer is null");
     return upload_rows(h, h->rows, x_host, SRC_HOST_F32, n);
@@ -721,6 +802,8 @@ int akm_superstep(akm_handle h, const double *centroids, int k0, int k, int step
     if (h->rows.n > 0) absorb_tensor_stats(h);
     accumulate_absorb(h);
     *k_out = h->h_iscal[0];
+    // the host will pass the compacted buffer back with the new k: the next labels use the new numbering
+    if (*k_out != k) AKM_TRY(accumulate_renumber(h, s->cmap, k, k0));
     if (converged_out) *converged_out = h->h_iscal[1];
     if (objective_out) *objective_out = h->h_dscal[0];
     if (shift_out && *k_out > 0) {
@@ -744,6 +827,11 @@ int akm_set_centroids(akm_handle h, const double *c0, int k0) {
     AKM_CUDA(h, cudaMemcpyAsync(h->cent[1], h->cent[0], sizeof(double) * kd, cudaMemcpyDeviceToDevice, h->stream));
     AKM_CUDA(h, cudaMemcpyAsync(h->clabel[1], h->clabel[0], sizeof(double) * (size_t)k0, cudaMemcpyDeviceToDevice, h->stream));
     AKM_CUDA(h, cudaMemsetAsync(h->sum, 0, sizeof(double) * ((size_t)k0 * (h->d + 1) + 2), h->stream));
+    // step 0 also prepares what the supersteps would otherwise build or allocate on their first pass
+    if (h->rows.n > 0) {
+        AKM_TRY(ensure_labels(h, h->rows.n));
+        if (h->engine != AKM_ENGINE_EXACT) AKM_TRY(tensor_warm(h, h->rows, k0));
+    }
     AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     h->k0 = k0; h->k = k0; h->step = 0;
     tensor_invalidate_seeds(h);
@@ -784,6 +872,7 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     if (h->rows.n > 0) absorb_tensor_stats(h);
     accumulate_absorb(h);
     h->k = h->h_iscal[0];
+    if (h->k != k_before) AKM_TRY(accumulate_renumber(h, h->cmap, k_before, k0));   // clusters were dropped
     if (prof) {
         float a = 0.f, b = 0.f, c = 0.f, m1 = 0.f;
         cudaEventElapsedTime(&a, h->pev[0], h->pev[1]);
@@ -1173,6 +1262,8 @@ extern "C" int akm_set_option(akm_handle h, const char *name, double value) {
     if (strcmp(name, "reorder_min_rows") == 0) { h->reorder_min_rows = (int64_t)value; return AKM_OK; }
     if (strcmp(name, "tile_pruning") == 0) { h->tile_pruning = value != 0.0; return AKM_OK; }
     if (strcmp(name, "delta_accumulate") == 0) { h->delta_accumulate = value != 0.0; h->acc_valid = false; h->last_changed = -1; return AKM_OK; }
+    if (strcmp(name, "merge_rotate") == 0) { h->merge_rotate = value != 0.0; return AKM_OK; }
+    if (strcmp(name, "epi_dbg") == 0) { h->epi_dbg = (int)value; return AKM_OK; }
     if (strcmp(name, "regroup_after") == 0) { h->regroup_after = std::max(1, (int)value); return AKM_OK; }
     return akm_fail(h, AKM_ERR_BADARG, std::string("unknown option: ") + name);
 }

@@ -31,6 +31,12 @@ struct RowStore {
     bool want16 = false;
     int x16_shift = 0;        // x16 = fp16(x * 2^x16_shift)
     bool x16_valid = false;
+    // Headroom for the regrouping (reorder.cu): the two wide arrays are allocated with `head` extra rows and the data
+    // starts at row offset 0 or >= one wave inside its allocation; a regrouping moves every wave of rows into the
+    // space the previous wave left, so the rows cross HBM once instead of twice.
+    void *x_alloc = nullptr; int64_t x_head = 0, x_off = 0;        // allocation behind x32 / x64
+    __half *x16_alloc = nullptr; int64_t x16_head = 0, x16_off = 0;
+    uint64_t x16_gen = 0;     // bumped whenever x16 is rebuilt (the search seeds refer to one generation)
     // cluster-ordered layout (reorder.cu): orig[pos] = caller's row index of the row now stored at pos
     int32_t *orig = nullptr; int64_t orig_cap = 0, orig_n = 0;
     bool reordered = false;
@@ -63,6 +69,7 @@ struct akm_handle_s {
     // incremental accumulation (kernels_exact.cu, accumulate_step): sums of this partition and the label every
     // row was added under
     double *sum_local = nullptr; int sum_local_k0 = 0;
+    double *sum_tmp = nullptr; int sum_tmp_k0 = 0;    // renumbering target (accumulate_renumber), swapped with sum_local
     int32_t *labels_acc = nullptr; int64_t labels_acc_cap = 0;
     bool acc_valid = false, acc_count_pending = false, xl_total_valid = false, delta_accumulate = true;
     int acc_k0 = 0, acc_delta_passes = 0, acc_mode_last = 0;
@@ -81,6 +88,8 @@ struct akm_handle_s {
     void *hstage = nullptr; size_t hstage_bytes = 0;     // pinned host staging (two halves)
     cudaEvent_t stage_free[2] = {nullptr, nullptr};      // half i of both buffers may be refilled
     bool stage_used[2] = {false, false}; int stage_slot = 0;
+    struct PendingChunk { bool active; bool prepared; int64_t row0, rows; };   // fp32-fit check still owed (akm_api.cu)
+    PendingChunk pend[2] = {{false, false, 0, 0}, {false, false, 0, 0}};
     // pinned bounce arena for the few-MB host buffers of the per-superstep calls (centroids, accumulator):
     // copies from/to pageable memory would be staged by the driver and block the calling thread one by one
     char *pin = nullptr; size_t pin_bytes = 0, pin_off = 0;
@@ -107,8 +116,10 @@ struct akm_handle_s {
     int reorders = 0;
     double reorder_ms = 0;
     int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
-    int regroup_after = 1;                // regroup once this many tensor-engine passes have produced labels
+    int regroup_after = 2;                // regroup once this many tensor-engine passes have produced labels
     bool sum_dev_is_local = false;        // Scratch::sum still holds what akm_assign_accumulate returned
+    bool merge_rotate = true;             // search epilogue: rotate the per-group merge over the four quarter warps
+    int epi_dbg = 0;                      // timing experiments on the search epilogue (results invalid when != 0)
     bool tile_pruning = true;             // skip (row group, centroid tile) pairs the triangle inequality rules out
 
     // optional per-phase profiling of akm_step
@@ -149,7 +160,7 @@ int download_pipelined(akm_handle h, const void *dev, void *host, size_t bytes);
 // prepareVectorData over `n` staged rows (src: double or float, row-major) appended at row `row0`.
 // prepared: the caller already ran prepareVectorData (COSINE rows are stored as given, not normalised again)
 int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n,
-                     bool prepared = false);
+                     bool prepared = false, int *inexact_flag = nullptr);
 // widen rows [0,n) of x32 into x64 (storage migration)
 int launch_widen_rows(akm_handle h, const float *x32, const double *xlabel, double *x64, int64_t n);
 // updateLabel on k0 centroids in place (EUCL: labels; COS: normalise rows unless cos_normalise == false,
@@ -174,6 +185,8 @@ int launch_update(akm_handle h, const double *sum, int k, int k0, double *Cnew, 
 // doubles = sums, objective of this partition, no-finite-distance flag.  accumulate_absorb() after h_iscal[8] is back.
 int accumulate_step(akm_handle h, const double *C, const double *clabel, int k0, double *sum_out);
 void accumulate_absorb(akm_handle h);
+// after an update that dropped clusters: renumber the incremental sums and their label record by `cmap` (device)
+int accumulate_renumber(akm_handle h, const int *cmap, int k_old, int k0);
 int launch_flag_from_sum(akm_handle h, const double *flag);
 // probs from all distances (getProbArrayFromDistanceArray)
 int launch_probs(akm_handle h, const double *dist_all, int64_t n, int k, double *probs);
@@ -186,6 +199,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
                   int32_t *labels, double *mind, int chain, const int *remap);
 void tensor_invalidate_seeds(akm_handle h);
 int tensor_prepare_x16(akm_handle h, RowStore &rs);
+int tensor_warm(akm_handle h, RowStore &rs, int k0);
 void tensor_free(akm_handle h);
 
 // ---------------------------------------------------------------- akm_nccl.cu
@@ -195,6 +209,8 @@ void nccl_destroy(akm_handle h);
 // ---------------------------------------------------------------- reorder.cu
 int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *useed, int k);
 int reorder_reserve(akm_handle h, const RowStore &rs, int64_t n);
+// rows of headroom the wide arrays of a partition of `cap` rows get (0: the partition is never regrouped)
+int64_t reorder_head_rows(akm_handle h, const RowStore &rs, int store, int64_t cap);
 int ensure_orig(akm_handle h, RowStore &rs);
 int copy_rows_out_i32(akm_handle h, const RowStore &rs, const int32_t *dev, int32_t *host, int64_t n);
 int copy_rows_out_i64(akm_handle h, const RowStore &rs, const int64_t *dev, int64_t *host, int64_t n);

@@ -110,11 +110,12 @@ prep_rows_kernel(const SrcT *__restrict__ src, int64_t n, int d, int64_t row0, f
     if (STORE == 4 && inexact) atomicExch(inexact_flag, 1);
 }
 
-int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n, bool prepared) {
+int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n, bool prepared,
+                     int *inexact_flag) {
     if (n <= 0) return AKM_OK;
     const unsigned grid = (unsigned)ceil_div64(n, PREP_ROWS);
     double *sx = h->dscal + 1;
-    int *flag = h->iscal + 3;
+    int *flag = inexact_flag ? inexact_flag : h->iscal + 3;
 #define PREP_LAUNCH(SRC, M, ST)                                                              \
     prep_rows_kernel<SRC, M, ST><<<grid, PREP_ROWS, 0, h->stream>>>((const SRC *)src, n, h->d, row0, rs.x32, \
                                                                     rs.x64, rs.xlabel, sx, flag, prepared ? 1 : 0)
@@ -891,10 +892,50 @@ int accumulate_step(akm_handle h, const double *C, const double *clabel, int k0,
 
 // after the caller copied iscal[8] back (h_iscal[8] = rows moved in the pass accumulate_step just ran)
 void accumulate_absorb(akm_handle h) {
+    h->stats.accumulate_mode = h->acc_mode_last;
+    h->stats.rows_moved = h->acc_count_pending ? (int64_t)h->h_iscal[8] : -1;
     if (!h->acc_count_pending) return;
     h->acc_count_pending = false;
     h->last_changed = h->h_iscal[8];
     if (h->acc_mode_last == 1) h->acc_changed_total += h->h_iscal[8];
+}
+
+// KMeansUpdateCentroids drops empty clusters and renumbers the rest (cmap: old index -> new index, -1 = dropped).
+// The next pass's labels use the new numbering, so the record behind the incremental sums follows: otherwise
+// nearly every row would look "moved" and the next pass would fall back to a full accumulation.
+__global__ void remap_labels_kernel(int32_t *__restrict__ labels_acc, int64_t n, const int *__restrict__ cmap, int k_old) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const int la = labels_acc[i];
+        if (la >= 0 && la < k_old) labels_acc[i] = cmap[la];
+    }
+}
+__global__ void remap_sums_kernel(const double *__restrict__ src, double *__restrict__ dst, const int *__restrict__ cmap,
+                                  int k_old, int d) {
+    const int j = blockIdx.x;
+    if (j >= k_old) return;
+    const int m = cmap[j];
+    if (m < 0) return;
+    for (int c = threadIdx.x; c <= d; c += blockDim.x) dst[(size_t)m * (d + 1) + c] = src[(size_t)j * (d + 1) + c];
+}
+int accumulate_renumber(akm_handle h, const int *cmap, int k_old, int k0) {
+    if (!h->acc_valid || !h->sum_local || !h->labels_acc || h->acc_k0 != k0 || h->rows.n <= 0) return AKM_OK;
+    const size_t L = (size_t)k0 * (size_t)(h->d + 1);
+    if (h->sum_tmp_k0 < k0) {
+        if (h->sum_tmp) cudaFree(h->sum_tmp);
+        h->sum_tmp = nullptr; h->sum_tmp_k0 = 0;
+        AKM_CUDA(h, cudaMalloc((void **)&h->sum_tmp, sizeof(double) * (L + 2)));
+        h->sum_tmp_k0 = k0;
+    }
+    AKM_CUDA(h, cudaMemsetAsync(h->sum_tmp, 0, sizeof(double) * L, h->stream));
+    remap_sums_kernel<<<k_old, 128, 0, h->stream>>>(h->sum_local, h->sum_tmp, cmap, k_old, h->d);
+    remap_labels_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(h->labels_acc, h->rows.n, cmap, k_old);
+    h->stats.kernel_launches += 2;
+    AKM_CUDA(h, cudaGetLastError());
+    std::swap(h->sum_local, h->sum_tmp);
+    std::swap(h->sum_local_k0, h->sum_tmp_k0);
+    return AKM_OK;
 }
 
 // if some rank flagged a row without a finite distance, every rank raises the error (sum[L+1] was all-reduced)

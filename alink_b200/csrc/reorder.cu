@@ -155,17 +155,32 @@ int ensure_orig(akm_handle h, RowStore &rs) {
     return AKM_OK;
 }
 
-// Scratch of the regrouping for a partition of n rows: one wave of rows (as many 32K-row chunks as fit 4 GB) and the
-// destination index of every row.  akm_reserve_rows calls this up front so that no cudaMalloc (which stalls the
-// device) lands inside the first supersteps of a training run.
+// A wave = the rows regrouped together (a cluster's rows end up contiguous inside each wave): as many 32K-row
+// chunks as make ~4 GB of the widest per-row array.
+static int64_t wave_chunks_for(int d, int store, int64_t nchunks) {
+    const size_t xbytes = (size_t)d * (size_t)store;
+    const size_t max_row = std::max(xbytes, std::max<size_t>((size_t)((d + 7) / 8) * 16, 8));   // rows, fp16 copy, side arrays
+    const size_t budget = (size_t)4 << 30;
+    return std::min<int64_t>(std::max<int64_t>(1, (int64_t)(budget / (max_row * REORDER_CHUNK))), std::max<int64_t>(nchunks, 1));
+}
+
+int64_t reorder_head_rows(akm_handle h, const RowStore &rs, int store, int64_t cap) {
+    if (&rs != &h->rows || h->engine == AKM_ENGINE_EXACT || cap < h->reorder_min_rows || cap >= ((int64_t)1 << 31)) return 0;
+    return wave_chunks_for(h->d, store, ceil_div64(cap, REORDER_CHUNK)) * REORDER_CHUNK;
+}
+
+// Scratch of the regrouping for a partition of n rows: one wave of the narrow per-row arrays (8 bytes per row; the
+// wide arrays move inside their own allocations, see RowStore) or, for a store without headroom, of the widest
+// array; plus the destination index of every row.  akm_reserve_rows calls this up front so that no cudaMalloc
+// (which stalls the device) lands inside the first supersteps of a training run.
 int reorder_reserve(akm_handle h, const RowStore &rs, int64_t n) {
     if (n <= 0 || n >= ((int64_t)1 << 31)) return AKM_OK;
-    const size_t xbytes = (size_t)h->d * (rs.store == 4 ? 4 : 8);
-    const size_t max_row = std::max(xbytes, std::max<size_t>((size_t)((h->d + 7) / 8) * 16, 8));   // rows, fp16 copy, side arrays
-    const size_t budget = (size_t)4 << 30;
     const int64_t nchunks = ceil_div64(n, REORDER_CHUNK);
-    const int64_t wave_chunks = std::min<int64_t>(std::max<int64_t>(1, (int64_t)(budget / (max_row * REORDER_CHUNK))), nchunks);
-    const size_t need = (size_t)wave_chunks * REORDER_CHUNK * max_row;
+    const int64_t wave_rows = wave_chunks_for(h->d, rs.store, nchunks) * REORDER_CHUNK;
+    const bool shifting = rs.x_head >= wave_rows && (!rs.x16_alloc || rs.x16_head >= wave_rows);
+    const size_t xbytes = (size_t)h->d * (size_t)rs.store;
+    const size_t max_row = shifting ? 32 : std::max(xbytes, std::max<size_t>((size_t)((h->d + 7) / 8) * 16, 32));   // 28 B of narrow arrays
+    const size_t need = (size_t)wave_rows * max_row;
     if (h->reorder_scratch_bytes < need) {
         if (h->reorder_scratch) cudaFree(h->reorder_scratch);
         h->reorder_scratch = nullptr; h->reorder_scratch_bytes = 0;
@@ -181,7 +196,101 @@ int reorder_reserve(akm_handle h, const RowStore &rs, int64_t n) {
     return AKM_OK;
 }
 
-// Regroup the rows of `rs` by `labels` inside chunks.  labels / useed are permuted with the rows.
+// dst[dest[r]] = src[r] for rows r in [row0, row0 + rows) (src and dst are the data pointers before / after the move).
+// A warp takes four rows at a time so that four row loads (and their destination indices) are in flight per lane:
+// the kernel is a scattered copy and lives on memory-level parallelism.
+template <typename U>
+__global__ void __launch_bounds__(256)
+move_rows_kernel(const U *__restrict__ src, U *__restrict__ dst, const int32_t *__restrict__ dest,
+                 int64_t row0, int64_t rows, int units_per_row) {
+    const int lane = threadIdx.x & 31;
+    int64_t w = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 4;
+    const int64_t stride = (((int64_t)gridDim.x * blockDim.x) >> 5) * 4;
+    for (; w < rows; w += stride) {
+        const int cnt = (int)min((int64_t)4, rows - w);
+        int64_t t[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) t[i] = (i < cnt) ? (int64_t)dest[row0 + w + i] : 0;
+        for (int u = lane; u < units_per_row; u += 32) {
+            U v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) if (i < cnt) v[i] = src[(row0 + w + i) * units_per_row + u];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) if (i < cnt) dst[t[i] * units_per_row + u] = v[i];
+        }
+    }
+}
+
+// The narrow per-row arrays of one wave in one launch, one thread per row: scatter into the scratch (laid out as
+// five consecutive arrays of `rows` entries), then copy back.  (A warp per 4- or 8-byte row would leave 30 lanes idle.)
+__global__ void __launch_bounds__(256)
+move_narrow_kernel(const int32_t *__restrict__ dest, int64_t row0, int64_t rows, const double *__restrict__ xlabel,
+                   const float2 *__restrict__ xerr, const int32_t *__restrict__ orig, const float *__restrict__ useed,
+                   const int32_t *__restrict__ labels, char *__restrict__ scratch) {
+    double *s_xl = reinterpret_cast<double *>(scratch);
+    float2 *s_xe = reinterpret_cast<float2 *>(scratch + (size_t)rows * 8);
+    int32_t *s_or = reinterpret_cast<int32_t *>(scratch + (size_t)rows * 16);
+    float *s_us = reinterpret_cast<float *>(scratch + (size_t)rows * 20);
+    int32_t *s_lb = reinterpret_cast<int32_t *>(scratch + (size_t)rows * 24);
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < rows; i += stride) {
+        const int64_t r = row0 + i;
+        const int64_t t = (int64_t)dest[r] - row0;
+        s_xl[t] = xlabel[r];
+        if (xerr) s_xe[t] = xerr[r];
+        s_or[t] = orig[r];
+        if (useed) s_us[t] = useed[r];
+        s_lb[t] = labels[r];
+    }
+}
+__global__ void __launch_bounds__(256)
+copy_narrow_back_kernel(int64_t row0, int64_t rows, double *__restrict__ xlabel, float2 *__restrict__ xerr,
+                        int32_t *__restrict__ orig, float *__restrict__ useed, int32_t *__restrict__ labels,
+                        const char *__restrict__ scratch) {
+    const double *s_xl = reinterpret_cast<const double *>(scratch);
+    const float2 *s_xe = reinterpret_cast<const float2 *>(scratch + (size_t)rows * 8);
+    const int32_t *s_or = reinterpret_cast<const int32_t *>(scratch + (size_t)rows * 16);
+    const float *s_us = reinterpret_cast<const float *>(scratch + (size_t)rows * 20);
+    const int32_t *s_lb = reinterpret_cast<const int32_t *>(scratch + (size_t)rows * 24);
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < rows; i += stride) {
+        const int64_t r = row0 + i;
+        xlabel[r] = s_xl[i];
+        if (xerr) xerr[r] = s_xe[i];
+        orig[r] = s_or[i];
+        if (useed) useed[r] = s_us[i];
+        labels[r] = s_lb[i];
+    }
+}
+
+// One wide array (rows of row_bytes, data at row offset `off` of an allocation with `head` spare rows): every wave
+// moves into the space next to it -- towards the front when the data sits behind the headroom (waves in ascending
+// order: wave i lands where wave i-1 was), towards the back otherwise (descending order).  Returns the new offset.
+static int shift_array(akm_handle h, char *alloc, size_t row_bytes, int64_t off, int64_t wave_rows, int64_t n,
+                       const int32_t *dest, int64_t *new_off) {
+    const bool down = off > 0;                               // off >= wave_rows was checked by the caller
+    const int64_t noff = down ? 0 : wave_rows;
+    const char *src = alloc + (size_t)off * row_bytes;
+    char *dst = alloc + (size_t)noff * row_bytes;
+    const int64_t nwaves = ceil_div64(n, wave_rows);
+    const int blocks = h->num_sms * 8;
+    for (int64_t i = 0; i < nwaves; ++i) {
+        const int64_t w = down ? i : nwaves - 1 - i;
+        const int64_t row0 = w * wave_rows, rows = std::min<int64_t>(wave_rows, n - row0);
+        if (row_bytes % 16 == 0)
+            move_rows_kernel<int4><<<blocks, 256, 0, h->stream>>>((const int4 *)src, (int4 *)dst, dest, row0, rows, (int)(row_bytes / 16));
+        else
+            move_rows_kernel<int><<<blocks, 256, 0, h->stream>>>((const int *)src, (int *)dst, dest, row0, rows, (int)(row_bytes / 4));
+        h->stats.kernel_launches++;
+    }
+    AKM_CUDA(h, cudaGetLastError());
+    *new_off = noff;
+    return AKM_OK;
+}
+
+// Regroup the rows of `rs` by `labels` inside waves.  labels / useed are permuted with the rows.
 int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *useed, int k) {
     const int64_t n = rs.n;
     if (n <= 0 || n >= ((int64_t)1 << 31)) return AKM_OK;
@@ -189,12 +298,16 @@ int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *us
     AKM_TRY(ensure_orig(h, rs));
     const int d = h->d;
     const size_t xbytes = (size_t)d * (rs.store == 4 ? 4 : 8);
-    const size_t x16bytes = (rs.x16 && rs.x16_valid && rs.x16_cap >= n) ? (size_t)rs.d16 * 2 : 0;
-    const size_t max_row = std::max(xbytes, std::max<size_t>((size_t)((d + 7) / 8) * 16, 8));      // as in reorder_reserve
+    const bool have16 = rs.x16 && rs.x16_valid && rs.x16_cap >= n;
+    const size_t x16bytes = have16 ? (size_t)rs.d16 * 2 : 0;
     AKM_TRY(reorder_reserve(h, rs, n));
-    const size_t budget = (size_t)4 << 30;
     const int64_t nchunks = ceil_div64(n, REORDER_CHUNK);
-    const int64_t wave_chunks = std::min<int64_t>(std::max<int64_t>(1, (int64_t)(budget / (max_row * REORDER_CHUNK))), nchunks);
+    const int64_t wave_chunks = wave_chunks_for(d, rs.store, nchunks);
+    const int64_t wave_rows = wave_chunks * REORDER_CHUNK;
+    // the wide arrays shift inside their allocations when both have the headroom and sit at offset 0 or >= one wave
+    const bool shift_x = rs.x_alloc && rs.x_head >= wave_rows && (rs.x_off == 0 || rs.x_off >= wave_rows) && xbytes % 4 == 0;
+    const bool shift_16 = !have16 || (rs.x16_alloc && rs.x16_head >= wave_rows && (rs.x16_off == 0 || rs.x16_off >= wave_rows));
+    const bool shifting = shift_x && shift_16;
     const size_t smem = (size_t)(k + 3) * sizeof(int);
     const int64_t nwaves = ceil_div64(nchunks, wave_chunks);
     const size_t hist_bytes = ((size_t)nchunks + (size_t)nwaves) * (size_t)(k + 1) * sizeof(int);
@@ -213,20 +326,34 @@ int reorder_rows_by_label(akm_handle h, RowStore &rs, int32_t *labels, float *us
                                                                                   h->reorder_dest);
     h->stats.kernel_launches += 3;
     AKM_CUDA(h, cudaGetLastError());
+    const int32_t *dest = h->reorder_dest;
+    if (shifting) {
+        int64_t noff = 0;
+        AKM_TRY(shift_array(h, (char *)rs.x_alloc, xbytes, rs.x_off, wave_rows, n, dest, &noff));
+        rs.x_off = noff;
+        if (rs.store == 4) rs.x32 = (float *)rs.x_alloc + (size_t)noff * d; else rs.x64 = (double *)rs.x_alloc + (size_t)noff * d;
+        if (have16) {
+            AKM_TRY(shift_array(h, (char *)rs.x16_alloc, x16bytes, rs.x16_off, wave_rows, n, dest, &noff));
+            rs.x16_off = noff;
+            rs.x16 = rs.x16_alloc + (size_t)noff * rs.d16;
+        }
+    }
     for (int64_t c0 = 0; c0 < nchunks; c0 += wave_chunks) {
         const int64_t row0 = c0 * REORDER_CHUNK;
-        const int64_t rows = std::min<int64_t>(n - row0, wave_chunks * REORDER_CHUNK);
+        const int64_t rows = std::min<int64_t>(n - row0, wave_rows);
         void *sc = h->reorder_scratch;
-        const int32_t *dest = h->reorder_dest;
-        AKM_TRY(permute_array(h, rs.store == 4 ? (void *)rs.x32 : (void *)rs.x64, xbytes, dest, row0, rows, sc));
-        AKM_TRY(permute_array(h, rs.xlabel, 8, dest, row0, rows, sc));
-        if (x16bytes) {
-            AKM_TRY(permute_array(h, rs.x16, x16bytes, dest, row0, rows, sc));
-            AKM_TRY(permute_array(h, rs.xerr, 8, dest, row0, rows, sc));
+        if (!shifting) {
+            AKM_TRY(permute_array(h, rs.store == 4 ? (void *)rs.x32 : (void *)rs.x64, xbytes, dest, row0, rows, sc));
+            if (x16bytes) AKM_TRY(permute_array(h, rs.x16, x16bytes, dest, row0, rows, sc));
         }
-        AKM_TRY(permute_array(h, rs.orig, 4, dest, row0, rows, sc));
-        if (useed) AKM_TRY(permute_array(h, useed, 4, dest, row0, rows, sc));
-        AKM_TRY(permute_array(h, labels, 4, dest, row0, rows, sc));   // last: the ranks were computed from it
+        // rows % 4 == 0 for every wave but the last, whose scratch sub-arrays only need 4-byte alignment after the
+        // two 8-byte ones: pad the layout to the wave size instead of the row count
+        move_narrow_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(dest, row0, rows, rs.xlabel, x16bytes ? rs.xerr : nullptr,
+                                                                  rs.orig, useed, labels, (char *)sc);
+        copy_narrow_back_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(row0, rows, rs.xlabel, x16bytes ? rs.xerr : nullptr,
+                                                                       rs.orig, useed, labels, (const char *)sc);
+        h->stats.kernel_launches += 2;
+        AKM_CUDA(h, cudaGetLastError());
     }
     rs.reordered = true;
     return AKM_OK;

@@ -31,7 +31,8 @@ class AkmError(RuntimeError):
 class Stats(ctypes.Structure):
     _fields_ = [("rows", ctypes.c_int64), ("rows_certified", ctypes.c_int64), ("rows_refined", ctypes.c_int64),
                 ("kernel_launches", ctypes.c_int64), ("engine_used", ctypes.c_int32), ("storage_bytes", ctypes.c_int32),
-                ("rows_exact_all", ctypes.c_int64), ("tiles_total", ctypes.c_int64), ("tiles_computed", ctypes.c_int64)]
+                ("rows_exact_all", ctypes.c_int64), ("tiles_total", ctypes.c_int64), ("tiles_computed", ctypes.c_int64),
+                ("rows_moved", ctypes.c_int64), ("accumulate_mode", ctypes.c_int32), ("reserved0", ctypes.c_int32)]
 
 
 _lib = None
@@ -69,6 +70,8 @@ def lib():
         L.akm_upload_rows_f32.argtypes = [_H, _c_fp, ctypes.c_int64]
         L.akm_upload_rows_prepared.argtypes = [_H, _c_dp, ctypes.c_int64]
         L.akm_upload_wait.argtypes = [_H]
+        L.akm_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
+        L.akm_host_free.argtypes = [ctypes.c_void_p]
         L.akm_superstep.argtypes = [_H, _c_dp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double, _c_dp,
                                     ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), _c_dp, _c_dp, _c_dp]
         L.akm_upload_rows_device_f32.argtypes = [_H, ctypes.c_void_p, ctypes.c_int64]
@@ -111,6 +114,33 @@ def _dp(a):
 
 def _f64(a):
     return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class PinnedArray:
+    """A numpy view of page-locked host memory from akm_host_alloc: uploads from it skip the staging copy."""
+
+    def __init__(self, shape, dtype=np.float64):
+        self.shape = tuple(int(x) for x in shape)
+        self.dtype = np.dtype(dtype)
+        nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        self._p = ctypes.c_void_p()
+        rc = lib().akm_host_alloc(nbytes, ctypes.byref(self._p))
+        if rc:
+            raise AkmError(rc, lib().akm_last_error(None).decode())
+        buf = (ctypes.c_char * max(nbytes, 1)).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    def free(self):
+        if self._p:
+            self.array = None
+            lib().akm_host_free(self._p)
+            self._p = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.free()
 
 
 def unique_id():

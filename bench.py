@@ -440,7 +440,7 @@ def main():
     h.set_centroids(C0)
     h.set_profiling(True)
     launches_a = h.stats()["kernel_launches"]
-    step_ms = []
+    step_ms, step_info = [], []
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(stream):
@@ -449,13 +449,16 @@ def main():
             t1 = time.perf_counter()
             h.step(0.0)                                       # returns after its own stream synchronisation
             step_ms.append((time.perf_counter() - t1) * 1e3)
+            st_i = h.stats()
+            step_info.append({"moved": int(st_i["rows_moved"]), "delta": int(st_i["accumulate_mode"]),
+                              "tiles": round(st_i["tiles_computed"] / max(1, st_i["tiles_total"]), 3)})
         ev1.record(stream)
     barrier()
     fi_ms = max_over_ranks(ev0.elapsed_time(ev1))
     fi_prof = h.get_profile(reset=True)
     from_init = {"value": N * args.max_iter / (fi_ms / 1e3), "unit": "sample-iters/s", "max_iter": args.max_iter,
                  "ms_total": fi_ms, "ms_per_step_mean": fi_ms / max(1, args.max_iter),
-                 "ms_per_step": [round(x, 3) for x in step_ms],
+                 "ms_per_step": [round(x, 3) for x in step_ms], "per_step": step_info,
                  "regroup": {"count": fi_prof["reorders"], "ms": fi_prof["reorder_ms"]},
                  "phases_ms_per_step_mean": phases(fi_prof),
                  "gpu_launches": int(h.stats()["kernel_launches"] - launches_a),
@@ -587,8 +590,25 @@ def main():
             t_ret = time.perf_counter() - t0
             h2.upload_wait()
             up_s = time.perf_counter() - t0
+        # the same rows from page-locked caller memory (akm_host_alloc): no staging copy, PCIe-bound
+        pinned = None
+        try:
+            rows_p = min(Xs.shape[0], int(2e9 / (d * 8)))
+            with native.PinnedArray((rows_p, d)) as pa, native.Handle(d, args.metric, device=local_rank) as h2:
+                np.copyto(pa.array, Xs[:rows_p])
+                h2.reserve_rows(4 * rows_p)
+                h2.upload_rows(pa.array[:1024]); h2.upload_wait(); h2.clear_rows(); h2.reserve_rows(4 * rows_p)
+                t0 = time.perf_counter()
+                for _ in range(4):
+                    h2.upload_rows(pa.array)
+                h2.upload_wait()
+                dt = time.perf_counter() - t0
+                pinned = {"host_bytes": int(4 * pa.array.nbytes), "seconds": dt, "host_gbps": 4 * pa.array.nbytes / dt / 1e9,
+                          "note": "source in akm_host_alloc memory: DMA straight from the caller's buffer (doubles cross PCIe)"}
+        except Exception as e:
+            pinned = {"error": "%s: %s" % (type(e).__name__, e)}
         upload = {"rows": int(Xs.shape[0]), "host_bytes": int(Xs.nbytes), "seconds": up_s, "seconds_until_return": t_ret,
-                  "host_gbps": Xs.nbytes / up_s / 1e9,
+                  "host_gbps": Xs.nbytes / up_s / 1e9, "page_locked_source": pinned,
                   "note": "akm_upload_rows from pageable host doubles incl. prepareVectorData: copy threads narrow fp32-representable "
                           "chunks to fp32 into pinned double buffers, DMA and kernel overlap; one-off, outside the iteration"}
         del Xs

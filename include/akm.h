@@ -26,6 +26,7 @@
 #ifndef AKM_H_
 #define AKM_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -113,6 +114,15 @@ int akm_upload_rows_prepared(akm_handle h, const double *x_host, int64_t n);
  * PCIe), and every later call on the handle is ordered behind the copies.  akm_upload_wait blocks until all
  * uploaded rows are resident and reports any deferred CUDA error.  No reference counterpart. */
 int akm_upload_wait(akm_handle h);
+
+/* Page-locked host memory for upload buffers (e.g. behind a java.nio direct ByteBuffer that the Java side fills
+ * instead of a double[]).  When the source of an upload call lies in such memory (or in memory the caller registered
+ * with CUDA), the rows are read by the DMA engine straight from it: no staging copy, PCIe sets the rate.  The
+ * buffer must then stay untouched until akm_upload_wait (or any later synchronising call on the handle) returns.
+ * A partition whose doubles are all fp32-representable is still stored as fp32 (the check runs on the device).
+ * No reference counterpart. */
+int akm_host_alloc(size_t bytes, void **out);
+int akm_host_free(void *p);
 
 /* Same, but the source already lives in device memory on the handle's device (used to measure
  * the resident-data throughput and to feed data produced on the GPU). */
@@ -241,6 +251,9 @@ typedef struct {
     int64_t rows_exact_all;   /* subset of rows_refined that was evaluated against all k centroids */
     int64_t tiles_total;      /* tensor engine: (256-row groups) x (256-centroid tiles) of the last pass */
     int64_t tiles_computed;   /* ... of which were evaluated; the rest were pruned by the triangle inequality */
+    int64_t rows_moved;       /* rows whose label differs from the previous pass's (-1: no previous pass to compare with) */
+    int32_t accumulate_mode;  /* 0: the accumulator was refilled from every row, 1: only the moved rows were applied */
+    int32_t reserved0;
 } akm_stats;
 int akm_get_stats(akm_handle h, akm_stats *out);
 
@@ -248,7 +261,8 @@ int akm_get_stats(akm_handle h, akm_stats *out);
  *   "reorder_min_rows"  partitions with at least this many rows are kept grouped by cluster inside the library
  *                       (outputs are always returned in the caller's row order); default 262144, a huge value
  *                       disables it.
- *   "regroup_after"     regroup once this many tensor-engine passes have produced labels (default 1).
+ *   "regroup_after"     regroup once this many tensor-engine passes have produced labels (default 2: the labels of
+ *                       the first pass come from the initial centroids and most of them move again).
  *   "tile_pruning"      (default 1) from the second pass of a training sequence on, the tensor engine skips every
  *                       (256-row group, 256-centroid tile) pair that the triangle inequality proves free of the
  *                       argmin and of every near-tie candidate (bounds from the previous pass;

@@ -1,0 +1,31 @@
+"""Timing experiments on the search kernel (AKM_EPI_DBG modes): dense passes over 20M x 128 rows, k = 1000."""
+import os, sys, time
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from alink_b200 import native
+n, d, k = int(float(os.environ.get("ROWS", 20e6))), 128, 1000
+with native.Handle(d, native.EUCLIDEAN) as h:
+    h.reserve_rows(n)
+    h.blobs_append(20260101, k, 0, n)
+    C0 = h.blobs_rows(20260101, k, (np.arange(k, dtype=np.int64) * n) // k).astype(np.float64)
+    h.set_option("tile_pruning", int(os.environ.get("PRUNE", "0")))
+    h.set_option("delta_accumulate", 1)
+    h.set_centroids(C0)
+    h.set_profiling(True)
+    for _ in range(6):
+        h.step(0.0)
+    for rot in (1, 0, 1, 0):
+        h.set_option("merge_rotate", rot)
+        h.step(0.0)
+        h.get_profile(reset=True)
+        for _ in range(5):
+            h.step(0.0)
+        pr = h.get_profile(reset=True)
+        print("merge_rotate=%d: search %.3f ms refine %.3f" % (rot, pr["search_ms"] / pr["steps"], pr["refine_ms"] / pr["steps"]))
+    h.set_option("epi_dbg", int(os.environ.get("AKM_EPI_DBG", "0")))
+    for _ in range(1 if os.environ.get("AKM_EPI_DBG") == "9" else 5):
+        h.step(0.0)
+    p = h.get_profile()
+    st = h.stats()
+    print("raw=%s prune=%s dbg=%s rows=%d search %.3f ms refine %.3f acc %.3f (tiles %d/%d)" % (os.environ.get("RAW", "1"), os.environ.get("PRUNE", "0"), os.environ.get("AKM_EPI_DBG", "0"), n,
+          p["search_ms"] / p["steps"], p["refine_ms"] / p["steps"], p["accumulate_ms"] / p["steps"], st["tiles_computed"], st["tiles_total"]))

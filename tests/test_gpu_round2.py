@@ -176,6 +176,30 @@ def test_upload_returns_once_staged_and_mixes_fp32_and_fp64_chunks(metric):
     assert (labels[sub] == l_ref).all()
 
 
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_upload_from_page_locked_memory_skips_staging_and_repairs_misfits(metric):
+    d = 64
+    rng = np.random.default_rng(41)
+    n_a, n_b = 300_000, 200_000                               # 154 MB + 102 MB of doubles: several 64 MB chunks each
+    Xa = rng.normal(size=(n_a, d)).astype(np.float32).astype(np.float64)
+    Xb = rng.normal(size=(n_b, d)).astype(np.float32).astype(np.float64)
+    Xb[150_000, 3] = 0.1                                      # one value that is not an fp32 value, in the second chunk
+    Xall = np.vstack([Xa, Xb, Xa[:500]])
+    Xp, _ = orc.prepare_rows(metric, Xall)
+    with native.PinnedArray((n_a, d)) as pa, native.PinnedArray((n_b, d)) as pb, native.Handle(d, metric) as h:
+        np.copyto(pa.array, Xa)
+        np.copyto(pb.array, Xb)
+        h.upload_rows(pa.array)
+        assert h.num_rows() == (n_a, 4)                       # all fp32 values: fp32 storage (checked on the device)
+        h.upload_rows(pb.array)                               # returns at once; the misfit is found after the fact
+        h.upload_rows(pa.array[:500])
+        h.upload_wait()
+        assert h.num_rows() == (n_a + n_b + 500, 8)
+        pick = np.array([0, n_a - 1, n_a, n_a + 131_071, n_a + 131_072, n_a + 150_000, n_a + n_b - 1, n_a + n_b + 499],
+                        dtype=np.int64)
+        assert (h.get_rows(pick) == Xp[pick]).all()
+
+
 def test_nan_rows_go_through_the_fp64_path():
     X = blobs(2000, 8, 3, seed=1)
     X[5, 3] = np.nan
