@@ -238,15 +238,21 @@ static char *pin_take(akm_handle h, size_t bytes) {
     h->pin_off = off + bytes;
     return h->pin + off;
 }
+// host buffers that are page-locked already (akm_host_alloc, or registered by the caller) need no bounce copy
+static bool host_is_pinned(const void *p) {
+    cudaPointerAttributes pa{};
+    if (cudaPointerGetAttributes(&pa, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return pa.type == cudaMemoryTypeHost;
+}
 static int pin_h2d(akm_handle h, void *dev, const void *host, size_t bytes) {
-    char *b = pin_take(h, bytes);
+    char *b = host_is_pinned(host) ? nullptr : pin_take(h, bytes);
     if (!b) { AKM_CUDA(h, cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, h->stream)); return AKM_OK; }
     memcpy(b, host, bytes);
     AKM_CUDA(h, cudaMemcpyAsync(dev, b, bytes, cudaMemcpyHostToDevice, h->stream));
     return AKM_OK;
 }
 static int pin_d2h(akm_handle h, void *host, const void *dev, size_t bytes) {
-    char *b = pin_take(h, bytes);
+    char *b = host_is_pinned(host) ? nullptr : pin_take(h, bytes);
     if (!b) { AKM_CUDA(h, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, h->stream)); return AKM_OK; }
     AKM_CUDA(h, cudaMemcpyAsync(b, dev, bytes, cudaMemcpyDeviceToHost, h->stream));
     h->pin_out.push_back({host, b, bytes});
@@ -802,8 +808,6 @@ int akm_superstep(akm_handle h, const double *centroids, int k0, int k, int step
     if (h->rows.n > 0) absorb_tensor_stats(h);
     accumulate_absorb(h);
     *k_out = h->h_iscal[0];
-    // the host will pass the compacted buffer back with the new k: the next labels use the new numbering
-    if (*k_out != k) AKM_TRY(accumulate_renumber(h, s->cmap, k, k0));
     if (converged_out) *converged_out = h->h_iscal[1];
     if (objective_out) *objective_out = h->h_dscal[0];
     if (shift_out && *k_out > 0) {
@@ -812,7 +816,10 @@ int akm_superstep(akm_handle h, const double *centroids, int k0, int k, int step
     }
     AKM_TRY(check_error_flag(h));
     if (h->rows.n == 0) return AKM_OK;
-    return maybe_reorder(h, k);
+    AKM_TRY(maybe_reorder(h, k));
+    // the host will pass the compacted buffer back with the new k: the next labels use the new numbering
+    if (*k_out != k) AKM_TRY(accumulate_renumber(h, s->cmap, k, k0));
+    return AKM_OK;
 }
 
 int akm_set_centroids(akm_handle h, const double *c0, int k0) {
@@ -872,7 +879,6 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     if (h->rows.n > 0) absorb_tensor_stats(h);
     accumulate_absorb(h);
     h->k = h->h_iscal[0];
-    if (h->k != k_before) AKM_TRY(accumulate_renumber(h, h->cmap, k_before, k0));   // clusters were dropped
     if (prof) {
         float a = 0.f, b = 0.f, c = 0.f, m1 = 0.f;
         cudaEventElapsedTime(&a, h->pev[0], h->pev[1]);
@@ -895,7 +901,11 @@ int akm_step(akm_handle h, double tol, int *converged_out, int *k_out, double *o
     AKM_TRY(check_error_flag(h));
     if (h->rows.n == 0) return AKM_OK;
     // labels index the centroids this step assigned against (k_before clusters)
-    return maybe_reorder(h, k_before);
+    AKM_TRY(maybe_reorder(h, k_before));
+    // clusters were dropped: the next pass numbers them anew (after the regrouping, which copies the label record
+    // in the numbering the sums still have)
+    if (h->k != k_before) AKM_TRY(accumulate_renumber(h, h->cmap, k_before, k0));
+    return AKM_OK;
 }
 
 int akm_get_model(akm_handle h, double *c_out, int *k_out, double *weights_out, int *steps_out) {

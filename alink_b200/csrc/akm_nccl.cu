@@ -104,6 +104,18 @@ int akm_comm_init(akm_handle h, const void *id, int rank, int world) {
     ncclResult_t r = a->CommInitRank(&comm, world, uid, rank);
     if (r != 0) return nccl_fail(h, "ncclCommInitRank", r);
     h->comm = comm;
+    // NCCL sets its channels up on the first collective (hundreds of milliseconds): do that here, once, instead of
+    // inside the first superstep of a training run
+    if (h->ar_cap < 8) {
+        if (h->ar_buf) cudaFree(h->ar_buf);
+        h->ar_buf = nullptr; h->ar_cap = 0;
+        AKM_CUDA(h, cudaMalloc((void **)&h->ar_buf, 8 * sizeof(double)));
+        h->ar_cap = 8;
+    }
+    AKM_CUDA(h, cudaMemsetAsync(h->ar_buf, 0, 8 * sizeof(double), h->stream));
+    r = a->AllReduce(h->ar_buf, h->ar_buf, 8, kNcclDouble, kNcclSum, comm, h->stream);
+    if (r != 0) return nccl_fail(h, "ncclAllReduce (warm-up)", r);
+    AKM_CUDA(h, cudaStreamSynchronize(h->stream));
     return AKM_OK;
 }
 

@@ -253,13 +253,15 @@ class Handle:
                                             ctypes.byref(nk), _dp(shift)))
         return C, nk.value, (shift[:nk.value] if shift is not None else None)
 
-    def superstep(self, C, k=None, step_no=1, tol=0.0, want_sum=False, want_shift=False):
+    def superstep(self, C, k=None, step_no=1, tol=0.0, want_sum=False, want_shift=False, out=None):
         """akm_superstep: assign + all-reduce + update + criterion with host buffers.
-        Returns dict(C[k0,d], k, converged, objective, sum|None, shift|None)."""
-        C = _f64(C)
+        Returns dict(C[k0,d], k, converged, objective, sum|None, shift|None).  `out`: a k0 x d float64 array to receive
+        the new centroids (e.g. a PinnedArray's view: page-locked buffers skip the library's bounce copies)."""
+        if not (isinstance(C, np.ndarray) and C.dtype == np.float64 and C.flags.c_contiguous):
+            C = _f64(C)
         k0 = C.shape[0]
         k = k0 if k is None else int(k)
-        Cn = np.empty((k0, self.d), dtype=np.float64)
+        Cn = out if out is not None else np.empty((k0, self.d), dtype=np.float64)
         nk, conv, obj = ctypes.c_int(), ctypes.c_int(), ctypes.c_double()
         s = np.empty(k0 * (self.d + 1), dtype=np.float64) if want_sum else None
         shift = np.zeros(k0, dtype=np.float64) if want_shift else None
