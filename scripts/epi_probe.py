@@ -1,4 +1,6 @@
-"""Timing experiments on the search kernel (AKM_EPI_DBG modes): dense passes over 20M x 128 rows, k = 1000."""
+"""Timing experiments on the search kernel: dense (PRUNE=0) or pruned passes over ROWS x 128 rows, k = 1000, with the
+epilogue switched off in stages (AKM_EPI_DBG = option "epi_dbg": 1 = accumulators read but not evaluated, 2 = not even
+read -- the MMA/TMA floor --, 3 = evaluated but not merged; results are invalid in those modes)."""
 import os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -14,18 +16,11 @@ with native.Handle(d, native.EUCLIDEAN) as h:
     h.set_profiling(True)
     for _ in range(6):
         h.step(0.0)
-    for rot in (1, 0, 1, 0):
-        h.set_option("merge_rotate", rot)
-        h.step(0.0)
-        h.get_profile(reset=True)
-        for _ in range(5):
-            h.step(0.0)
-        pr = h.get_profile(reset=True)
-        print("merge_rotate=%d: search %.3f ms refine %.3f" % (rot, pr["search_ms"] / pr["steps"], pr["refine_ms"] / pr["steps"]))
+    h.get_profile(reset=True)
     h.set_option("epi_dbg", int(os.environ.get("AKM_EPI_DBG", "0")))
-    for _ in range(1 if os.environ.get("AKM_EPI_DBG") == "9" else 5):
+    for _ in range(5):
         h.step(0.0)
     p = h.get_profile()
     st = h.stats()
-    print("raw=%s prune=%s dbg=%s rows=%d search %.3f ms refine %.3f acc %.3f (tiles %d/%d)" % (os.environ.get("RAW", "1"), os.environ.get("PRUNE", "0"), os.environ.get("AKM_EPI_DBG", "0"), n,
+    print("prune=%s dbg=%s rows=%d search %.3f ms refine %.3f acc %.3f (tiles %d/%d)" % (os.environ.get("PRUNE", "0"), os.environ.get("AKM_EPI_DBG", "0"), n,
           p["search_ms"] / p["steps"], p["refine_ms"] / p["steps"], p["accumulate_ms"] / p["steps"], st["tiles_computed"], st["tiles_total"]))
