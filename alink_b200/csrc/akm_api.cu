@@ -1272,7 +1272,6 @@ extern "C" int akm_set_option(akm_handle h, const char *name, double value) {
     if (strcmp(name, "reorder_min_rows") == 0) { h->reorder_min_rows = (int64_t)value; return AKM_OK; }
     if (strcmp(name, "tile_pruning") == 0) { h->tile_pruning = value != 0.0; return AKM_OK; }
     if (strcmp(name, "delta_accumulate") == 0) { h->delta_accumulate = value != 0.0; h->acc_valid = false; h->last_changed = -1; return AKM_OK; }
-    if (strcmp(name, "merge_rotate") == 0) { h->merge_rotate = value != 0.0; return AKM_OK; }
     if (strcmp(name, "epi_dbg") == 0) { h->epi_dbg = (int)value; return AKM_OK; }
     if (strcmp(name, "regroup_after") == 0) { h->regroup_after = std::max(1, (int)value); return AKM_OK; }
     return akm_fail(h, AKM_ERR_BADARG, std::string("unknown option: ") + name);

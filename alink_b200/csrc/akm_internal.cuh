@@ -118,8 +118,7 @@ struct akm_handle_s {
     int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
     int regroup_after = 2;                // regroup once this many tensor-engine passes have produced labels
     bool sum_dev_is_local = false;        // Scratch::sum still holds what akm_assign_accumulate returned
-    bool merge_rotate = true;             // search epilogue: rotate the per-group merge over the four quarter warps
-    int epi_dbg = 0;                      // timing experiments on the search epilogue (results invalid when != 0)
+    int epi_dbg = 0;                      // -DAKM_EPI_DBG builds: timing experiments on the search epilogue (results invalid when != 0)
     bool tile_pruning = true;             // skip (row group, centroid tile) pairs the triangle inequality rules out
 
     // optional per-phase profiling of akm_step

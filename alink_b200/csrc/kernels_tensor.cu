@@ -125,9 +125,9 @@ struct SearchParams {
     int k_prev;             // 0: no seeds this pass
     const float2 *wm;       // per row {window W, seeded upper bound of the minimum score (INF: none)} from rowprep_kernel
     const uint32_t *gmask;  // per 256-row group: bit t set = centroid tile t must be evaluated (nullptr: all tiles)
-    int rotate;             // 1: the merge duty rotates over the four column-quarter warps of a row quarter
-    int dbg;                // timing experiments only (option "epi_dbg"; results invalid): 1 = accumulators read but not
-                            // evaluated, 2 = not even read (the MMA/TMA floor), 3 = evaluated but not merged
+    int dbg;                // builds with -DAKM_EPI_DBG only (option "epi_dbg"; timing experiments, results invalid):
+                            // 1 = accumulators read but not evaluated, 2 = not even read (the MMA/TMA floor),
+                            // 3 = evaluated but not merged
 };
 
 // ------------------------------------------------------------------------------------------ per-row window / seed
@@ -302,8 +302,6 @@ constexpr uint32_t IDESC_F16_256x256 = (1u << 4) | ((256u >> 3) << 17) | ((256u 
 constexpr int PAIR_N = 256;                       // centroids per tile (128 per CTA)
 }  // namespace
 
-// The epilogue looks for the LARGEST u = -score = 2 x16.c16 * 2^-(sx+sc) - ||c||^2 (two packed FMAs per four columns,
-// then a max tree); candidates are the columns with u >= max - W.
 template <int KB>
 __global__ void __launch_bounds__(576, 1)
 search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__ CUtensorMap tmapC,
@@ -316,7 +314,6 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
     constexpr int A_STAGE = STREAM ? 2 * BOX_BYTES : KB * BOX_BYTES;   // 128 rows of this CTA (STREAM: rows + centroids block)
     constexpr int B_TILE = KB * BOX_BYTES;             // this CTA's 128 centroids of a 256-centroid tile
     constexpr int MAX_STAGES = 8;
-    constexpr int MC = MAX_CAND;                       // candidate ring per (row, column quarter)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
@@ -328,14 +325,14 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
 
     unsigned char *a_smem = smem;
     unsigned char *b_smem = smem + (size_t)ns * A_STAGE;
-    float *cn_s = reinterpret_cast<float *>(b_smem + (size_t)nt * B_TILE);  // nt * 256 score offsets (negated)
+    float *cn_s = reinterpret_cast<float *>(b_smem + (size_t)nt * B_TILE);
     uint64_t *bars = reinterpret_cast<uint64_t *>(cn_s + nt * PAIR_N);
     uint64_t *t_full = bars, *t_empty = bars + 2, *b_full = bars + 4, *a_full = bars + 5, *a_empty = a_full + MAX_STAGES;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(a_empty + MAX_STAGES);
     float *pc_s = reinterpret_cast<float *>(tmem_slot + 2);
-    float2 *cand_s = reinterpret_cast<float2 *>(pc_s + 8);                 // [4 quarters][128 rows][MC]
-    float *xch_s = reinterpret_cast<float *>(cand_s + 4 * TILE_M * MC);    // [4 quarters][128 rows][4]
-    int *mstage_s = reinterpret_cast<int *>(xch_s + 4 * TILE_M * 4);       // [128 rows][WL_CAND] merged candidates
+    float2 *cand_s = reinterpret_cast<float2 *>(pc_s + 8);                 // [4 quarters][128 rows][MAX_CAND]
+    float *xch_s = reinterpret_cast<float *>(cand_s + 4 * TILE_M * MAX_CAND);   // [4 quarters][128 rows][4]
+    int *mstage_s = reinterpret_cast<int *>(xch_s + 4 * TILE_M * 4);            // [128 rows][WL_CAND] merged candidates
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < ns; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
@@ -345,7 +342,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         pc_s[0] = p.pc->c16_max; pc_s[1] = p.pc->dc_max; pc_s[2] = p.pc->c_max; pc_s[3] = p.pc->score_scale;
         pc_s[4] = p.pc->bad ? 1.f : 0.f;
     }
-    for (int i = threadIdx.x; i < nt * PAIR_N; i += blockDim.x) cn_s[i] = -p.cn[i];     // u = -score (padding: -1e30)
+    for (int i = threadIdx.x; i < nt * PAIR_N; i += blockDim.x) cn_s[i] = p.cn[i];
     if (warp == 1) tmem_alloc_2sm(smem_u32(tmem_slot), 512);
     tc_fence_before();
     __syncthreads();
@@ -396,7 +393,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
     } else if (warp == 1) {
         // =============================== MMA issuer: one thread of the leader CTA drives both tensor cores
         if (leader) {
-            constexpr uint32_t DESC_HI = 64u | (1u << 14) | (2u << 29);      // 128-byte swizzle, 1024 bytes per 8-row group
+            constexpr uint32_t DESC_HI = 64u | (1u << 14) | (2u << 29);
             const uint32_t a_lo0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) | (1u << 16);
             if constexpr (STREAM) {
                 int s_i = 0, ph = 0, t_it = 0;
@@ -469,17 +466,16 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         const int e = warp - 2;
         const int quarter = e >> 2;
         const int q = warp & 3;
-        const float nscale = -pc_s[3];                              // u = acc * (-scale) - ||c||^2
+        const float scale = pc_s[3];
         uint64_t scale2;
-        asm("mov.b64 %0, {%1, %1};" : "=l"(scale2) : "f"(nscale));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(scale2) : "f"(scale));
         const float *cn_q = cn_s + quarter * 64;
         const int rt = q * 32 + lane;
-        float2 *my_ring = cand_s + ((size_t)quarter * TILE_M + rt) * MC;
+        float2 *my_ring = cand_s + ((size_t)quarter * TILE_M + rt) * MAX_CAND;
         float *my_xch = xch_s + ((size_t)quarter * TILE_M + rt) * 4;
         const int bar_id = 1 + q;
         int t_it = 0;
         int wl_pos = 0, wl_end = 0, wl_used = 0;
-        bool wl_full = false;
         float2 wm_next = make_float2(0.f, INFINITY);
         int a_next = -1;
         uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
@@ -487,40 +483,6 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             const int64_t row0 = (int64_t)pair_id * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
             if (pair_id < ngroups && row0 < p.n) { wm_next = p.wm[row0]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[row0] : -1; }
         }
-        // The merge of a group's four column quarters is done by ONE of the four warps that share the rows, and the
-        // duty rotates from group to group: a warp that merged falls behind by the merge time and catches up over
-        // the next three groups (its accumulators are already waiting), so no warp is a standing bottleneck.
-        int git = 0;
-        // one 32-column chunk (values u in v): running maximum, and the candidate path for the 8-column groups that
-        // can hold a value inside the window
-        auto scan_chunk = [&](const float (&u)[32], int j0, float W, float &m, float &thr, int &ncand, float &dropped) {
-            float g8[4];
-#pragma unroll
-            for (int gq = 0; gq < 4; ++gq) {
-                const float a1 = fmaxf(fmaxf(u[gq * 8 + 0], u[gq * 8 + 1]), u[gq * 8 + 2]);
-                const float a2 = fmaxf(fmaxf(u[gq * 8 + 3], u[gq * 8 + 4]), u[gq * 8 + 5]);
-                g8[gq] = fmaxf(fmaxf(u[gq * 8 + 6], u[gq * 8 + 7]), fmaxf(a1, a2));
-            }
-            const float cmax = fmaxf(fmaxf(g8[0], g8[1]), fmaxf(g8[2], g8[3]));
-            m = fmaxf(m, cmax);
-            thr = m - W;                                            // padding rows: NaN, never admits a candidate
-            if (cmax >= thr) {
-#pragma unroll
-                for (int gq = 0; gq < 4; ++gq) {
-                    if (g8[gq] >= thr) {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            if (u[gq * 8 + i] >= thr) {
-                                const int slot = ncand & (MC - 1);
-                                if (ncand >= MC) dropped = fmaxf(dropped, my_ring[slot].y);
-                                my_ring[slot] = make_float2(__int_as_float(j0 + gq * 8 + i), u[gq * 8 + i]);
-                                ++ncand;
-                            }
-                        }
-                    }
-                }
-            }
-        };
         for (int g = pair_id; g < ngroups; g += npairs) {
             const int64_t row = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
             const bool valid = row < p.n;
@@ -528,17 +490,15 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             const int a_old = a_next;
             const uint32_t gm = gm_next;
             if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
-            const int owner = p.rotate ? (git & 3) : 0;   // the quarter whose warp merges this group
-            ++git;
             {   // prefetch the next group's two floats (and old label) while this group is processed
                 const int64_t rown = (int64_t)(g + npairs) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
-                if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == (p.rotate ? (git & 3) : 0)) ? p.labels[rown] : -1; }
+                if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[rown] : -1; }
             }
             const float W = valid ? wm.x : NAN;          // padding rows: NaN thresholds never admit a candidate
-            float m = -wm.y;                             // seeded lower bound of the maximum of u (-INF: none)
-            float thr = m - W;
+            float m = wm.y;
+            float thr = m + W;
             int ncand = 0;
-            float dropped = -INFINITY;
+            float dropped = INFINITY;
 
             for (int t = 0; t < nt; ++t) {
                 if (!((gm >> t) & 1u)) continue;                    // pruned for this group: no accumulator was produced
@@ -547,9 +507,10 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 ++t_it;
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * PAIR_N + quarter * 64);
-                // columns at or beyond k are padding: a quarter or chunk that holds nothing else is not read at all --
-                // small k (BASELINE configs 2 and 3) leaves most issue slots free
+                // columns at or beyond k are padding (score offset PAD_SCORE): a quarter or chunk that holds nothing
+                // else is not read at all -- small k (BASELINE configs 2 and 3) leaves most issue slots free
                 const int live = p.k - (t * PAIR_N + quarter * 64);      // real centroids in this quarter of the tile
+#ifdef AKM_EPI_DBG
                 if (p.dbg == 1 || p.dbg == 2) {
                     if (p.dbg == 1 && live > 0) {
                         uint32_t v[32];
@@ -567,73 +528,100 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);
                     continue;
                 }
+#endif
                 if (live <= 0) {
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);
                     continue;
                 }
-                const int j0 = t * PAIR_N + quarter * 64;
-                {
 #pragma unroll
-                    for (int c = 0; c < 2; ++c) {
-                        uint32_t v[32];
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v[32];
+                    __syncwarp();
+                    if (c == 1 && live <= 32) {
+                        tc_fence_before();
                         __syncwarp();
-                        if (c == 1 && live <= 32) {
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);
-                            break;
-                        }
-                        tmem_ld32(taddr + c * 32, v);
-                        tmem_ld_wait();
-                        if (c == 1) {
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);   // the leader's MMA thread waits on it
-                        }
-                        const float *cn_t = cn_q + t * PAIR_N + c * 32;
-                        float u[32];
+                        if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);
+                        break;
+                    }
+                    tmem_ld32(taddr + c * 32, v);
+                    tmem_ld_wait();
+                    if (c == 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(smem_u32(t_empty + tb), 0);   // the leader's MMA thread waits on it
+                    }
+                    const float *cn_t = cn_q + t * PAIR_N + c * 32;
+                    float sc[32];
 #pragma unroll
-                        for (int gq = 0; gq < 8; ++gq) {
-                            const float4 o = *reinterpret_cast<const float4 *>(cn_t + gq * 4);
-                            ffma2(u[gq * 4 + 0], u[gq * 4 + 1], v[gq * 4 + 0], v[gq * 4 + 1], scale2, o.x, o.y);
-                            ffma2(u[gq * 4 + 2], u[gq * 4 + 3], v[gq * 4 + 2], v[gq * 4 + 3], scale2, o.z, o.w);
+                    for (int gq = 0; gq < 8; ++gq) {
+                        const float4 o = *reinterpret_cast<const float4 *>(cn_t + gq * 4);
+                        ffma2(sc[gq * 4 + 0], sc[gq * 4 + 1], v[gq * 4 + 0], v[gq * 4 + 1], scale2, o.x, o.y);
+                        ffma2(sc[gq * 4 + 2], sc[gq * 4 + 3], v[gq * 4 + 2], v[gq * 4 + 3], scale2, o.z, o.w);
+                    }
+                    float g8[4];
+#pragma unroll
+                    for (int gq = 0; gq < 4; ++gq) {
+                        const float a1 = fminf(fminf(sc[gq * 8 + 0], sc[gq * 8 + 1]), sc[gq * 8 + 2]);
+                        const float a2 = fminf(fminf(sc[gq * 8 + 3], sc[gq * 8 + 4]), sc[gq * 8 + 5]);
+                        g8[gq] = fminf(fminf(sc[gq * 8 + 6], sc[gq * 8 + 7]), fminf(a1, a2));
+                    }
+                    const float cmin = fminf(fminf(g8[0], g8[1]), fminf(g8[2], g8[3]));
+                    m = fminf(m, cmin);
+                    thr = m + W;                                   // padding rows: W = -INF (set above)
+                    if (cmin <= thr) {
+                        const int j0 = t * PAIR_N + quarter * 64 + c * 32;
+#pragma unroll
+                        for (int gq = 0; gq < 4; ++gq) {
+                            if (g8[gq] <= thr) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    if (sc[gq * 8 + i] <= thr) {
+                                        const int slot = ncand & (MAX_CAND - 1);
+                                        if (ncand >= MAX_CAND) dropped = fminf(dropped, my_ring[slot].y);
+                                        my_ring[slot] = make_float2(__int_as_float(j0 + gq * 8 + i), sc[gq * 8 + i]);
+                                        ++ncand;
+                                    }
+                                }
+                            }
                         }
-                        scan_chunk(u, j0 + c * 32, W, m, thr, ncand, dropped);    // padding columns: u = -1e30
                     }
                 }
             }
+#ifdef AKM_EPI_DBG
             if (p.dbg != 0) continue;
-            // ---- merge the four column quarters of each row (the owner quarter's warp), then the certificate
-            if (quarter != owner) { my_xch[0] = m; my_xch[1] = dropped; my_xch[2] = __int_as_float(ncand); }
+#endif
+            // ---- merge the four column quarters of each row (quarter 0 owns the row), then the certificate
+            if (quarter != 0) { my_xch[0] = m; my_xch[1] = dropped; my_xch[2] = __int_as_float(ncand); }
             asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-            if (quarter == owner) {
+            if (quarter == 0) {
                 bool need_exact = false, changed = false;
-                int *stage = mstage_s + (size_t)rt * WL_CAND;     // merged candidate list of this row
+                // merged candidate list of this row: 8 ints in the exchange area of quarter 0 (unused otherwise) + 4 more
+                int *stage = reinterpret_cast<int *>(mstage_s + (size_t)rt * WL_CAND);
                 if (valid) {
                     float xm[4], xd[4];
                     int xn[4];
+                    xm[0] = m; xd[0] = dropped; xn[0] = ncand;
 #pragma unroll
-                    for (int qq = 0; qq < 4; ++qq) {
+                    for (int qq = 1; qq < 4; ++qq) {
                         const float4 x4 = *reinterpret_cast<const float4 *>(xch_s + ((size_t)qq * TILE_M + rt) * 4);
-                        const bool mine = qq == quarter;     // (its own slot holds an older group's values)
-                        xm[qq] = mine ? m : x4.x; xd[qq] = mine ? dropped : x4.y; xn[qq] = mine ? ncand : __float_as_int(x4.z);
+                        xm[qq] = x4.x; xd[qq] = x4.y; xn[qq] = __float_as_int(x4.z);
                     }
-                    const float mF = fmaxf(fmaxf(xm[0], xm[1]), fmaxf(xm[2], xm[3]));
-                    const float thrF = mF - W;
+                    const float mF = fminf(fminf(xm[0], xm[1]), fminf(xm[2], xm[3]));
+                    const float thrF = mF + W;
                     bool overflow = false;
                     int cnt = 0, best = -1, first = -1;
                     *reinterpret_cast<int4 *>(stage) = make_int4(-1, -1, -1, -1);
                     *reinterpret_cast<int4 *>(stage + 4) = make_int4(-1, -1, -1, -1);
 #pragma unroll
                     for (int qq = 0; qq < 4; ++qq) {
-                        overflow = overflow || !(xd[qq] < thrF);
-                        const float2 *ring = cand_s + ((size_t)qq * TILE_M + rt) * MC;
-                        const int lim = min(xn[qq], MC);
+                        overflow = overflow || !(xd[qq] > thrF);
+                        const float2 *ring = cand_s + ((size_t)qq * TILE_M + rt) * MAX_CAND;
+                        const int lim = min(xn[qq], MAX_CAND);
                         for (int i = 0; i < lim; ++i) {           // rings are nearly always empty or hold one entry
                             const float2 cv = ring[i];
-                            if (cv.y >= thrF) {
+                            if (cv.y <= thrF) {
                                 const int j = __float_as_int(cv.x);
                                 if (cnt < WL_CAND) stage[cnt] = (j < p.k) ? j : -1;
                                 if (cnt == 0) first = j;
@@ -649,44 +637,38 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     if (all) stage[0] = -2;
                     if (p.k_prev > 0 && a_old != best) changed = true;
                     p.labels[row] = best;
-                    // seed of the next pass: an upper bound of this pass's minimum score
-                    if (p.useed) p.useed[row] = (best >= 0 && mF > -3.0e38f) ? (0.5f * W - mF) : INFINITY;
+                    if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
                 }
                 const unsigned chm = __ballot_sync(0xffffffffu, changed);
                 if (chm && lane == 0) atomicAdd(p.counters + 2, __popc(chm));
                 const unsigned mask = __ballot_sync(0xffffffffu, need_exact);
                 if (mask) {
                     const int cnt = __popc(mask);
-                    if (!wl_full && wl_pos + cnt > wl_end) {
+                    if (wl_pos + cnt > wl_end) {
                         for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
                         int base = 0;
                         if (lane == 0) base = atomicAdd(p.counters, WL_BLOCK);
                         wl_pos = __shfl_sync(0xffffffffu, base, 0);
                         wl_end = wl_pos + WL_BLOCK;
-                        // the allocation is sized for the worst case (tensor_assign), so this never triggers; if it
-                        // ever did, the rows go straight to the exact list (one slot per row of the partition)
-                        if (wl_end > p.wl_cap) { wl_full = true; wl_pos = wl_end = 0; }
                     }
+                    const int base = wl_pos;
+                    wl_pos += cnt;
                     wl_used += cnt;
-                    if (wl_full) {
-                        if (need_exact) p.exact_rows[atomicAdd(p.exact_count, 1)] = (int32_t)row;
-                    } else {
-                        const int base = wl_pos;
-                        wl_pos += cnt;
-                        if (need_exact) {
-                            const int pos = base + __popc(mask & ((1u << lane) - 1));
-                            p.wl_rows[pos] = (int32_t)row;
-                            int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
-                            dst[0] = *reinterpret_cast<const int4 *>(stage);
-                            dst[1] = *reinterpret_cast<const int4 *>(stage + 4);
-                        }
+                    if (need_exact) {
+                        const int pos = base + __popc(mask & ((1u << lane) - 1));
+                        p.wl_rows[pos] = (int32_t)row;
+                        int4 *dst = reinterpret_cast<int4 *>(p.wl_cand + (size_t)pos * WL_CAND);
+                        dst[0] = *reinterpret_cast<const int4 *>(stage);
+                        dst[1] = *reinterpret_cast<const int4 *>(stage + 4);
                     }
                 }
             }
             asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
         }
-        for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;      // every warp owns worklist blocks now
-        if (lane == 0 && wl_used) atomicAdd(p.counters + 3, wl_used);
+        if (quarter == 0) {
+            for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
+            if (lane == 0 && wl_used) atomicAdd(p.counters + 3, wl_used);
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -1148,8 +1130,8 @@ static int ensure_tensor_buffers(akm_handle h, TensorCtx *c, RowStore &rs, int k
         cudaFree(c->wl_rows); cudaFree(c->wl_cand); cudaFree(c->exact_rows);
         c->wl_rows = c->wl_cand = c->exact_rows = nullptr;
         // worst case: every row needs exact work; a warp abandons up to 31 slots of each 2048-slot block (a ballot that
-        // does not fit starts a new block) and leaves one partial block at the end (16 reserving warps per CTA)
-        size_t slots = (size_t)rs.n + (size_t)rs.n / 64 + (size_t)h->num_sms * 20 * WL_BLOCK;
+        // does not fit starts a new block) and leaves one partial block at the end (4 reserving warps per CTA)
+        size_t slots = (size_t)rs.n + (size_t)rs.n / 64 + (size_t)h->num_sms * 8 * WL_BLOCK;
         slots = (slots + WL_BLOCK - 1) / WL_BLOCK * WL_BLOCK;
         c->wl_slots = (int64_t)std::min<size_t>(slots, (((size_t)1 << 31) - ((size_t)1 << 23)) / WL_BLOCK * WL_BLOCK);   // int counter, + slack for one last reservation per warp
         slots = (size_t)c->wl_slots;
@@ -1301,7 +1283,6 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     AKM_CUDA(h, cudaGetLastError());
     sp.wm = c->wm;
     sp.dbg = h->epi_dbg;
-    sp.rotate = h->merge_rotate ? 1 : 0;
     sp.gmask = prune ? c->gmask : nullptr;
     h->stats.tiles_total = (int64_t)ngroups2 * ntiles;
     const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;

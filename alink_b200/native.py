@@ -16,7 +16,7 @@ ENGINE_AUTO, ENGINE_EXACT, ENGINE_TENSOR = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libakm.so")
+LIB_PATH = os.environ.get("AKM_LIB") or os.path.join(_HERE, "csrc", "libakm.so")   # AKM_LIB: A/B builds
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "akm.h")
 
 ERR_NAMES = {-1: "BADARG", -2: "CUDA", -3: "NCCL", -4: "OOM", -5: "NOFINITE", -6: "STATE", -7: "UNSUPPORTED"}

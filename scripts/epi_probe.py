@@ -1,12 +1,14 @@
-"""Timing experiments on the search kernel: dense (PRUNE=0) or pruned passes over ROWS x 128 rows, k = 1000, with the
+"""Timing experiments on the search kernel: dense (PRUNE=0) or pruned passes over ROWS x D rows, K centroids (METRIC=euclidean|cosine), with the
 epilogue switched off in stages (AKM_EPI_DBG = option "epi_dbg": 1 = accumulators read but not evaluated, 2 = not even
-read -- the MMA/TMA floor --, 3 = evaluated but not merged; results are invalid in those modes)."""
+read -- the MMA/TMA floor --, 3 = evaluated but not merged; results are invalid in those modes; they exist only in a
+library built with `make -C alink_b200/csrc clean all EXTRA=-DAKM_EPI_DBG`)."""
 import os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from alink_b200 import native
-n, d, k = int(float(os.environ.get("ROWS", 20e6))), 128, 1000
-with native.Handle(d, native.EUCLIDEAN) as h:
+n, d, k = int(float(os.environ.get("ROWS", 20e6))), int(os.environ.get("D", 128)), int(os.environ.get("K", 1000))
+metric = native.COSINE if os.environ.get("METRIC", "euclidean") == "cosine" else native.EUCLIDEAN
+with native.Handle(d, metric) as h:
     h.reserve_rows(n)
     h.blobs_append(20260101, k, 0, n)
     C0 = h.blobs_rows(20260101, k, (np.arange(k, dtype=np.int64) * n) // k).astype(np.float64)
