@@ -730,7 +730,6 @@ int akm_assign_accumulate(akm_handle h, const double *centroids, int k0, int k, 
     pin_finish(h);
     absorb_tensor_stats(h);
     accumulate_absorb(h);
-    h->sum_dev_is_local = true;                      // s->sum holds this partition's sums (akm_allreduce_sum may use them)
     if (objective_out) *objective_out = h->h_dscal[0];
     AKM_TRY(check_error_flag(h));
     return maybe_reorder(h, k);
@@ -745,7 +744,6 @@ int akm_update_centroids(akm_handle h, const double *sum, int k0, int k, int ste
     const size_t L = (size_t)k0 * (size_t)(d + 1);
     AKM_TRY(ensure_scratch(h, k0));
     Scratch *s = scratch_of(h);
-    h->sum_dev_is_local = false;
     AKM_TRY(pin_begin(h, sizeof(double) * (L + 2 * (size_t)k0 * d + (size_t)k0)));
     AKM_TRY(pin_h2d(h, s->sum, sum, sizeof(double) * L));
     const double *dprev = nullptr, *lprev = nullptr;
@@ -784,7 +782,6 @@ int akm_superstep(akm_handle h, const double *centroids, int k0, int k, int step
     const size_t L = (size_t)k0 * (size_t)(d + 1), kd = (size_t)k0 * d;
     AKM_TRY(ensure_scratch(h, k0));
     Scratch *s = scratch_of(h);
-    h->sum_dev_is_local = false;
     AKM_TRY(ensure_labels(h, std::max<int64_t>(h->rows.n, 1)));
     AKM_TRY(pin_begin(h, sizeof(double) * (2 * kd + L + (size_t)k0 + 64)));
     AKM_TRY(pin_h2d(h, s->c[0], centroids, sizeof(double) * kd));

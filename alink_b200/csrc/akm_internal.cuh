@@ -117,7 +117,6 @@ struct akm_handle_s {
     double reorder_ms = 0;
     int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
     int regroup_after = 2;                // regroup once this many tensor-engine passes have produced labels
-    bool sum_dev_is_local = false;        // Scratch::sum still holds what akm_assign_accumulate returned
     int epi_dbg = 0;                      // -DAKM_EPI_DBG builds: timing experiments on the search epilogue (results invalid when != 0)
     bool tile_pruning = true;             // skip (row group, centroid tile) pairs the triangle inequality rules out
 

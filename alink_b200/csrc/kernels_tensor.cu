@@ -302,7 +302,11 @@ constexpr uint32_t IDESC_F16_256x256 = (1u << 4) | ((256u >> 3) << 17) | ((256u 
 constexpr int PAIR_N = 256;                       // centroids per tile (128 per CTA)
 }  // namespace
 
-template <int KB>
+// SPLIT (one centroid tile, k <= 128): only two of the four 64-column quarters hold centroids, so the sixteen epilogue
+// warps work as two teams of eight -- quarters {0,1} take the even row groups of the pair, quarters {2,3} the odd ones,
+// each team with its own accumulator buffer and its own merge -- instead of leaving half the warps idle while the
+// per-group merge and its barriers (the cost that dominates at one tile per group) run on the others.
+template <int KB, bool SPLIT>
 __global__ void __launch_bounds__(576, 1)
 search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__ CUtensorMap tmapC,
                    const SearchParams p) {
@@ -337,7 +341,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
     if (threadIdx.x == 0) {
         for (int i = 0; i < ns; ++i) { mbar_init(smem_u32(a_full + i), 1); mbar_init(smem_u32(a_empty + i), 1); }
         mbar_init(smem_u32(b_full), 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), 32); }
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), SPLIT ? 16 : 32); }
         fence_barrier_init();
         pc_s[0] = p.pc->c16_max; pc_s[1] = p.pc->dc_max; pc_s[2] = p.pc->c_max; pc_s[3] = p.pc->score_scale;
         pc_s[4] = p.pc->bad ? 1.f : 0.f;
@@ -469,30 +473,35 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         const float scale = pc_s[3];
         uint64_t scale2;
         asm("mov.b64 %0, {%1, %1};" : "=l"(scale2) : "f"(scale));
-        const float *cn_q = cn_s + quarter * 64;
+        constexpr int NQ = SPLIT ? 2 : 4;                          // column quarters merged per row
+        const int team = SPLIT ? (quarter >> 1) : 0;
+        const int qbase = SPLIT ? (quarter & 2) : 0;               // the quarter that owns the merge of this thread's row
+        const int colq = SPLIT ? (quarter & 1) : quarter;          // 64-column block of a tile this thread scans
+        const int gfirst = pair_id + team * npairs, gstep = SPLIT ? 2 * npairs : npairs;
+        const float *cn_q = cn_s + colq * 64;
         const int rt = q * 32 + lane;
         float2 *my_ring = cand_s + ((size_t)quarter * TILE_M + rt) * MAX_CAND;
         float *my_xch = xch_s + ((size_t)quarter * TILE_M + rt) * 4;
-        const int bar_id = 1 + q;
+        const int bar_id = 1 + q + 4 * team;
         int t_it = 0;
         int wl_pos = 0, wl_end = 0, wl_used = 0;
         float2 wm_next = make_float2(0.f, INFINITY);
         int a_next = -1;
-        uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
+        uint32_t gm_next = (p.gmask && gfirst < ngroups) ? p.gmask[gfirst] : 0xFFFFFFFFu;
         {
-            const int64_t row0 = (int64_t)pair_id * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
-            if (pair_id < ngroups && row0 < p.n) { wm_next = p.wm[row0]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[row0] : -1; }
+            const int64_t row0 = (int64_t)gfirst * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+            if (gfirst < ngroups && row0 < p.n) { wm_next = p.wm[row0]; a_next = (p.k_prev > 0 && quarter == qbase) ? p.labels[row0] : -1; }
         }
-        for (int g = pair_id; g < ngroups; g += npairs) {
+        for (int g = gfirst; g < ngroups; g += gstep) {
             const int64_t row = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
             const bool valid = row < p.n;
             const float2 wm = wm_next;
             const int a_old = a_next;
             const uint32_t gm = gm_next;
-            if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
+            if (p.gmask && g + gstep < ngroups) gm_next = p.gmask[g + gstep];
             {   // prefetch the next group's two floats (and old label) while this group is processed
-                const int64_t rown = (int64_t)(g + npairs) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
-                if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == 0) ? p.labels[rown] : -1; }
+                const int64_t rown = (int64_t)(g + gstep) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+                if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == qbase) ? p.labels[rown] : -1; }
             }
             const float W = valid ? wm.x : NAN;          // padding rows: NaN thresholds never admit a candidate
             float m = wm.y;
@@ -502,14 +511,15 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
 
             for (int t = 0; t < nt; ++t) {
                 if (!((gm >> t) & 1u)) continue;                    // pruned for this group: no accumulator was produced
-                const int tb = t_it & 1;
-                mbar_wait(smem_u32(t_full + tb), (t_it >> 1) & 1);
+                // (SPLIT: the pair's groups alternate between the two buffers, and so between the two teams)
+                const int tb = SPLIT ? team : (t_it & 1);
+                mbar_wait(smem_u32(t_full + tb), SPLIT ? (t_it & 1) : ((t_it >> 1) & 1));
                 ++t_it;
                 tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * PAIR_N + quarter * 64);
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * PAIR_N + colq * 64);
                 // columns at or beyond k are padding (score offset PAD_SCORE): a quarter or chunk that holds nothing
                 // else is not read at all -- small k (BASELINE configs 2 and 3) leaves most issue slots free
-                const int live = p.k - (t * PAIR_N + quarter * 64);      // real centroids in this quarter of the tile
+                const int live = p.k - (t * PAIR_N + colq * 64);         // real centroids in this quarter of the tile
 #ifdef AKM_EPI_DBG
                 if (p.dbg == 1 || p.dbg == 2) {
                     if (p.dbg == 1 && live > 0) {
@@ -571,7 +581,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     m = fminf(m, cmin);
                     thr = m + W;                                   // padding rows: W = -INF (set above)
                     if (cmin <= thr) {
-                        const int j0 = t * PAIR_N + quarter * 64 + c * 32;
+                        const int j0 = t * PAIR_N + colq * 64 + c * 32;
 #pragma unroll
                         for (int gq = 0; gq < 4; ++gq) {
                             if (g8[gq] <= thr) {
@@ -593,31 +603,32 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             if (p.dbg != 0) continue;
 #endif
             // ---- merge the four column quarters of each row (quarter 0 owns the row), then the certificate
-            if (quarter != 0) { my_xch[0] = m; my_xch[1] = dropped; my_xch[2] = __int_as_float(ncand); }
-            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-            if (quarter == 0) {
+            if (quarter != qbase) { my_xch[0] = m; my_xch[1] = dropped; my_xch[2] = __int_as_float(ncand); }
+            asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(NQ * 32) : "memory");
+            if (quarter == qbase) {
                 bool need_exact = false, changed = false;
                 // merged candidate list of this row: 8 ints in the exchange area of quarter 0 (unused otherwise) + 4 more
-                int *stage = reinterpret_cast<int *>(mstage_s + (size_t)rt * WL_CAND);
+                int *stage = reinterpret_cast<int *>(mstage_s + ((size_t)team * TILE_M + rt) * WL_CAND);   // (SPLIT: one area per team)
                 if (valid) {
-                    float xm[4], xd[4];
-                    int xn[4];
+                    float xm[NQ], xd[NQ];
+                    int xn[NQ];
                     xm[0] = m; xd[0] = dropped; xn[0] = ncand;
 #pragma unroll
-                    for (int qq = 1; qq < 4; ++qq) {
-                        const float4 x4 = *reinterpret_cast<const float4 *>(xch_s + ((size_t)qq * TILE_M + rt) * 4);
+                    for (int qq = 1; qq < NQ; ++qq) {
+                        const float4 x4 = *reinterpret_cast<const float4 *>(xch_s + ((size_t)(qbase + qq) * TILE_M + rt) * 4);
                         xm[qq] = x4.x; xd[qq] = x4.y; xn[qq] = __float_as_int(x4.z);
                     }
-                    const float mF = fminf(fminf(xm[0], xm[1]), fminf(xm[2], xm[3]));
+                    float mF = fminf(xm[0], xm[1]);
+                    if constexpr (NQ == 4) mF = fminf(mF, fminf(xm[2], xm[3]));
                     const float thrF = mF + W;
                     bool overflow = false;
                     int cnt = 0, best = -1, first = -1;
                     *reinterpret_cast<int4 *>(stage) = make_int4(-1, -1, -1, -1);
                     *reinterpret_cast<int4 *>(stage + 4) = make_int4(-1, -1, -1, -1);
 #pragma unroll
-                    for (int qq = 0; qq < 4; ++qq) {
+                    for (int qq = 0; qq < NQ; ++qq) {
                         overflow = overflow || !(xd[qq] > thrF);
-                        const float2 *ring = cand_s + ((size_t)qq * TILE_M + rt) * MAX_CAND;
+                        const float2 *ring = cand_s + ((size_t)(qbase + qq) * TILE_M + rt) * MAX_CAND;
                         const int lim = min(xn[qq], MAX_CAND);
                         for (int i = 0; i < lim; ++i) {           // rings are nearly always empty or hold one entry
                             const float2 cv = ring[i];
@@ -663,9 +674,9 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     }
                 }
             }
-            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+            asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(NQ * 32) : "memory");
         }
-        if (quarter == 0) {
+        if (quarter == qbase) {
             for (int i = wl_pos + lane; i < wl_end; i += 32) p.wl_rows[i] = -1;
             if (lane == 0 && wl_used) atomicAdd(p.counters + 3, wl_used);
         }
@@ -1094,9 +1105,9 @@ void tensor_invalidate_seeds(akm_handle h) {
 
 // chain: 0 = stand-alone pass (no seeds), 1 = akm_step sequence (remap = compaction map of the last update),
 //        2 = sequence of host-buffer passes (identity map, only while k is unchanged)
-template <int KB>
+template <int KB, bool SPLIT>
 static int launch_pair(akm_handle h, const CUtensorMap &mx, const CUtensorMap &mc, const SearchParams &sp, size_t smem, int grid) {
-    auto kern = search_pair_kernel<KB>;
+    auto kern = search_pair_kernel<KB, SPLIT>;
     AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)grid);
@@ -1130,8 +1141,8 @@ static int ensure_tensor_buffers(akm_handle h, TensorCtx *c, RowStore &rs, int k
         cudaFree(c->wl_rows); cudaFree(c->wl_cand); cudaFree(c->exact_rows);
         c->wl_rows = c->wl_cand = c->exact_rows = nullptr;
         // worst case: every row needs exact work; a warp abandons up to 31 slots of each 2048-slot block (a ballot that
-        // does not fit starts a new block) and leaves one partial block at the end (4 reserving warps per CTA)
-        size_t slots = (size_t)rs.n + (size_t)rs.n / 64 + (size_t)h->num_sms * 8 * WL_BLOCK;
+        // does not fit starts a new block) and leaves one partial block at the end (at most 8 reserving warps per CTA)
+        size_t slots = (size_t)rs.n + (size_t)rs.n / 64 + (size_t)h->num_sms * 16 * WL_BLOCK;
         slots = (slots + WL_BLOCK - 1) / WL_BLOCK * WL_BLOCK;
         c->wl_slots = (int64_t)std::min<size_t>(slots, (((size_t)1 << 31) - ((size_t)1 << 23)) / WL_BLOCK * WL_BLOCK);   // int counter, + slack for one last reservation per warp
         slots = (size_t)c->wl_slots;
@@ -1203,8 +1214,11 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     const size_t budget = std::min<size_t>(h->smem_optin, 227 * 1024);
     const int ntiles = (k + PAIR_N - 1) / PAIR_N;
     const int kpad = ntiles * PAIR_N;
+    // one centroid tile of which at most half holds centroids: two teams of epilogue warps (see the kernel)
+    static const int split_env = getenv("AKM_TC_SPLIT") ? atoi(getenv("AKM_TC_SPLIT")) : 1;      // tuning aid
+    const bool split = split_env != 0 && ntiles == 1 && k <= PAIR_N / 2 && KB <= 2;
     const size_t pair_fixed = (size_t)kpad * 4 + 256 + (size_t)4 * TILE_M * MAX_CAND * 8 + (size_t)4 * TILE_M * 16 +
-                              (size_t)TILE_M * WL_CAND * 4 + 1024;   // offsets, barriers, rings, exchange, merge staging, alignment
+                              (size_t)(split ? 2 : 1) * TILE_M * WL_CAND * 4 + 1024;   // offsets, barriers, rings, exchange, merge staging (per team), alignment
     size_t pair_smem = (size_t)2 * KB * BOX_BYTES + (size_t)ntiles * KB * BOX_BYTES + pair_fixed;
     static const bool stream_env = getenv("AKM_TC_STREAM") && atoi(getenv("AKM_TC_STREAM")) != 0;   // tuning aid
     const bool pair_resident = KB <= 2 && pair_smem <= budget && !stream_env;
@@ -1286,9 +1300,10 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     sp.gmask = prune ? c->gmask : nullptr;
     h->stats.tiles_total = (int64_t)ngroups2 * ntiles;
     const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;
-    const int rc = pair_stream ? launch_pair<0>(h, mapX, mapC, sp, pair_smem, pgrid)
-                   : (KB == 1) ? launch_pair<1>(h, mapX, mapC, sp, pair_smem, pgrid)
-                               : launch_pair<2>(h, mapX, mapC, sp, pair_smem, pgrid);
+    int rc;
+    if (pair_stream) rc = launch_pair<0, false>(h, mapX, mapC, sp, pair_smem, pgrid);   // (streamed operands: no gain measured)
+    else if (KB == 1) rc = split ? launch_pair<1, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<1, false>(h, mapX, mapC, sp, pair_smem, pgrid);
+    else rc = split ? launch_pair<2, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2, false>(h, mapX, mapC, sp, pair_smem, pgrid);
     AKM_TRY(rc);
     if (train_rows) {
         AKM_CUDA(h, cudaMemcpyAsync(c->Cprev, C, sizeof(double) * (size_t)k * d, cudaMemcpyDeviceToDevice, h->stream));
