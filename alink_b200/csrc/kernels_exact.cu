@@ -707,9 +707,10 @@ int launch_accumulate(akm_handle h, const RowStore &rs, const int32_t *labels, c
 // the label each row was added under (labels_acc) and moves just the rows whose label changed:
 //     S[old] -= x,  S[new] += x,  count[old] -= 1,  count[new] += 1.
 // Counts stay exact.  The sums pick up one fp64 rounding per moved value, so the policy in
-// accumulate_step() falls back to a full pass when many rows move, every 16 passes, and when the moved
-// rows since the last full pass exceed a quarter of the partition (drift stays many orders below the
-// 1e-6 parity bar; clusters that end up empty are reset to exact zeros).
+// accumulate_step() falls back to a full pass when more than 1/16 of the rows moved in the previous pass,
+// after 64 incremental passes, and once the rows moved since the last full pass exceed 1/16 of the
+// partition (at most n/16 roundings of 2^-53 relative each: many orders below the 1e-6 parity bar;
+// clusters that end up empty are reset to exact zeros).
 // =====================================================================================
 template <typename T, int METRIC>
 __global__ void __launch_bounds__(256)
@@ -858,7 +859,7 @@ int accumulate_step(akm_handle h, const double *C, const double *clabel, int k0,
     }
     const bool known = h->acc_valid && h->acc_n == n && h->acc_k0 == k0;
     const bool delta = known && h->delta_accumulate && h->last_changed >= 0 && h->last_changed * 16 <= n &&
-                       h->acc_delta_passes < 16 && h->acc_changed_total * 4 <= n;
+                       h->acc_delta_passes < 64 && h->acc_changed_total * 16 <= n;
     if (delta) {
         const int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)h->num_sms * 16);
 #define DELTA(T, PTR, M) accumulate_delta_kernel<T, M><<<blocks, 256, 0, h->stream>>>(PTR, rs.xlabel, h->labels, h->labels_acc, n, d, k0, h->sum_local, h->iscal + 8)
