@@ -191,7 +191,7 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
                         const float rhs = ((metric == AKM_EUCLIDEAN) ? 2.f : 4.f) * W * 1.01f + 1e-30f;
                         mask = 1u << (ja / 256);                       // its own tile is always evaluated
                         for (int t = 0; t < ntiles; ++t) {
-                            const float dm = dmin[(size_t)ja * ntiles + t];                       // distances, rounded down
+                            const float dm = sqrtf(dmin[(size_t)ja * ntiles + t]) * 0.999999f;    // table holds squares
                             const float lhs = dm * (dm - 2.f * ub) * 0.999999f;
                             if (!(dm > 2.f * ub && lhs > rhs)) mask |= 1u << t;
                         }
@@ -245,12 +245,6 @@ centroid_tile_dist_kernel(const double *__restrict__ C, int k, int d, int ntiles
             atomicMin(dmin2 + (size_t)a * ntiles + j / 256, __float_as_uint(fmaxf(f, 0.f)));
         }
     }
-}
-
-// squares -> distances, rounded down (once per pass, k * ntiles values, instead of once per row in rowprep_kernel)
-__global__ void dmin_sqrt_kernel(float *__restrict__ dmin, int count) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < count) dmin[i] = sqrtf(dmin[i]) * 0.999999f;
 }
 
 // ------------------------------------------------------------------------------------------ search kernel
@@ -1294,8 +1288,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
         AKM_CUDA(h, cudaMemsetAsync(c->dmin, 0x7F, sizeof(float) * need, h->stream));     // 3.4e38: "no other centroid in this tile"
         centroid_tile_dist_kernel<<<dim3((k + 31) / 32, (k + 31) / 32), 256, 0, h->stream>>>(C, k, d, ntiles,
                                                                                              reinterpret_cast<unsigned *>(c->dmin));
-        dmin_sqrt_kernel<<<(int)((need + 255) / 256), 256, 0, h->stream>>>(c->dmin, (int)need);
-        h->stats.kernel_launches += 2;
+        h->stats.kernel_launches++;
     }
     rowprep_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,
                                                           c->sig_old, k_prev, (chain == 1) ? remap : nullptr, c->wm,
