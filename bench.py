@@ -744,6 +744,10 @@ def run_config(native, torch, stream, pk, name, n, d, k, metric, max_iter):
                                    "hbm_frac": n * (4.0 * d + 4.0) / (ms_dense / 1e3) / 1e9 / pk["hbm"],
                                    "tensor_frac": 2.0 * n * kk * d / (ms_dense / 1e3) / 1e12 / pk["tf_sust"]},
                "roofline": roofline_objects(pk, n, d, k, kk, ms, ph["search"] if engine_tensor else ph["refine"], tf, engine_tensor)}
+        tr = measured_traffic("search_pair_kernel", n, d, k)
+        out["roofline"]["traffic"] = tr["bytes_per_launch"] if tr else None
+        out["roofline"]["traffic_source"] = tr if tr else "no ncu capture of this build and shape under profiles/"
+        out["roofline"]["traffic_kernel"] = "search_pair_kernel" 
         if name == "cfg5":
             m = h.get_model()
             C = m["C"][: m["k"]]
