@@ -126,6 +126,7 @@ static int upload_threads() {
 static int ensure_dev_stage(akm_handle h, size_t bytes) {
     if (h->stage_bytes >= bytes) return AKM_OK;
     if (h->stage) cudaFree(h->stage);
+    if (h->csr_dev) cudaFree(h->csr_dev);
     h->stage = nullptr; h->stage_bytes = 0;
     AKM_CUDA(h, cudaMalloc(&h->stage, bytes));
     h->stage_bytes = bytes;
@@ -659,6 +660,63 @@ int akm_host_alloc(size_t bytes, void **out) {
 
 int akm_host_free(void *p) {
     if (p) cudaFreeHost(p);
+    return AKM_OK;
+}
+
+int akm_upload_rows_csr(akm_handle h, const int64_t *indptr, const int32_t *indices, const double *values, int64_t n) {
+    AKM_TRY(bind_device(h));
+    REQUIRE(h, n >= 0, "negative row count");
+    if (n == 0) return AKM_OK;
+    REQUIRE(h, indptr && indptr[0] == 0, "indptr is null or does not start at 0");
+    REQUIRE(h, indptr[n] == 0 || (indices && values), "indices / values is null");
+    RowStore &rs = h->rows;
+    const size_t d = (size_t)h->d;
+    // every value an fp32 value?  (the non-zeros only: cheap on the host, and it settles the storage before any row lands)
+    bool exact = true;
+    for (int64_t i = 0; i < indptr[n] && exact; ++i) exact = (double)(float)values[i] == values[i];
+    if (!exact && rs.store == 4) AKM_TRY(rowstore_widen(h, rs));
+    AKM_TRY(rowstore_reserve(h, rs, rs.n + n));
+    h->xl_total_valid = false; h->acc_valid = false; h->last_changed = -1;
+    rs.x16_valid = false;
+    int64_t chunk = (int64_t)std::max<size_t>(1, UPLOAD_HALF_BYTES / (d * 8));      // dense doubles of a chunk fill one staging half
+    chunk = std::min<int64_t>(chunk, n);
+    AKM_TRY(ensure_dev_stage(h, 2 * (size_t)chunk * d * 8));
+    const size_t dhalf = h->stage_bytes / 2;
+    for (int64_t off = 0; off < n; off += chunk) {
+        const int64_t m = std::min<int64_t>(chunk, n - off);
+        for (int64_t r = off; r < off + m; ++r)
+            if (indptr[r + 1] < indptr[r]) return akm_fail(h, AKM_ERR_BADARG, "indptr must be non-decreasing");
+        const int64_t nnz0 = indptr[off], nnz = indptr[off + m] - nnz0;
+        const size_t need = sizeof(int64_t) * (size_t)(m + 1) + (size_t)nnz * 12 + 64;
+        if (h->csr_bytes < need) {
+            AKM_CUDA(h, cudaStreamSynchronize(h->stream));
+            if (h->csr_dev) cudaFree(h->csr_dev);
+            h->csr_dev = nullptr; h->csr_bytes = 0;
+            AKM_CUDA(h, cudaMalloc(&h->csr_dev, need + need / 2));
+            h->csr_bytes = need + need / 2;
+        }
+        // (pageable sources: these copies return once the driver has staged them, so the caller's arrays are free
+        // again when the call returns)
+        int64_t *ip = (int64_t *)h->csr_dev;
+        double *vp = (double *)(ip + ((m + 1 + 1) & ~(int64_t)1));
+        int32_t *xp = (int32_t *)(vp + nnz);
+        const int slot = h->stage_slot;
+        h->stage_slot ^= 1;
+        double *dense = (double *)((char *)h->stage + (size_t)slot * dhalf);
+        AKM_CUDA(h, cudaMemcpyAsync(ip, indptr + off, sizeof(int64_t) * (size_t)(m + 1), cudaMemcpyHostToDevice, h->stream));
+        if (nnz > 0) {
+            AKM_CUDA(h, cudaMemcpyAsync(vp, values + nnz0, sizeof(double) * (size_t)nnz, cudaMemcpyHostToDevice, h->stream));
+            AKM_CUDA(h, cudaMemcpyAsync(xp, indices + nnz0, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, h->stream));
+        }
+        AKM_CUDA(h, cudaMemsetAsync(h->iscal + 9, 0, sizeof(int), h->stream));
+        AKM_TRY(launch_csr_expand(h, ip, xp, vp, nnz0, m, dense, h->iscal + 9));
+        AKM_TRY(launch_prep_rows(h, rs, dense, false, rs.n, m, false));
+        AKM_CUDA(h, cudaMemcpyAsync(h->h_iscal + 9, h->iscal + 9, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        AKM_CUDA(h, cudaStreamSynchronize(h->stream));            // the CSR chunk buffer is reused by the next chunk
+        if (h->h_iscal[9] != 0) return akm_fail(h, AKM_ERR_BADARG, "a column index lies outside [0, vectorSize)");
+        rs.n += m;
+    }
+    if (rs.reordered) AKM_TRY(ensure_orig(h, rs));
     return AKM_OK;
 }
 

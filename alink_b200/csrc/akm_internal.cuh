@@ -85,6 +85,7 @@ struct akm_handle_s {
 
     // staging for uploads
     void *stage = nullptr; size_t stage_bytes = 0;       // device staging (two halves, used alternately)
+    void *csr_dev = nullptr; size_t csr_bytes = 0;       // device copy of one CSR chunk (akm_upload_rows_csr)
     void *hstage = nullptr; size_t hstage_bytes = 0;     // pinned host staging (two halves)
     cudaEvent_t stage_free[2] = {nullptr, nullptr};      // half i of both buffers may be refilled
     bool stage_used[2] = {false, false}; int stage_slot = 0;
@@ -159,6 +160,9 @@ int download_pipelined(akm_handle h, const void *dev, void *host, size_t bytes);
 // prepared: the caller already ran prepareVectorData (COSINE rows are stored as given, not normalised again)
 int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f32, int64_t row0, int64_t n,
                      bool prepared = false, int *inexact_flag = nullptr);
+// CSR rows [.., rows) -> dense doubles in dense_dev (indptr_dev holds rows + 1 entries whose first value is nnz0)
+int launch_csr_expand(akm_handle h, const int64_t *indptr_dev, const int32_t *indices_dev, const double *values_dev,
+                      int64_t nnz0, int64_t rows, double *dense_dev, int *bad_index_dev);
 // widen rows [0,n) of x32 into x64 (storage migration)
 int launch_widen_rows(akm_handle h, const float *x32, const double *xlabel, double *x64, int64_t n);
 // updateLabel on k0 centroids in place (EUCL: labels; COS: normalise rows unless cos_normalise == false,

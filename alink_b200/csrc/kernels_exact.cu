@@ -132,6 +132,34 @@ int launch_prep_rows(akm_handle h, RowStore &rs, const void *src, bool src_is_f3
     return AKM_OK;
 }
 
+// CSR -> dense rows in a staging buffer (zero-filled first): one warp per row walks its non-zeros.
+__global__ void csr_expand_kernel(const int64_t *__restrict__ indptr, const int32_t *__restrict__ indices,
+                                  const double *__restrict__ values, int64_t nnz0, int64_t rows, int d,
+                                  double *__restrict__ dense, int *__restrict__ bad_index) {
+    const int lane = threadIdx.x & 31;
+    int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; r < rows; r += stride) {
+        const int64_t a = indptr[r] - nnz0, b = indptr[r + 1] - nnz0;
+        for (int64_t i = a + lane; i < b; i += 32) {
+            const int c = indices[i];
+            if (c >= 0 && c < d) dense[r * d + c] = values[i];
+            else atomicExch(bad_index, 1);
+        }
+    }
+}
+
+int launch_csr_expand(akm_handle h, const int64_t *indptr_dev, const int32_t *indices_dev, const double *values_dev,
+                      int64_t nnz0, int64_t rows, double *dense_dev, int *bad_index_dev) {
+    AKM_CUDA(h, cudaMemsetAsync(dense_dev, 0, sizeof(double) * (size_t)rows * (size_t)h->d, h->stream));
+    if (rows <= 0) return AKM_OK;
+    const int blocks = (int)std::min<int64_t>((rows + 7) / 8, (int64_t)h->num_sms * 16);
+    csr_expand_kernel<<<blocks, 256, 0, h->stream>>>(indptr_dev, indices_dev, values_dev, nnz0, rows, h->d, dense_dev, bad_index_dev);
+    h->stats.kernel_launches++;
+    AKM_CUDA(h, cudaGetLastError());
+    return AKM_OK;
+}
+
 // fp32 -> fp64 storage migration.  EUCLIDEAN: plain widening.  COSINE (xlabel != nullptr): the fp64 store holds
 // the normalised rows, so the scaling a raw fp32 store defers is applied here.
 __global__ void widen_rows_kernel(const float *__restrict__ a, const double *__restrict__ xlabel, int d,

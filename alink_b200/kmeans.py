@@ -15,7 +15,7 @@ from . import model as model_io
 from . import native
 from . import init as init_mod
 from .javafmt import java_vector_to_string
-from .vector import rows_to_matrix
+from .vector import is_sparse_text, rows_to_csr, rows_to_matrix
 
 _DIST = {"EUCLIDEAN": native.EUCLIDEAN, "COSINE": native.COSINE}
 
@@ -165,25 +165,35 @@ class KMeansTrainBatchOp(_TrainParams):
         vec_col = self.get("vectorCol")
         if vec_col is None:
             raise ValueError("vectorCol is required")
-        X, null_mask = rows_to_matrix(in_table.col(vec_col))
-        if null_mask.any():
-            raise ValueError("null vector in training data")
+        col = in_table.col(vec_col)
+        csr, X = None, None
+        if len(col) > 0 and all(is_sparse_text(v) for v in col):
+            # SparseVector column: CSR arrays go to the device as they are (akm_upload_rows_csr)
+            csr = rows_to_csr(col)
+            n_local, d = len(col), csr[3]
+        else:
+            X, null_mask = rows_to_matrix(col)
+            if null_mask.any():
+                raise ValueError("null vector in training data")
+            n_local, d = X.shape
         dist = distributed
-        n_local = X.shape[0]
         n_total = n_local
         if dist is not None:
             n_total = int(dist.all_sum(np.array([float(n_local)]))[0])
         if n_total == 0:
             raise RuntimeError("The train dataset is empty!")            # KMeansTrainBatchOp.java:106
-        d = X.shape[1]
         if dist is not None:
-            d = int(dist.all_max(np.array([float(d)]))[0])               # vector summary -> vectorSize
-            if X.shape[1] != d:
-                X = np.pad(X, ((0, 0), (0, d - X.shape[1])))
+            d_all = int(dist.all_max(np.array([float(d)]))[0])           # vector summary -> vectorSize
+            if X is not None and X.shape[1] != d_all:
+                X = np.pad(X, ((0, 0), (0, d_all - X.shape[1])))
+            d = d_all
         metric = _DIST[self.get("distanceType")]
         with native.Handle(d, metric, device=self.device) as h:
             h.set_engine(self.engine)
-            h.upload_rows(X)
+            if csr is not None:
+                h.upload_rows_csr(csr[0], csr[1], csr[2])
+            else:
+                h.upload_rows(X)
             if dist is not None:
                 dist.attach(h)
             init_info = {}

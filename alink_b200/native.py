@@ -69,6 +69,7 @@ def lib():
         L.akm_upload_rows.argtypes = [_H, _c_dp, ctypes.c_int64]
         L.akm_upload_rows_f32.argtypes = [_H, _c_fp, ctypes.c_int64]
         L.akm_upload_rows_prepared.argtypes = [_H, _c_dp, ctypes.c_int64]
+        L.akm_upload_rows_csr.argtypes = [_H, _c_lp, _c_ip, _c_dp, ctypes.c_int64]
         L.akm_upload_wait.argtypes = [_H]
         L.akm_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
         L.akm_host_free.argtypes = [ctypes.c_void_p]
@@ -212,6 +213,14 @@ class Handle:
         if X.ndim != 2 or X.shape[1] != self.d:
             raise ValueError("rows must be n x %d" % self.d)
         self._ck(lib().akm_upload_rows_prepared(self._h, _dp(X), X.shape[0]))
+
+    def upload_rows_csr(self, indptr, indices, values):
+        """Sparse samples in CSR form (scipy.sparse.csr_matrix fields): expanded to dense rows on the device."""
+        indptr = np.ascontiguousarray(indptr, dtype=np.int64)
+        indices = np.ascontiguousarray(indices, dtype=np.int32)
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        self._ck(lib().akm_upload_rows_csr(self._h, indptr.ctypes.data_as(_c_lp), indices.ctypes.data_as(_c_ip), _dp(values),
+                                           indptr.size - 1))
 
     def upload_wait(self):
         self._ck(lib().akm_upload_wait(self._h))

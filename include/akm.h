@@ -109,6 +109,16 @@ int akm_upload_rows_f32(akm_handle h, const float *x_host, int64_t n);
  * COSINE (akm_eval_clusters) wants the raw vectors: use akm_upload_rows for a partition that is evaluated. */
 int akm_upload_rows_prepared(akm_handle h, const double *x_host, int64_t n);
 
+/* Appends n sparse samples in CSR form (SparseVector training data: CORE/common/linalg/BLAS.java:217-240 and
+ * KMeansUtil.java:79-82 walk the non-zeros; VectorUtil.java:52-114 parses "$size$i:v ..." into them).  The rows are
+ * expanded to dense vectors on the device -- the terms a dense evaluation adds for the zeros are + c_i * 0.0 and
+ * + 0.0, which change no finite sum, so every result equals the sparse evaluation bit for bit -- and then go
+ * through prepareVectorData like any other upload.  Only the non-zeros cross PCIe.
+ *   indptr   int64[n + 1], indptr[0] = 0, non-decreasing
+ *   indices  int32[indptr[n]], 0 <= index < d, unique within a row (SparseVector keeps sorted unique indices)
+ *   values   double[indptr[n]] */
+int akm_upload_rows_csr(akm_handle h, const int64_t *indptr, const int32_t *indices, const double *values, int64_t n);
+
 /* The upload calls above return once the caller's rows sit in the library's pinned staging buffers: the host
  * buffer may be refilled at once (KMeans' Java side fills its next chunk while this one is still crossing
  * PCIe), and every later call on the handle is ordered behind the copies.  akm_upload_wait blocks until all

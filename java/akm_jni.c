@@ -37,6 +37,18 @@ JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_
     return rc;
 }
 
+JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_uploadRowsCsr(
+    JNIEnv *env, jclass cls, jlong h, jlongArray indptr, jintArray indices, jdoubleArray values, jlong n) {
+    jlong *ip = (*env)->GetLongArrayElements(env, indptr, NULL);
+    jint *ix = (*env)->GetIntArrayElements(env, indices, NULL);
+    jdouble *v = (*env)->GetDoubleArrayElements(env, values, NULL);
+    int rc = akm_upload_rows_csr(H(h), (const int64_t *)ip, (const int32_t *)ix, v, n);
+    (*env)->ReleaseLongArrayElements(env, indptr, ip, JNI_ABORT);
+    (*env)->ReleaseIntArrayElements(env, indices, ix, JNI_ABORT);
+    (*env)->ReleaseDoubleArrayElements(env, values, v, JNI_ABORT);
+    return rc;
+}
+
 JNIEXPORT jint JNICALL Java_com_alibaba_alink_operator_common_clustering_kmeans_gpu_AkmNative_uploadWait(
     JNIEnv *env, jclass cls, jlong h) { return akm_upload_wait(H(h)); }
 

@@ -22,6 +22,8 @@ public final class AkmNative {
     public static native int uploadRows(long handle, double[] rowsRowMajor, long n);
     /** rows that already went through FastDistance.prepareVectorData (the ComQueue's "trainData") */
     public static native int uploadRowsPrepared(long handle, double[] rowsRowMajor, long n);
+    /** SparseVector rows as CSR: indptr[n + 1], the concatenated SparseVector.getIndices() / getValues() */
+    public static native int uploadRowsCsr(long handle, long[] indptr, int[] indices, double[] values, long n);
     public static native int uploadWait(long handle);
     /** assign + all-reduce (NCCL) + update + criterion in one native call; out arrays may be null except cOut, kOut */
     public static native int superstep(long handle, double[] centroids, int k0, int k, int stepNo, double tol,

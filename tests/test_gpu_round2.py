@@ -200,6 +200,57 @@ def test_upload_from_page_locked_memory_skips_staging_and_repairs_misfits(metric
         assert (h.get_rows(pick) == Xp[pick]).all()
 
 
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+@pytest.mark.parametrize("fp32", [True, False])
+def test_csr_upload_equals_dense_upload(metric, fp32):
+    # SparseVector samples (BLAS.java:217-240, KMeansUtil.java:79-82): expanded on the device, bit-identical to dense
+    rng = np.random.default_rng(77)
+    n, d, k0 = 70_000, 300, 9                                 # 168 MB dense: three staging chunks
+    dense = np.zeros((n, d))
+    nnz_per_row = rng.integers(0, 12, size=n)                 # some rows are empty
+    indptr = np.zeros(n + 1, dtype=np.int64)
+    indices, values = [], []
+    for r in range(n):
+        cols = np.sort(rng.choice(d, size=nnz_per_row[r], replace=False))
+        vals = rng.normal(size=cols.size)
+        if fp32:
+            vals = vals.astype(np.float32).astype(np.float64)
+        dense[r, cols] = vals
+        indices.append(cols); values.append(vals)
+        indptr[r + 1] = indptr[r] + cols.size
+    indices = np.concatenate(indices).astype(np.int32)
+    values = np.concatenate(values)
+    C = dense[rng.choice(n, k0, replace=False)] + 0.01
+    with native.Handle(d, metric) as ha, native.Handle(d, metric) as hb:
+        ha.upload_rows_csr(indptr, indices, values)
+        hb.upload_rows(dense)
+        assert ha.num_rows() == hb.num_rows() == (n, 4 if fp32 else 8)
+        pick = np.array([0, 1, 27_961, 27_962, 55_923, n - 1], dtype=np.int64)
+        assert (ha.get_rows(pick) == hb.get_rows(pick)).all()
+        Cp, _ = orc.prepare_centroids(metric, C)
+        sa, oa, la = ha.assign_accumulate(Cp, want_labels=True)
+        sb, ob, lb = hb.assign_accumulate(Cp, want_labels=True)
+    assert (la == lb).all()
+    np.testing.assert_allclose(sa, sb, rtol=1e-13, atol=1e-13)
+    with native.Handle(d, metric) as h:
+        with pytest.raises(native.AkmError) as e:
+            h.upload_rows_csr(np.array([0, 1]), np.array([d], dtype=np.int32), np.array([1.0]))
+        assert e.value.code == -1
+
+
+def test_train_op_takes_a_sparse_vector_column_through_csr():
+    from alink_b200.kmeans import KMeansTrainBatchOp, Table
+    rows = ["$6$0:%g 3:%g" % (a, b) for a, b in [(0.0, 0.1), (0.1, 0.0), (0.2, 0.2), (9.0, 9.1), (9.1, 9.0), (9.2, 9.2)]]
+    dense = ["%g 0 0 %g 0 0" % (a, b) for a, b in [(0.0, 0.1), (0.1, 0.0), (0.2, 0.2), (9.0, 9.1), (9.1, 9.0), (9.2, 9.2)]]
+    models = []
+    for col in (rows, dense):
+        t = Table([(v,) for v in col], ["vec"])
+        op = KMeansTrainBatchOp().setVectorCol("vec").setK(2).setInitCentroids(np.array([[0, 0, 0, 0, 0, 0], [9, 0, 0, 9, 0, 0.0]]))
+        op.linkFrom(t)
+        models.append(op.model_rows)
+    assert models[0] == models[1]
+
+
 def test_nan_rows_go_through_the_fp64_path():
     X = blobs(2000, 8, 3, seed=1)
     X[5, 3] = np.nan

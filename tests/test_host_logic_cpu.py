@@ -54,6 +54,22 @@ def test_parse_vector_like_vectorutil():
     assert mask.tolist() == [False, True, False] and X[2].tolist() == [3.0, 4.0]
 
 
+def test_sparse_vector_column_to_csr():
+    from alink_b200.vector import is_sparse_text, parse_vector, rows_to_csr
+    col = ["$5$1:0.1 3:0.4", "0:2,4:-1", "$5$", "2:7 2:8"]      # header optional, comma or space, empty row, repeated index
+    assert all(is_sparse_text(v) for v in col) and not is_sparse_text("1 2 3")
+    indptr, indices, data, d = rows_to_csr(col)
+    assert d == 5 and indptr.tolist() == [0, 2, 4, 4, 5]
+    assert indices.tolist() == [1, 3, 0, 4, 2] and data.tolist() == [0.1, 0.4, 2.0, -1.0, 8.0]
+    dense = np.zeros((4, 5))
+    for r in range(4):
+        dense[r, indices[indptr[r]:indptr[r + 1]]] = data[indptr[r]:indptr[r + 1]]
+    for r, v in enumerate(col):
+        assert (dense[r] == parse_vector(v, 5)).all()           # same values as the dense parse
+    with pytest.raises(ValueError):
+        rows_to_csr(col, vector_size=3)
+
+
 def test_java_double_to_string():
     cases = {1.0: "1.0", 0.001: "0.001", 1e-4: "1.0E-4", 1e7: "1.0E7", 9999999.0: "9999999.0", -0.0: "-0.0",
              float("nan"): "NaN", float("inf"): "Infinity", 123456.789: "123456.789",
