@@ -149,16 +149,18 @@ struct SearchParams {
 __global__ void __launch_bounds__(256)
 rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restrict__ pc,
                const float2 *__restrict__ xerr, int32_t *__restrict__ labels,
-               const float *__restrict__ useed, const float *__restrict__ sig_old, int k_prev,
+               float *__restrict__ useed, const float *__restrict__ sig_old, int k_prev,
                const int *__restrict__ remap, float2 *__restrict__ wm,
-               const float *__restrict__ dmin, int ntiles, int k, uint32_t *__restrict__ gmask) {
+               const float *__restrict__ dmin, int ntiles, int k, uint32_t *__restrict__ gmask, int allow_skip) {
     const float c16_max = pc->c16_max, dc_max = pc->dc_max, c_max = pc->c_max;
     const bool bad = pc->bad != 0;
     const int64_t ngroups = (n + 255) / 256;
     const uint32_t all_tiles = ntiles >= 32 ? 0xFFFFFFFFu : ((1u << ntiles) - 1u);
     for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
         const int64_t row = g * 256 + threadIdx.x;
-        uint32_t mask = 0;
+        uint32_t mask = 0, own = 0;
+        float u_skip = INFINITY;
+        bool row_live = false;
         if (row < n) {
             const float2 xe = xerr[row];
             const float r = xe.x, er = xe.y;
@@ -170,6 +172,7 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
             if (bad) W = NAN;
             float m0 = INFINITY;
             mask = all_tiles;
+            row_live = true;
             if (k_prev > 0) {
                 const int a = labels[row];
                 if (a >= 0 && a < k_prev) {
@@ -189,7 +192,11 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
                     const int ja = remap ? remap[a] : a;                // this pass's numbering (-1: cluster dropped)
                     if (dmin != nullptr && ja >= 0 && ja < k && u == u && ub < 3.0e37f && W == W) {
                         const float rhs = ((metric == AKM_EUCLIDEAN) ? 2.f : 4.f) * W * 1.01f + 1e-30f;
-                        mask = 1u << (ja / 256);                       // its own tile is always evaluated
+                        // (dmin of the row's own tile leaves c_a itself out: when that tile passes too, no other
+                        //  centroid can take the row and, allow_skip given, the whole search of the group is dropped)
+                        own = 1u << (ja / 256);
+                        mask = allow_skip ? 0u : own;
+                        u_skip = u;
                         for (int t = 0; t < ntiles; ++t) {
                             const float dm = sqrtf(dmin[(size_t)ja * ntiles + t]) * 0.999999f;    // table holds squares
                             const float lhs = dm * (dm - 2.f * ub) * 0.999999f;
@@ -205,7 +212,15 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
         }
         if (gmask != nullptr) {
             mask = __reduce_or_sync(0xffffffffu, mask);
-            if ((threadIdx.x & 31) == 0 && mask) atomicOr(gmask + g, mask);
+            own = __reduce_or_sync(0xffffffffu, own);
+            // A group none of whose rows needs any tile is not searched at all: labels stay, and the seed of the next
+            // pass is this pass's bound (the search would have replaced it by the tighter score it found).  A group
+            // that is searched must see the tile of every row's previous centroid: that is where the row's winner is.
+            if (__syncthreads_or((int)mask)) {
+                if ((threadIdx.x & 31) == 0 && (mask | own)) atomicOr(gmask + g, mask | own);
+            } else if (row_live) {
+                useed[row] = u_skip;
+            }
         }
     }
 }
@@ -381,10 +396,15 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     for (int kb = 0; kb < KB; ++kb)
                         tma_load_2d_2sm(smem_u32(b_smem + (size_t)t * B_TILE + kb * BOX_BYTES), &tmapC, bfull_leader, kb * KBLK,
                                         t * PAIR_N + (int)rank * TILE_M);
-                int it = 0;
-                for (int g = pair_id; g < ngroups; g += npairs, ++it) {
+                int it = 0;                                        // row groups that are searched (gmask 0: skipped whole)
+                uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
+                for (int g = pair_id; g < ngroups; g += npairs) {
+                    const uint32_t gm = gm_next;
+                    if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
+                    if (gm == 0u) continue;
                     const int as = it & 1;
                     mbar_wait(smem_u32(a_empty + as), ((it >> 1) & 1) ^ 1);
+                    ++it;
                     if (leader) mbar_expect_tx(smem_u32(a_full + as), 2u * A_STAGE);
                     const uint32_t afull_leader = smem_u32(a_full + as) & PEER_BIT_MASK;
                     const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
@@ -433,11 +453,13 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 mbar_wait(smem_u32(b_full), 0);
                 int it = 0, t_it = 0;
                 uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
-                for (int g = pair_id; g < ngroups; g += npairs, ++it) {
-                    const int as = it & 1;
+                for (int g = pair_id; g < ngroups; g += npairs) {
                     const uint32_t gm = gm_next;
                     if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
+                    if (gm == 0u) continue;                         // no tile needed: the group was not loaded either
+                    const int as = it & 1;
                     mbar_wait(smem_u32(a_full + as), (it >> 1) & 1);
+                    ++it;
                     for (int t = 0; t < nt; ++t) {
                         if (!((gm >> t) & 1u)) continue;            // pruned for this group (rowprep_kernel)
                         const int tb = t_it & 1;
@@ -503,6 +525,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 const int64_t rown = (int64_t)(g + gstep) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
                 if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == qbase) ? p.labels[rown] : -1; }
             }
+            if (gm == 0u) continue;                      // whole group skipped (rowprep_kernel kept labels and seeds)
             const float W = valid ? wm.x : NAN;          // padding rows: NaN thresholds never admit a candidate
             float m = wm.y;
             float thr = m + W;
@@ -1269,9 +1292,11 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     sp.sig_old = c->sig_old;
     sp.k_prev = k_prev;
     // tile pruning needs seeds (an upper bound of every row's distance to its previous centroid) and pays when a
-    // group's rows share that centroid, i.e. on a cluster-ordered partition; with a single tile there is nothing to skip
+    // group's rows share that centroid, i.e. on a cluster-ordered partition; a group that needs no tile at all (every
+    // other centroid provably out of reach of every row) is skipped whole
     const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
-    const bool prune = k_prev > 0 && ntiles > 1 && h->tile_pruning;
+    // (the two-team kernel pairs row groups with accumulator buffers by parity, so it searches every group)
+    const bool prune = k_prev > 0 && h->tile_pruning && (ntiles > 1 || !split);
     if (prune) {
         const size_t need = (size_t)k * ntiles;
         if (c->dmin_cap < need) {
@@ -1292,7 +1317,8 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     }
     rowprep_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,
                                                           c->sig_old, k_prev, (chain == 1) ? remap : nullptr, c->wm,
-                                                          prune ? c->dmin : nullptr, ntiles, k, prune ? c->gmask : nullptr);
+                                                          prune ? c->dmin : nullptr, ntiles, k, prune ? c->gmask : nullptr,
+                                                          split ? 0 : 1);
     h->stats.kernel_launches++;
     AKM_CUDA(h, cudaGetLastError());
     sp.wm = c->wm;

@@ -249,8 +249,50 @@ def test_tile_pruning_changes_nothing_but_the_work(metric):
         assert (labels == ref["labels"]).all() and m["k"] == ref["k"]
         np.testing.assert_allclose(m["C"][: m["k"]], ref["C"][: ref["k"]], rtol=1e-9, atol=1e-12)
     assert out[0][2]["tiles_computed"] == out[0][2]["tiles_total"] > 0
-    assert 0 < out[1][2]["tiles_computed"] < out[1][2]["tiles_total"]      # something was skipped
+    assert 0 <= out[1][2]["tiles_computed"] < out[1][2]["tiles_total"]     # something was skipped
     assert (out[1][1]["C"] == out[0][1]["C"]).all() or metric == native.COSINE
+
+
+@pytest.mark.parametrize("metric,k,nb,centred", [(native.EUCLIDEAN, 700, 700, True), (native.EUCLIDEAN, 700, 700, False),
+                                                 (native.EUCLIDEAN, 200, 120, False), (native.COSINE, 300, 300, True),
+                                                 (native.EUCLIDEAN, 520, 260, False)])
+def test_whole_group_skipping_pass_by_pass(metric, k, nb, centred):
+    # Row groups whose rows provably keep their centroid are not searched at all (no tile of theirs is evaluated).
+    # Every pass of a long run must still give the labels and sums of the exact engine; k < nb leaves clusters that
+    # span several blobs (far rows: no skipping there), k > nb clusters that split a blob (close centroids).
+    n, d, iters = 50000, 24, 14
+    X = blobs(n, d, nb, seed=5, spread=15.0)
+    C0 = X[np.random.default_rng(6).choice(n, k, replace=False)].copy()
+    if centred:                                  # one start per blob (the first draw of blobs() is the centres)
+        C0 = np.random.default_rng(5).uniform(-15.0, 15.0, size=(nb, d)) + 0.3
+    hs = []
+    for engine in (native.ENGINE_TENSOR, native.ENGINE_EXACT):
+        h = native.Handle(d, metric)
+        h.set_engine(engine)
+        h.set_option("reorder_min_rows", 1)
+        h.upload_rows(X)
+        h.set_centroids(C0)
+        hs.append(h)
+    skipped_whole = 0
+    try:
+        for it in range(iters):
+            ra, rb = hs[0].step(0.0), hs[1].step(0.0)
+            la, lb = hs[0].get_labels(), hs[1].get_labels()
+            assert (la == lb).all(), "pass %d: %d labels differ" % (it, int((la != lb).sum()))
+            assert ra[1] == rb[1]                                          # k after the update
+            np.testing.assert_allclose(ra[2], rb[2], rtol=1e-9)            # objective
+            st = hs[0].stats()
+            ntiles = (ra[1] + 255) // 256
+            if st["tiles_total"] and st["tiles_computed"] * ntiles < st["tiles_total"]:
+                skipped_whole += 1                                         # fewer tiles than one per row group
+        ma, mb = hs[0].get_model(), hs[1].get_model()
+        assert (ma["weights"] == mb["weights"]).all()
+        np.testing.assert_allclose(ma["C"][: ma["k"]], mb["C"][: mb["k"]], rtol=1e-10, atol=1e-12)
+    finally:
+        for h in hs:
+            h.close()
+    if centred and metric == native.EUCLIDEAN:
+        assert skipped_whole > 0                                           # well-separated blobs: most groups drop out
 
 
 def test_only_the_first_k_centroids_are_candidates():
