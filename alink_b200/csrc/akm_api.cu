@@ -466,6 +466,7 @@ static int run_assign(akm_handle h, RowStore &rs, const double *C, const double 
                       int32_t *labels, double *mind, int chain = 0, const int *remap = nullptr) {
     h->stats.rows = rs.n;
     h->stats.storage_bytes = rs.store;
+    h->searched_valid = false;                 // only a tensor search that skipped groups says which ones it looked at
     bool use_tensor = false;
     if (h->engine != AKM_ENGINE_EXACT) {
         use_tensor = tensor_supported(h, k0) && rs.n > 0;
@@ -509,6 +510,7 @@ static int maybe_reorder(akm_handle h, int k) {
     if (!go) return AKM_OK;
     if (h->profiling) cudaEventRecord(h->pev[3], h->stream);
     AKM_TRY(reorder_rows_by_label(h, h->rows, h->labels, tensor_useed(h), k));
+    tensor_rows_permuted(h);
     // the incremental sums were formed from these very labels: their record moves with the rows
     if (h->acc_valid && h->labels_acc && h->labels_acc_cap >= h->rows.n)
         AKM_CUDA(h, cudaMemcpyAsync(h->labels_acc, h->labels, sizeof(int32_t) * (size_t)h->rows.n, cudaMemcpyDeviceToDevice, h->stream));

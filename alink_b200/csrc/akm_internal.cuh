@@ -118,6 +118,9 @@ struct akm_handle_s {
     double reorder_ms = 0;
     int64_t reorder_min_rows = 1 << 18;   // partitions smaller than this are left in input order
     int regroup_after = 2;                // regroup once this many tensor-engine passes have produced labels
+    // the 256-row groups the tensor search of the running pass looked at (device list + length; nobody else's labels
+    // can have changed): set by the search, consumed by accumulate_step of the same pass
+    const int2 *searched_list = nullptr; const int *searched_n = nullptr; bool searched_valid = false;
     int epi_dbg = 0;                      // -DAKM_EPI_DBG builds: timing experiments on the search epilogue (results invalid when != 0)
     bool tile_pruning = true;             // skip (row group, centroid tile) pairs the triangle inequality rules out
 
@@ -217,6 +220,7 @@ int ensure_orig(akm_handle h, RowStore &rs);
 int copy_rows_out_i32(akm_handle h, const RowStore &rs, const int32_t *dev, int32_t *host, int64_t n);
 int copy_rows_out_i64(akm_handle h, const RowStore &rs, const int64_t *dev, int64_t *host, int64_t n);
 int copy_rows_out_f64(akm_handle h, const RowStore &rs, const double *dev, double *host, int64_t n);
+void tensor_rows_permuted(akm_handle h);   // kernels_tensor.cu: per-row state that does not move with a regrouping is dropped
 float *tensor_useed(akm_handle h);   // kernels_tensor.cu: per-row seeds of the cached partition (may be null)
 
 // ---------------------------------------------------------------- init.cu

@@ -744,13 +744,15 @@ template <typename T, int METRIC>
 __global__ void __launch_bounds__(256)
 accumulate_delta_kernel(const T *__restrict__ X, const double *__restrict__ xlabel, const int32_t *__restrict__ labels,
                         int32_t *__restrict__ labels_acc, int64_t n, int d, int k0, double *__restrict__ sum,
-                        int *__restrict__ changed_out) {
+                        int *__restrict__ changed_out, const int2 *__restrict__ glist, const int *__restrict__ glist_n) {
+    // glist: the 256-row groups the search of this pass looked at -- no other row can have changed its label
     const int lane = threadIdx.x & 31;
-    const int64_t nblk = (n + 31) / 32;
-    int64_t blk = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nblk = glist ? (int64_t)*glist_n * 8 : (n + 31) / 32;
+    int64_t it = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
     int moved = 0;
-    for (; blk < nblk; blk += stride) {
+    for (; it < nblk; it += stride) {
+        const int64_t blk = glist ? (int64_t)glist[it >> 3].x * 8 + (it & 7) : it;
         const int64_t r = blk * 32 + lane;
         int lb = -1, la = -1;
         if (r < n) { lb = labels[r]; la = labels_acc[r]; }
@@ -890,7 +892,10 @@ int accumulate_step(akm_handle h, const double *C, const double *clabel, int k0,
                        h->acc_delta_passes < 64 && h->acc_changed_total * 16 <= n;
     if (delta) {
         const int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)h->num_sms * 16);
-#define DELTA(T, PTR, M) accumulate_delta_kernel<T, M><<<blocks, 256, 0, h->stream>>>(PTR, rs.xlabel, h->labels, h->labels_acc, n, d, k0, h->sum_local, h->iscal + 8)
+        // the tensor search of this pass says which groups it looked at (consumed here: valid for one pass)
+        const int2 *gl = h->searched_valid ? h->searched_list : nullptr;
+        const int *gln = h->searched_valid ? h->searched_n : nullptr;
+#define DELTA(T, PTR, M) accumulate_delta_kernel<T, M><<<blocks, 256, 0, h->stream>>>(PTR, rs.xlabel, h->labels, h->labels_acc, n, d, k0, h->sum_local, h->iscal + 8, gl, gln)
         if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) DELTA(float, rs.x32, AKM_EUCLIDEAN); else DELTA(double, rs.x64, AKM_EUCLIDEAN); }
         else { if (rs.store == 4) DELTA(float, rs.x32, AKM_COSINE); else DELTA(double, rs.x64, AKM_COSINE); }
 #undef DELTA
@@ -911,6 +916,7 @@ int accumulate_step(akm_handle h, const double *C, const double *clabel, int k0,
         h->acc_count_pending = known;       // without a previous record the count means nothing
         if (!known) h->last_changed = -1;
     }
+    h->searched_valid = false;
     finish_sums_kernel<<<(k0 + 7) / 8, 256, 0, h->stream>>>(h->metric, h->sum_local, C, clabel, k0, d, h->dscal + 2,
                                                           h->iscal + 2, sum_out);
     h->stats.kernel_launches++;

@@ -123,8 +123,12 @@ struct SearchParams {
     float *useed;           // in: previous pass min score + its error bound; out: same for this pass (nullable)
     const float *sig_old;   // per OLD label: distance its centroid moved (INF if the cluster was dropped)
     int k_prev;             // 0: no seeds this pass
-    const float2 *wm;       // per row {window W, seeded upper bound of the minimum score (INF: none)} from rowprep_kernel
-    const uint32_t *gmask;  // per 256-row group: bit t set = centroid tile t must be evaluated (nullptr: all tiles)
+    const float2 *wm;       // per row {recording window (encodes W, see encode_window), seeded upper bound of the
+                            // minimum score (INF: none)} from rowprep_kernel
+    float2 *lb;             // per row {lower bound of the distance to every centroid but the row's own, r2lo}
+                            // (nullable; rowprep_kernel presets .x to the bound for the tiles that are not evaluated)
+    const int2 *glist;      // the row groups (256 rows) to search, ascending: {group, mask of the centroid tiles it needs};
+    const int *glist_n;     // its length (on the device).  nullptr: every group, every tile
     int dbg;                // builds with -DAKM_EPI_DBG only (option "epi_dbg"; timing experiments, results invalid):
                             // 1 = accumulators read but not evaluated, 2 = not even read (the MMA/TMA floor),
                             // 3 = evaluated but not merged
@@ -146,24 +150,95 @@ struct SearchParams {
 // no score of the tile can come within the window of the row's minimum, so the tile holds neither the argmin nor
 // a candidate.  A tile is skipped for a 256-row group when that holds for every row of the group; rows of a
 // cluster-ordered partition share their previous centroid, so whole groups agree.  gmask[g] = OR of the rows' masks.
-__global__ void __launch_bounds__(256)
+//
+// Second-nearest bound (Hamerly's test, per row).  A searched row also learns a lower bound lb of its distance to
+// every centroid other than its winner: the epilogue records scores up to a window W' >= W above the running minimum
+// (only those within W are candidates; the others just bound lb from above), so whatever was not recorded lies more
+// than W' above the minimum.  In the next pass every other centroid is at least lb - (largest movement of another
+// centroid) away, the own one at most ub: when that gap passes the same margin as the tile lemma, the row needs no
+// tile at all.  W' = W * 2^e travels in the slot of W with e in the five low mantissa bits (encode_window), so the
+// search kernel's per-row state does not grow.
+// a window without an exponent must decode to itself: its low bits are cleared (rounding up)
+__device__ __forceinline__ float plain_window(float W) {
+    if (!(W == W)) return W;
+    return __uint_as_float((__float_as_uint(W) + 31u) & ~31u);
+}
+__device__ __forceinline__ float encode_window(float W, float target) {
+    if (!(W == W) || !(W > 1e-20f) || !(target > W) || !(target < 1e30f)) return plain_window(W);
+    int e = 0;
+    frexpf(target / W, &e);                       // target / W = f * 2^e, f in [0.5, 1)
+    e = max(0, min(e - 1, 24));
+    const uint32_t bits = ((__float_as_uint(ldexpf(W, e)) + 31u) & ~31u) | (uint32_t)e;
+    return __uint_as_float(bits);
+}
+__device__ __forceinline__ float decode_window(float Wenc) {     // the window W that certifies (>= the encoded one)
+    const uint32_t e = __float_as_uint(Wenc) & 31u;
+    return Wenc * __uint_as_float((127u - e) << 23);
+}
+
+// largest and second largest movement among the surviving old clusters (dropped ones carry INF and no longer compete)
+__global__ void __launch_bounds__(256) shift_top2_kernel(const float *__restrict__ sig_old, int k_prev, float *__restrict__ top) {
+    __shared__ float s1[256], s2[256];
+    __shared__ int sa[256];
+    float m1 = 0.f, m2 = 0.f;
+    int a1 = -1;
+    for (int i = threadIdx.x; i < k_prev; i += 256) {
+        const float v = sig_old[i];
+        if (!(v < 3.0e38f)) { if (v != v) { m1 = NAN; } continue; }
+        if (v > m1) { m2 = m1; m1 = v; a1 = i; } else if (v > m2) m2 = v;
+    }
+    s1[threadIdx.x] = m1; s2[threadIdx.x] = m2; sa[threadIdx.x] = a1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float b1 = 0.f, b2 = 0.f; int ba = -1; bool nan = false;
+        for (int i = 0; i < 256; ++i) {
+            if (s1[i] != s1[i]) nan = true;
+            if (s1[i] > b1) { b2 = fmaxf(b1, s2[i]); b1 = s1[i]; ba = sa[i]; }
+            else b2 = fmaxf(b2, s1[i]);
+        }
+        top[0] = nan ? NAN : b1; top[1] = nan ? NAN : b2; top[2] = __int_as_float(ba);
+    }
+}
+
+constexpr int ROWPREP_THREADS = 128;     // two rows of the 256-row group per thread: twice the loads in flight
+__global__ void __launch_bounds__(ROWPREP_THREADS)
 rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restrict__ pc,
                const float2 *__restrict__ xerr, int32_t *__restrict__ labels,
                float *__restrict__ useed, const float *__restrict__ sig_old, int k_prev,
                const int *__restrict__ remap, float2 *__restrict__ wm,
-               const float *__restrict__ dmin, int ntiles, int k, uint32_t *__restrict__ gmask, int allow_skip) {
+               const float *__restrict__ dmin, int ntiles, int k, uint32_t *__restrict__ gmask,
+               float2 *__restrict__ lbv, int lb_valid, const float *__restrict__ top) {
     const float c16_max = pc->c16_max, dc_max = pc->dc_max, c_max = pc->c_max;
     const bool bad = pc->bad != 0;
+    // movement of the fastest and second fastest surviving centroid (a row excludes its own)
+    const float top1 = (lbv && k_prev > 0) ? top[0] : 0.f, top2 = (lbv && k_prev > 0) ? top[1] : 0.f;
+    const int top_a = (lbv && k_prev > 0) ? __float_as_int(top[2]) : -1;
     const int64_t ngroups = (n + 255) / 256;
     const uint32_t all_tiles = ntiles >= 32 ? 0xFFFFFFFFu : ((1u << ntiles) - 1u);
     for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
-        const int64_t row = g * 256 + threadIdx.x;
         uint32_t mask = 0, own = 0;
-        float u_skip = INFINITY;
-        bool row_live = false;
-        if (row < n) {
-            const float2 xe = xerr[row];
-            const float r = xe.x, er = xe.y;
+        // everything the two rows need from global memory first, then the arithmetic
+        float2 xe2[2], lb2[2];
+        int a2[2];
+        float u02[2];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int64_t row = g * 256 + hh * ROWPREP_THREADS + threadIdx.x;
+            xe2[hh] = make_float2(0.f, 0.f); lb2[hh] = make_float2(0.f, 0.f); a2[hh] = -1; u02[hh] = INFINITY;
+            if (row < n) {
+                xe2[hh] = xerr[row];
+                if (k_prev > 0) {
+                    a2[hh] = labels[row];
+                    u02[hh] = useed[row];
+                    if (lbv != nullptr && lb_valid) lb2[hh] = lbv[row];
+                }
+            }
+        }
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int64_t row = g * 256 + hh * ROWPREP_THREADS + threadIdx.x;
+            if (row >= n) continue;
+            const float r = xe2[hh].x, er = xe2[hh].y;
             const float rc = r + c_max;
             // |S - true| <= 2(|dx||c16| + |x||dc|) + 2 eta |x16||c16| + fp32 epilogue rounding
             const float B = 2.f * (er * c16_max + r * dc_max) + 2.f * eta * (r + er) * c16_max + 4.8e-7f * rc * rc;
@@ -171,57 +246,105 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
             float W = 2.004f * B + 2.f * epsJ + 1e-30f;
             if (bad) W = NAN;
             float m0 = INFINITY;
-            mask = all_tiles;
-            row_live = true;
-            if (k_prev > 0) {
-                const int a = labels[row];
-                if (a >= 0 && a < k_prev) {
-                    const float sg_a = sig_old[a], u0 = useed[row];
-                    float u, ub;                                    // ub: distance (COSINE: chord) to c_a, rounded up
-                    if (metric == AKM_EUCLIDEAN) {
-                        const float r2 = r * r;
-                        const float t = sqrtf(fmaxf(u0 + r2 * 1.000001f, 0.f)) * 1.000001f + sg_a;
-                        u = t * t * 1.000001f - r2 * 0.999998f + 0.5f * W + 1e-5f * (t * t + r2);
-                        ub = t;
+            float Wenc = plain_window(W);
+            W = decode_window(Wenc);                        // the value the search certifies with
+            // distance^2 (COSINE: chord^2) >= alpha * score + r2lo for a score that is short of the truth by at most W / 2
+            const float r2lo = (metric == AKM_EUCLIDEAN) ? (r * r * 0.999998f - 0.5f * W) : (2.f - W);
+            float lb_out = INFINITY;
+            uint32_t need = all_tiles;
+            const int a = a2[hh];
+            if (k_prev > 0 && a >= 0 && a < k_prev) {
+                const float sg_a = sig_old[a], u0 = u02[hh];
+                float u, ut, ub;                                // ub: distance (COSINE: chord) to c_a, rounded up
+                if (metric == AKM_EUCLIDEAN) {
+                    const float r2 = r * r;
+                    const float t = sqrtf(fmaxf(u0 + r2 * 1.000001f, 0.f)) * 1.000001f + sg_a;
+                    ut = t * t * 1.000001f - r2 * 0.999998f + 2e-6f * (t * t + r2);   // bounds the true score
+                    u = ut + 0.5f * W + 8e-6f * (t * t + r2);                          // ... and the approximate one
+                    ub = t;
+                } else {
+                    ut = u0 + sg_a * (r + er) * 1.000001f + 2e-7f;
+                    u = ut + 0.5f * W + 8e-7f;
+                    ub = sqrtf(fmaxf(2.f + 2.f * u, 0.f)) * 1.000001f + 1e-6f;
+                    if (!(fabsf(r - 1.f) < 1e-5f)) ub = INFINITY;   // not a unit vector (zero row): no pruning
+                }
+                if (u == u) m0 = u;                                 // NaN: no seed
+                if (!(ut == ut)) ut = INFINITY;
+                const int ja = remap ? remap[a] : a;                // this pass's numbering (-1: cluster dropped)
+                if (dmin != nullptr && ja >= 0 && ja < k && u == u && ub < 3.0e37f && W == W) {
+                    const float rhs = ((metric == AKM_EUCLIDEAN) ? 2.f : 4.f) * W * 1.01f + 1e-30f;
+                    // (dmin of the row's own tile leaves c_a itself out: when that tile passes too, no other centroid
+                    //  can take the row)
+                    own |= 1u << (ja / 256);
+                    need = 0u;
+                    // second-nearest bound carried over from the last search of this row.  Nothing is evaluated for
+                    // a row that passes, so the margin only has to cover Java's own rounding of the two distances
+                    // (the tile lemma's margin also keeps would-be candidates of the fp16 window out of pruned tiles).
+                    float lbp = 0.f;
+                    if (lbv != nullptr && lb_valid) lbp = lb2[hh].x - ((a == top_a) ? top2 : top1);
+                    if (!(lbp < 3.0e37f)) lbp = 0.f;            // NaN, or a bound nobody computed
+                    const float rhs_row = 16.f * epsJ + 1e-30f;
+                    if (lbp > ub && (lbp - ub) * (lbp + ub) * 0.999999f > rhs_row) {
+                        lb_out = lbp * 0.999999f;                      // every other centroid is out of reach
                     } else {
-                        u = u0 + sg_a * (r + er) * 1.000001f + 0.5f * W + 1e-6f;
-                        ub = sqrtf(fmaxf(2.f + 2.f * u, 0.f)) * 1.000001f + 1e-6f;
-                        if (!(fabsf(r - 1.f) < 1e-5f)) ub = INFINITY;   // not a unit vector (zero row): no pruning
-                    }
-                    if (u == u) m0 = u;                                 // NaN: no seed
-                    const int ja = remap ? remap[a] : a;                // this pass's numbering (-1: cluster dropped)
-                    if (dmin != nullptr && ja >= 0 && ja < k && u == u && ub < 3.0e37f && W == W) {
-                        const float rhs = ((metric == AKM_EUCLIDEAN) ? 2.f : 4.f) * W * 1.01f + 1e-30f;
-                        // (dmin of the row's own tile leaves c_a itself out: when that tile passes too, no other
-                        //  centroid can take the row and, allow_skip given, the whole search of the group is dropped)
-                        own = 1u << (ja / 256);
-                        mask = allow_skip ? 0u : own;
-                        u_skip = u;
+                        float geo = INFINITY;                          // bound for the tiles this row lets go
                         for (int t = 0; t < ntiles; ++t) {
                             const float dm = sqrtf(dmin[(size_t)ja * ntiles + t]) * 0.999999f;    // table holds squares
                             const float lhs = dm * (dm - 2.f * ub) * 0.999999f;
-                            if (!(dm > 2.f * ub && lhs > rhs)) mask |= 1u << t;
+                            if (!(dm > 2.f * ub && lhs > rhs)) need |= 1u << t;
+                            else geo = fminf(geo, (dm - ub) * 0.999999f);
                         }
+                        lb_out = fmaxf(geo, lbp * 0.999999f);
                     }
-                    // express the old label in this pass's cluster numbering (empty clusters were compacted away),
-                    // so the search kernel can tell which rows really changed cluster
-                    if (remap) labels[row] = remap[a];
+                    if (need == 0u) {
+                        // The row keeps its centroid whatever the search finds.  If its group is searched for the
+                        // sake of other rows it only rides along: a seed of -INF lets no score of its through, the
+                        // epilogue leaves its label, seed and bound alone, and it never reaches the refinement.
+                        m0 = -INFINITY;
+                        useed[row] = ut;
+                    } else if (lbv != nullptr) {
+                        // record scores up to 1.5 x the distance of the own centroid: the next pass can then tell
+                        // that far apart the second nearest is (alpha * window = (1.5^2 - 1) * ub^2)
+                        Wenc = encode_window(W, W + ((metric == AKM_EUCLIDEAN) ? 1.25f : 0.625f) * ub * ub);
+                    }
                 }
+                // express the old label in this pass's cluster numbering (empty clusters were compacted away),
+                // so the search kernel can tell which rows really changed cluster
+                if (remap) labels[row] = remap[a];
             }
-            wm[row] = make_float2(W, m0);
+            mask |= need;
+            wm[row] = make_float2(Wenc, m0);
+            // searched rows: the epilogue lowers .x to what it saw; rows that pass keep it for the next pass
+            if (lbv != nullptr) lbv[row] = make_float2(lb_out, r2lo);
         }
         if (gmask != nullptr) {
             mask = __reduce_or_sync(0xffffffffu, mask);
             own = __reduce_or_sync(0xffffffffu, own);
-            // A group none of whose rows needs any tile is not searched at all: labels stay, and the seed of the next
-            // pass is this pass's bound (the search would have replaced it by the tighter score it found).  A group
-            // that is searched must see the tile of every row's previous centroid: that is where the row's winner is.
-            if (__syncthreads_or((int)mask)) {
-                if ((threadIdx.x & 31) == 0 && (mask | own)) atomicOr(gmask + g, mask | own);
-            } else if (row_live) {
-                useed[row] = u_skip;
-            }
+            // A group none of whose rows needs any tile is not searched at all (its rows have seen to their seeds and
+            // bounds above).  A group that is searched must see the tile of every row's previous centroid: that is
+            // where the row's winner is.
+            if (__syncthreads_or((int)mask) && (threadIdx.x & 31) == 0 && (mask | own)) atomicOr(gmask + g, mask | own);
         }
+    }
+}
+
+// The groups that need a search with their tile masks: the search kernel's three roles walk this list, so groups
+// that are skipped cost them nothing and every per-group prefetch is one searched group ahead.  A warp looks at 32
+// consecutive groups and reserves their slots with one atomic (neighbouring groups stay together; the order of the
+// warps' runs is the order they arrive in, which no result depends on).
+__global__ void __launch_bounds__(256) group_list_kernel(const uint32_t *__restrict__ gmask, int ngroups, int2 *__restrict__ glist,
+                                                         int *__restrict__ count) {
+    const int lane = threadIdx.x & 31;
+    const int nw = (ngroups + 31) / 32;
+    for (int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < nw; w += (gridDim.x * blockDim.x) >> 5) {
+        const int g = w * 32 + lane;
+        const uint32_t m = g < ngroups ? gmask[g] : 0u;
+        const unsigned b = __ballot_sync(0xffffffffu, m != 0u);
+        if (b == 0u) continue;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(count, __popc(b));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (m) glist[base + __popc(b & ((1u << lane) - 1u))] = make_int2(g, (int)m);
     }
 }
 
@@ -321,7 +444,8 @@ constexpr int PAIR_N = 256;                       // centroids per tile (128 per
 // warps work as two teams of eight -- quarters {0,1} take the even row groups of the pair, quarters {2,3} the odd ones,
 // each team with its own accumulator buffer and its own merge -- instead of leaving half the warps idle while the
 // per-group merge and its barriers (the cost that dominates at one tile per group) run on the others.
-template <int KB, bool SPLIT>
+// LB: the epilogue also records how far the runner-up of every row is (second-nearest bound, see rowprep_kernel).
+template <int KB, bool SPLIT, bool LB>
 __global__ void __launch_bounds__(576, 1)
 search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_constant__ CUtensorMap tmapC,
                    const SearchParams p) {
@@ -368,16 +492,21 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const int ngroups = (int)((p.n + 2 * TILE_M - 1) / (2 * TILE_M));     // 256 rows per pair and group
+    // the launch walks `ng` entries: the groups rowprep_kernel / group_list_kernel found in need of a search, or all
+    const int ng = p.glist ? *p.glist_n : (int)((p.n + 2 * TILE_M - 1) / (2 * TILE_M));     // 256 rows per pair and group
+    auto entry = [&](int i) -> int2 { return p.glist ? p.glist[i] : make_int2(i, -1); };
 
     if (warp == 0) {
         // =============================== TMA producer (both CTAs; completion lands on the leader's barriers)
         if (lane == 0) {
             if constexpr (STREAM) {
                 int s_i = 0, ph = 0;
-                for (int g = pair_id; g < ngroups; g += npairs) {
-                    const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
-                    const uint32_t gm = p.gmask ? p.gmask[g] : 0xFFFFFFFFu;
+                int2 e_next = pair_id < ng ? entry(pair_id) : make_int2(0, 0);
+                for (int i = pair_id; i < ng; i += npairs) {
+                    const int2 en = e_next;
+                    if (i + npairs < ng) e_next = entry(i + npairs);
+                    const int64_t row0 = (int64_t)en.x * (2 * TILE_M) + (int64_t)rank * TILE_M;
+                    const uint32_t gm = (uint32_t)en.y;
                     for (int t = 0; t < nt; ++t)
                         for (int kb = 0; kb < nkb && ((gm >> t) & 1u); ++kb) {
                             mbar_wait(smem_u32(a_empty + s_i), ph ^ 1);
@@ -396,18 +525,16 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     for (int kb = 0; kb < KB; ++kb)
                         tma_load_2d_2sm(smem_u32(b_smem + (size_t)t * B_TILE + kb * BOX_BYTES), &tmapC, bfull_leader, kb * KBLK,
                                         t * PAIR_N + (int)rank * TILE_M);
-                int it = 0;                                        // row groups that are searched (gmask 0: skipped whole)
-                uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
-                for (int g = pair_id; g < ngroups; g += npairs) {
-                    const uint32_t gm = gm_next;
-                    if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
-                    if (gm == 0u) continue;
+                int it = 0;
+                int2 e_next = pair_id < ng ? entry(pair_id) : make_int2(0, 0);
+                for (int i = pair_id; i < ng; i += npairs, ++it) {
+                    const int2 en = e_next;
+                    if (i + npairs < ng) e_next = entry(i + npairs);
                     const int as = it & 1;
                     mbar_wait(smem_u32(a_empty + as), ((it >> 1) & 1) ^ 1);
-                    ++it;
                     if (leader) mbar_expect_tx(smem_u32(a_full + as), 2u * A_STAGE);
                     const uint32_t afull_leader = smem_u32(a_full + as) & PEER_BIT_MASK;
-                    const int64_t row0 = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M;
+                    const int64_t row0 = (int64_t)en.x * (2 * TILE_M) + (int64_t)rank * TILE_M;
                     for (int kb = 0; kb < KB; ++kb)
                         tma_load_2d_2sm(smem_u32(a_smem + (size_t)as * A_STAGE + kb * BOX_BYTES), &tmapX, afull_leader, kb * KBLK,
                                         (int)row0);
@@ -421,8 +548,10 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             const uint32_t a_lo0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) | (1u << 16);
             if constexpr (STREAM) {
                 int s_i = 0, ph = 0, t_it = 0;
-                for (int g = pair_id; g < ngroups; g += npairs) {
-                    const uint32_t gm = p.gmask ? p.gmask[g] : 0xFFFFFFFFu;
+                int2 e_next = pair_id < ng ? entry(pair_id) : make_int2(0, 0);
+                for (int i = pair_id; i < ng; i += npairs) {
+                    const uint32_t gm = (uint32_t)e_next.y;
+                    if (i + npairs < ng) e_next = entry(i + npairs);
                     for (int t = 0; t < nt; ++t) {
                         if (!((gm >> t) & 1u)) continue;            // pruned for this group (rowprep_kernel)
                         const int tb = t_it & 1;
@@ -452,16 +581,15 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                 const uint32_t b_lo0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) | (1u << 16);
                 mbar_wait(smem_u32(b_full), 0);
                 int it = 0, t_it = 0;
-                uint32_t gm_next = (p.gmask && pair_id < ngroups) ? p.gmask[pair_id] : 0xFFFFFFFFu;
-                for (int g = pair_id; g < ngroups; g += npairs) {
-                    const uint32_t gm = gm_next;
-                    if (p.gmask && g + npairs < ngroups) gm_next = p.gmask[g + npairs];
-                    if (gm == 0u) continue;                         // no tile needed: the group was not loaded either
+                int2 e_next = pair_id < ng ? entry(pair_id) : make_int2(0, 0);
+                for (int i = pair_id; i < ng; i += npairs, ++it) {
+                    const uint32_t gm = (uint32_t)e_next.y;
+                    if (i + npairs < ng) e_next = entry(i + npairs);
                     const int as = it & 1;
                     mbar_wait(smem_u32(a_full + as), (it >> 1) & 1);
-                    ++it;
                     for (int t = 0; t < nt; ++t) {
                         if (!((gm >> t) & 1u)) continue;            // pruned for this group (rowprep_kernel)
+                        // (SPLIT: one tile per entry, so entries -- and with them the teams -- alternate between the buffers)
                         const int tb = t_it & 1;
                         mbar_wait(smem_u32(t_empty + tb), ((t_it >> 1) & 1) ^ 1);
                         ++t_it;
@@ -499,7 +627,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         const int team = SPLIT ? (quarter >> 1) : 0;
         const int qbase = SPLIT ? (quarter & 2) : 0;               // the quarter that owns the merge of this thread's row
         const int colq = SPLIT ? (quarter & 1) : quarter;          // 64-column block of a tile this thread scans
-        const int gfirst = pair_id + team * npairs, gstep = SPLIT ? 2 * npairs : npairs;
+        const int ifirst = pair_id + team * npairs, istep = SPLIT ? 2 * npairs : npairs;   // entries of this thread's team
         const float *cn_q = cn_s + colq * 64;
         const int rt = q * 32 + lane;
         float2 *my_ring = cand_s + ((size_t)quarter * TILE_M + rt) * MAX_CAND;
@@ -509,28 +637,31 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
         int wl_pos = 0, wl_end = 0, wl_used = 0;
         float2 wm_next = make_float2(0.f, INFINITY);
         int a_next = -1;
-        uint32_t gm_next = (p.gmask && gfirst < ngroups) ? p.gmask[gfirst] : 0xFFFFFFFFu;
+        int2 e_next = ifirst < ng ? entry(ifirst) : make_int2(0, 0);
         {
-            const int64_t row0 = (int64_t)gfirst * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
-            if (gfirst < ngroups && row0 < p.n) { wm_next = p.wm[row0]; a_next = (p.k_prev > 0 && quarter == qbase) ? p.labels[row0] : -1; }
+            const int64_t row0 = (int64_t)e_next.x * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+            if (ifirst < ng && row0 < p.n) { wm_next = p.wm[row0]; a_next = (p.k_prev > 0 && quarter == qbase) ? p.labels[row0] : -1; }
         }
-        for (int g = gfirst; g < ngroups; g += gstep) {
-            const int64_t row = (int64_t)g * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+        for (int i = ifirst; i < ng; i += istep) {
+            const int64_t row = (int64_t)e_next.x * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
             const bool valid = row < p.n;
             const float2 wm = wm_next;
             const int a_old = a_next;
-            const uint32_t gm = gm_next;
-            if (p.gmask && g + gstep < ngroups) gm_next = p.gmask[g + gstep];
-            {   // prefetch the next group's two floats (and old label) while this group is processed
-                const int64_t rown = (int64_t)(g + gstep) * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
+            const uint32_t gm = (uint32_t)e_next.y;
+            if (i + istep < ng) {   // prefetch the next entry's two floats per row (and old label) while this one is processed
+                e_next = entry(i + istep);
+                const int64_t rown = (int64_t)e_next.x * (2 * TILE_M) + (int64_t)rank * TILE_M + rt;
                 if (rown < p.n) { wm_next = p.wm[rown]; a_next = (p.k_prev > 0 && quarter == qbase) ? p.labels[rown] : -1; }
+                if constexpr (LB) { if (quarter == qbase && rown < p.n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.lb + rown)); }
             }
-            if (gm == 0u) continue;                      // whole group skipped (rowprep_kernel kept labels and seeds)
-            const float W = valid ? wm.x : NAN;          // padding rows: NaN thresholds never admit a candidate
+            // W: recording window (scores up to W above the running minimum reach the slow path); the certifying
+            // window Wc <= W is decoded from it there.  Padding rows: NaN thresholds never admit anything.
+            const float W = valid ? wm.x : NAN;
             float m = wm.y;
             float thr = m + W;
             int ncand = 0;
             float dropped = INFINITY;
+            if constexpr (LB) my_xch[1] = INFINITY;      // smallest recorded score that was no candidate
 
             for (int t = 0; t < nt; ++t) {
                 if (!((gm >> t) & 1u)) continue;                    // pruned for this group: no accumulator was produced
@@ -605,20 +736,27 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     thr = m + W;                                   // padding rows: W = -INF (set above)
                     if (cmin <= thr) {
                         const int j0 = t * PAIR_N + colq * 64 + c * 32;
+                        const float thr_c = LB ? m + decode_window(W) : thr;   // candidates; the rest only bounds the runner-up
+                        float far = INFINITY;
+                        if constexpr (LB) far = my_xch[1];
 #pragma unroll
                         for (int gq = 0; gq < 4; ++gq) {
                             if (g8[gq] <= thr) {
 #pragma unroll
                                 for (int i = 0; i < 8; ++i) {
-                                    if (sc[gq * 8 + i] <= thr) {
+                                    const float v = sc[gq * 8 + i];
+                                    if (v <= thr_c) {
                                         const int slot = ncand & (MAX_CAND - 1);
                                         if (ncand >= MAX_CAND) dropped = fminf(dropped, my_ring[slot].y);
-                                        my_ring[slot] = make_float2(__int_as_float(j0 + gq * 8 + i), sc[gq * 8 + i]);
+                                        my_ring[slot] = make_float2(__int_as_float(j0 + gq * 8 + i), v);
                                         ++ncand;
+                                    } else if (LB && v <= thr) {
+                                        far = fminf(far, v);
                                     }
                                 }
                             }
                         }
+                        if constexpr (LB) my_xch[1] = far;
                     }
                 }
             }
@@ -626,24 +764,35 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
             if (p.dbg != 0) continue;
 #endif
             // ---- merge the four column quarters of each row (quarter 0 owns the row), then the certificate
-            if (quarter != qbase) { my_xch[0] = m; my_xch[1] = dropped; my_xch[2] = __int_as_float(ncand); }
+            float far_own = INFINITY;
+            if constexpr (LB) far_own = my_xch[1];
+            if (quarter != qbase) {
+                my_xch[0] = m; my_xch[1] = dropped; my_xch[2] = __int_as_float(ncand);
+                if constexpr (LB) my_xch[3] = far_own;
+            }
             asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(NQ * 32) : "memory");
             if (quarter == qbase) {
                 bool need_exact = false, changed = false;
                 // merged candidate list of this row: 8 ints in the exchange area of quarter 0 (unused otherwise) + 4 more
                 int *stage = reinterpret_cast<int *>(mstage_s + ((size_t)team * TILE_M + rt) * WL_CAND);   // (SPLIT: one area per team)
-                if (valid) {
+                if (valid && wm.y != -INFINITY) {           // (-INF: the row keeps its centroid, rowprep_kernel has seen to it)
+                    float2 lbr = make_float2(0.f, 0.f);
+                    if constexpr (LB) lbr = p.lb[row];
                     float xm[NQ], xd[NQ];
                     int xn[NQ];
                     xm[0] = m; xd[0] = dropped; xn[0] = ncand;
+                    float far = far_own;
 #pragma unroll
                     for (int qq = 1; qq < NQ; ++qq) {
                         const float4 x4 = *reinterpret_cast<const float4 *>(xch_s + ((size_t)(qbase + qq) * TILE_M + rt) * 4);
                         xm[qq] = x4.x; xd[qq] = x4.y; xn[qq] = __float_as_int(x4.z);
+                        if constexpr (LB) far = fminf(far, x4.w);
                     }
                     float mF = fminf(xm[0], xm[1]);
                     if constexpr (NQ == 4) mF = fminf(mF, fminf(xm[2], xm[3]));
-                    const float thrF = mF + W;
+                    const float Wc = LB ? decode_window(W) : W;
+                    const float thrF = mF + Wc;
+                    if constexpr (LB) far = fminf(far, mF + W);   // nothing that was not recorded lies below this
                     bool overflow = false;
                     int cnt = 0, best = -1, first = -1;
                     *reinterpret_cast<int4 *>(stage) = make_int4(-1, -1, -1, -1);
@@ -651,6 +800,7 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
 #pragma unroll
                     for (int qq = 0; qq < NQ; ++qq) {
                         overflow = overflow || !(xd[qq] > thrF);
+                        if constexpr (LB) far = fminf(far, xd[qq]);   // (an evicted candidate makes the row exact anyway)
                         const float2 *ring = cand_s + ((size_t)(qbase + qq) * TILE_M + rt) * MAX_CAND;
                         const int lim = min(xn[qq], MAX_CAND);
                         for (int i = 0; i < lim; ++i) {           // rings are nearly always empty or hold one entry
@@ -661,6 +811,8 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                                 if (cnt == 0) first = j;
                                 if (cv.y == mF) best = j;
                                 ++cnt;
+                            } else if (LB) {
+                                far = fminf(far, cv.y);           // was a candidate of an earlier, larger minimum
                             }
                         }
                     }
@@ -671,7 +823,15 @@ search_pair_kernel(const __grid_constant__ CUtensorMap tmapX, const __grid_const
                     if (all) stage[0] = -2;
                     if (p.k_prev > 0 && a_old != best) changed = true;
                     p.labels[row] = best;
-                    if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * W) : INFINITY;
+                    if (p.useed) p.useed[row] = (best >= 0 && mF < 3.0e38f) ? (mF + 0.5f * Wc) : INFINITY;
+                    if constexpr (LB) {
+                        // every centroid but the candidates scored at least `far`: as a distance (COSINE: chord), rounded
+                        // down; rows that are evaluated against all centroids learn nothing
+                        float lbn = 0.f;
+                        if (!all && far == far)                 // (several candidates: the refinement adds their exact distances)
+                            lbn = sqrtf(fmaxf(((p.metric == AKM_EUCLIDEAN) ? far : 2.f * far) * (far > 0.f ? 0.999999f : 1.000001f) + lbr.y, 0.f)) * 0.999999f;
+                        p.lb[row].x = fminf(lbr.x, lbn);
+                    }
                 }
                 const unsigned chm = __ballot_sync(0xffffffffu, changed);
                 if (chm && lane == 0) atomicAdd(p.counters + 2, __popc(chm));
@@ -863,7 +1023,8 @@ refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xla
                          const double *__restrict__ C, const double *__restrict__ clabel, int k,
                          const int32_t *__restrict__ wl_rows, const int32_t *__restrict__ wl_cand,
                          const int *__restrict__ counters, int wl_cap, int32_t *__restrict__ labels,
-                         int32_t *__restrict__ exact_rows, int *__restrict__ exact_count) {
+                         int32_t *__restrict__ exact_rows, int *__restrict__ exact_count,
+                         float *__restrict__ useed, float2 *__restrict__ lbv) {
     const int nwl = min(counters[0], wl_cap);             // blocks reserved past the capacity were never written
     int e = blockIdx.x * blockDim.x + threadIdx.x;
     const int stride = gridDim.x * blockDim.x;
@@ -947,7 +1108,18 @@ refine_candidates_kernel(const T *__restrict__ X, const double *__restrict__ xla
             const double tau = 8.0 * (double)(d + 16) * 2.220446049250313e-16 * rc * rc;
             if (i1 >= 0 && (v2 - v1) > tau) winner = i1;   // false for NaN
             else to_exact = true;
+            if (lbv != nullptr && !to_exact) {
+                // The exact values tighten what the next pass knows about this row: the seed (an upper bound of the
+                // winner's score, |c|^2 - 2 x.c or -x.c) and the second-nearest bound, which the search set from
+                // everything that was no candidate and which the losing candidates now lower.
+                const double s1 = (METRIC == AKM_EUCLIDEAN) ? (v1 - xl) : (v1 - 1.0);
+                useed[row] = __double2float_ru(s1 + tau + 1e-7 * fabs(s1));
+                const double d2 = fmax(((METRIC == AKM_EUCLIDEAN) ? 1.0 : 2.0) * (v2 - tau), 0.0);
+                const float lb2 = (v2 < DBL_MAX) ? __double2float_rd(sqrt(d2) * (1.0 - 1e-7)) : INFINITY;
+                lbv[row].x = fminf(lbv[row].x, lb2);
+            }
         }
+        if (to_exact && lbv != nullptr) lbv[row].x = 0.f;     // the exact list may pick any centroid
         if (to_exact) exact_rows[atomicAdd(exact_count, 1)] = row;
         else labels[row] = winner;
     }
@@ -1026,9 +1198,11 @@ struct TensorCtx {
     float2 *wm = nullptr; int64_t wm_cap = 0;
     // tile pruning: per-centroid distance to the nearest other centroid of every tile, per-group tile masks
     float *dmin = nullptr; size_t dmin_cap = 0;
-    uint32_t *gmask = nullptr; int64_t gmask_cap = 0;
+    uint32_t *gmask = nullptr; int2 *glist = nullptr; int64_t gmask_cap = 0;
     // seeds (only for the cached training partition)
     float *useed = nullptr; int64_t useed_cap = 0;
+    float2 *lb = nullptr; bool lb_valid = false;     // second-nearest bounds (same capacity as useed), see rowprep_kernel
+    float *top = nullptr;                            // shift_top2_kernel's three values
     double *Cprev = nullptr; float *sig_old = nullptr; int prev_cap = 0;
     int k_prev = 0; int64_t seed_rows = -1; uint64_t seed_x16 = 0;
     int chain = 0, step_prev = -1;
@@ -1045,6 +1219,7 @@ void tensor_free(akm_handle h) {
     cudaFree(c->c16); cudaFree(c->cn); cudaFree(c->pc); cudaFree(c->wl_rows); cudaFree(c->wl_cand);
     cudaFree(c->exact_rows); cudaFree(c->counters); cudaFree(c->absmax);
     cudaFree(c->useed); cudaFree(c->Cprev); cudaFree(c->sig_old); cudaFree(c->wm); cudaFree(c->dmin); cudaFree(c->gmask);
+    cudaFree(c->lb); cudaFree(c->top); cudaFree(c->glist);
     delete c;
     h->tc = nullptr;
 }
@@ -1123,14 +1298,20 @@ float *tensor_useed(akm_handle h) {
 
 void tensor_invalidate_seeds(akm_handle h) {
     TensorCtx *c = (TensorCtx *)h->tc;
-    if (c) { c->k_prev = 0; c->chain = 0; }
+    if (c) { c->k_prev = 0; c->chain = 0; c->lb_valid = false; }
+}
+
+// the rows were regrouped: labels and seeds moved with them, the second-nearest bounds are rebuilt by the next search
+void tensor_rows_permuted(akm_handle h) {
+    TensorCtx *c = (TensorCtx *)h->tc;
+    if (c) c->lb_valid = false;
 }
 
 // chain: 0 = stand-alone pass (no seeds), 1 = akm_step sequence (remap = compaction map of the last update),
 //        2 = sequence of host-buffer passes (identity map, only while k is unchanged)
-template <int KB, bool SPLIT>
+template <int KB, bool SPLIT, bool LB>
 static int launch_pair(akm_handle h, const CUtensorMap &mx, const CUtensorMap &mc, const SearchParams &sp, size_t smem, int grid) {
-    auto kern = search_pair_kernel<KB, SPLIT>;
+    auto kern = search_pair_kernel<KB, SPLIT, LB>;
     AKM_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)grid);
@@ -1183,9 +1364,12 @@ static int ensure_tensor_buffers(akm_handle h, TensorCtx *c, RowStore &rs, int k
         if (c->useed_cap < rs.n) {
             cudaFree(c->useed); c->useed = nullptr;
             AKM_CUDA(h, cudaMalloc((void **)&c->useed, sizeof(float) * (size_t)rs.n));
+            cudaFree(c->lb); c->lb = nullptr; c->lb_valid = false;
+            AKM_CUDA(h, cudaMalloc((void **)&c->lb, sizeof(float2) * (size_t)rs.n));
             c->useed_cap = rs.n;
             *fresh_seeds = true;
         }
+        if (!c->top) AKM_CUDA(h, cudaMalloc((void **)&c->top, 4 * sizeof(float)));
         if (c->prev_cap < k0) {
             cudaFree(c->Cprev); cudaFree(c->sig_old); c->Cprev = nullptr; c->sig_old = nullptr;
             AKM_CUDA(h, cudaMalloc((void **)&c->Cprev, sizeof(double) * (size_t)k0 * d));
@@ -1295,8 +1479,7 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     // group's rows share that centroid, i.e. on a cluster-ordered partition; a group that needs no tile at all (every
     // other centroid provably out of reach of every row) is skipped whole
     const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
-    // (the two-team kernel pairs row groups with accumulator buffers by parity, so it searches every group)
-    const bool prune = k_prev > 0 && h->tile_pruning && (ntiles > 1 || !split);
+    const bool prune = k_prev > 0 && h->tile_pruning;
     if (prune) {
         const size_t need = (size_t)k * ntiles;
         if (c->dmin_cap < need) {
@@ -1305,8 +1488,9 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
             c->dmin_cap = need;
         }
         if (c->gmask_cap < ngroups2) {
-            cudaFree(c->gmask); c->gmask = nullptr; c->gmask_cap = 0;
+            cudaFree(c->gmask); cudaFree(c->glist); c->gmask = nullptr; c->glist = nullptr; c->gmask_cap = 0;
             AKM_CUDA(h, cudaMalloc((void **)&c->gmask, sizeof(uint32_t) * (size_t)ngroups2));
+            AKM_CUDA(h, cudaMalloc((void **)&c->glist, sizeof(int2) * (size_t)ngroups2));
             c->gmask_cap = ngroups2;
         }
         AKM_CUDA(h, cudaMemsetAsync(c->gmask, 0, sizeof(uint32_t) * (size_t)ngroups2, h->stream));
@@ -1315,25 +1499,46 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
                                                                                              reinterpret_cast<unsigned *>(c->dmin));
         h->stats.kernel_launches++;
     }
-    rowprep_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,
+    // second-nearest bounds live with the seeds: only the cached training partition keeps them between passes
+    // and they pay only where groups can be skipped: pruning on, rows cluster-ordered
+    float2 *lbv = (train_rows && h->tile_pruning && rs.reordered) ? c->lb : nullptr;
+    if (!use_seed || !lbv) c->lb_valid = false;
+    if (lbv && k_prev > 0) {
+        shift_top2_kernel<<<1, 256, 0, h->stream>>>(c->sig_old, k_prev, c->top);
+        h->stats.kernel_launches++;
+    }
+    rowprep_kernel<<<h->num_sms * 16, ROWPREP_THREADS, 0, h->stream>>>(rs.n, d, h->metric, sp.eta, c->pc, rs.xerr, labels, c->useed,
                                                           c->sig_old, k_prev, (chain == 1) ? remap : nullptr, c->wm,
                                                           prune ? c->dmin : nullptr, ntiles, k, prune ? c->gmask : nullptr,
-                                                          split ? 0 : 1);
+                                                          lbv, c->lb_valid ? 1 : 0, c->top);
     h->stats.kernel_launches++;
+    sp.lb = lbv;
     AKM_CUDA(h, cudaGetLastError());
     sp.wm = c->wm;
     sp.dbg = h->epi_dbg;
-    sp.gmask = prune ? c->gmask : nullptr;
+    if (prune) {
+        group_list_kernel<<<std::max(1, std::min(h->num_sms, (ngroups2 + 255) / 256)), 256, 0, h->stream>>>(c->gmask, ngroups2, c->glist, c->counters + 5);
+        h->stats.kernel_launches++;
+        AKM_CUDA(h, cudaGetLastError());
+        sp.glist = c->glist; sp.glist_n = c->counters + 5;
+    }
+    // (counters are reused by the next pass only: the list stays readable for this pass's accumulation)
+    h->searched_valid = false;
+    if (prune && train_rows && labels == h->labels) { h->searched_list = c->glist; h->searched_n = c->counters + 5; h->searched_valid = true; }
     h->stats.tiles_total = (int64_t)ngroups2 * ntiles;
     const int pgrid = std::max(1, std::min(h->num_sms / 2, ngroups2)) * 2;
     int rc;
-    if (pair_stream) rc = launch_pair<0, false>(h, mapX, mapC, sp, pair_smem, pgrid);   // (streamed operands: no gain measured)
-    else if (KB == 1) rc = split ? launch_pair<1, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<1, false>(h, mapX, mapC, sp, pair_smem, pgrid);
-    else rc = split ? launch_pair<2, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2, false>(h, mapX, mapC, sp, pair_smem, pgrid);
+    const bool lbk = sp.lb != nullptr;
+    if (pair_stream) rc = lbk ? launch_pair<0, false, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<0, false, false>(h, mapX, mapC, sp, pair_smem, pgrid);
+    else if (split && KB == 1) rc = lbk ? launch_pair<1, true, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<1, true, false>(h, mapX, mapC, sp, pair_smem, pgrid);
+    else if (split) rc = lbk ? launch_pair<2, true, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2, true, false>(h, mapX, mapC, sp, pair_smem, pgrid);
+    else if (KB == 1) rc = lbk ? launch_pair<1, false, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<1, false, false>(h, mapX, mapC, sp, pair_smem, pgrid);
+    else rc = lbk ? launch_pair<2, false, true>(h, mapX, mapC, sp, pair_smem, pgrid) : launch_pair<2, false, false>(h, mapX, mapC, sp, pair_smem, pgrid);
     AKM_TRY(rc);
     if (train_rows) {
         AKM_CUDA(h, cudaMemcpyAsync(c->Cprev, C, sizeof(double) * (size_t)k * d, cudaMemcpyDeviceToDevice, h->stream));
         c->k_prev = k; c->chain = chain; c->step_prev = h->step; c->seed_rows = rs.n; c->seed_x16 = rs.x16_gen;
+        c->lb_valid = lbv != nullptr;
     } else if (labels == h->labels) {
         c->k_prev = 0;                       // somebody else's labels now live in the buffer the seeds refer to
     }
@@ -1343,7 +1548,8 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     const int rblocks = h->num_sms * 32;
 #define REFINE(T, PTR, M)                                                                                         \
     refine_candidates_kernel<T, M><<<rblocks, 128, 0, h->stream>>>(PTR, rs.xlabel, d, C, clabel, k, c->wl_rows, \
-                                                                   c->wl_cand, c->counters, (int)c->wl_slots, labels, c->exact_rows, c->counters + 1)
+                                                                   c->wl_cand, c->counters, (int)c->wl_slots, labels, c->exact_rows, c->counters + 1, \
+                                                                   c->useed, sp.lb)
     if (h->metric == AKM_EUCLIDEAN) { if (rs.store == 4) REFINE(float, rs.x32, AKM_EUCLIDEAN); else REFINE(double, rs.x64, AKM_EUCLIDEAN); }
     else { if (rs.store == 4) REFINE(float, rs.x32, AKM_COSINE); else REFINE(double, rs.x64, AKM_COSINE); }
 #undef REFINE

@@ -255,7 +255,10 @@ def test_tile_pruning_changes_nothing_but_the_work(metric):
 
 @pytest.mark.parametrize("metric,k,nb,centred", [(native.EUCLIDEAN, 700, 700, True), (native.EUCLIDEAN, 700, 700, False),
                                                  (native.EUCLIDEAN, 200, 120, False), (native.COSINE, 300, 300, True),
-                                                 (native.EUCLIDEAN, 520, 260, False)])
+                                                 (native.EUCLIDEAN, 520, 260, False),
+                                                 # k <= 128: the two-team kernel
+                                                 (native.EUCLIDEAN, 100, 100, True), (native.COSINE, 90, 60, False),
+                                                 (native.EUCLIDEAN, 128, 300, False)])
 def test_whole_group_skipping_pass_by_pass(metric, k, nb, centred):
     # Row groups whose rows provably keep their centroid are not searched at all (no tile of theirs is evaluated).
     # Every pass of a long run must still give the labels and sums of the exact engine; k < nb leaves clusters that
