@@ -377,11 +377,11 @@ centroid_tile_dist_kernel(const double *__restrict__ C, int k, int d, int ntiles
     const int j = j0 + tx;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const int a = a0 + ty + 8 * i;
-        if (a < k && j < k && a != j && acc[i] == acc[i]) {
-            const float f = __double2float_rd(acc[i] * (1.0 - 1e-9));
-            atomicMin(dmin2 + (size_t)a * ntiles + j / 256, __float_as_uint(fmaxf(f, 0.f)));
-        }
+        const int a = a0 + ty + 8 * i;                     // the same for the whole warp; its 32 j share one tile
+        unsigned bits = 0x7F7F7F7Fu;                       // the table's preset: "no other centroid in this tile"
+        if (a < k && j < k && a != j && acc[i] == acc[i]) bits = __float_as_uint(fmaxf(__double2float_rd(acc[i] * (1.0 - 1e-9)), 0.f));
+        bits = __reduce_min_sync(0xffffffffu, bits);       // non-negative floats order like their bit patterns
+        if (tx == 0 && a < k && bits != 0x7F7F7F7Fu) atomicMin(dmin2 + (size_t)a * ntiles + j0 / 256, bits);
     }
 }
 
@@ -1370,6 +1370,20 @@ static int ensure_tensor_buffers(akm_handle h, TensorCtx *c, RowStore &rs, int k
             *fresh_seeds = true;
         }
         if (!c->top) AKM_CUDA(h, cudaMalloc((void **)&c->top, 4 * sizeof(float)));
+        // pruning: tile distance table (k <= k0 centroids x their tiles) and the per-group masks / list
+        const size_t dneed = (size_t)k0 * (size_t)(kpad / PAIR_N);
+        if (c->dmin_cap < dneed) {
+            cudaFree(c->dmin); c->dmin = nullptr; c->dmin_cap = 0;
+            AKM_CUDA(h, cudaMalloc((void **)&c->dmin, sizeof(float) * dneed));
+            c->dmin_cap = dneed;
+        }
+        const int64_t gneed = ceil_div64(rs.n, 2 * TILE_M);
+        if (c->gmask_cap < gneed) {
+            cudaFree(c->gmask); cudaFree(c->glist); c->gmask = nullptr; c->glist = nullptr; c->gmask_cap = 0;
+            AKM_CUDA(h, cudaMalloc((void **)&c->gmask, sizeof(uint32_t) * (size_t)gneed));
+            AKM_CUDA(h, cudaMalloc((void **)&c->glist, sizeof(int2) * (size_t)gneed));
+            c->gmask_cap = gneed;
+        }
         if (c->prev_cap < k0) {
             cudaFree(c->Cprev); cudaFree(c->sig_old); c->Cprev = nullptr; c->sig_old = nullptr;
             AKM_CUDA(h, cudaMalloc((void **)&c->Cprev, sizeof(double) * (size_t)k0 * d));
@@ -1481,18 +1495,8 @@ int tensor_assign(akm_handle h, RowStore &rs, const double *C, const double *cla
     const int ngroups2 = (int)ceil_div64(rs.n, 2 * TILE_M);
     const bool prune = k_prev > 0 && h->tile_pruning;
     if (prune) {
-        const size_t need = (size_t)k * ntiles;
-        if (c->dmin_cap < need) {
-            cudaFree(c->dmin); c->dmin = nullptr; c->dmin_cap = 0;
-            AKM_CUDA(h, cudaMalloc((void **)&c->dmin, sizeof(float) * need));
-            c->dmin_cap = need;
-        }
-        if (c->gmask_cap < ngroups2) {
-            cudaFree(c->gmask); cudaFree(c->glist); c->gmask = nullptr; c->glist = nullptr; c->gmask_cap = 0;
-            AKM_CUDA(h, cudaMalloc((void **)&c->gmask, sizeof(uint32_t) * (size_t)ngroups2));
-            AKM_CUDA(h, cudaMalloc((void **)&c->glist, sizeof(int2) * (size_t)ngroups2));
-            c->gmask_cap = ngroups2;
-        }
+        const size_t need = (size_t)k * ntiles;           // (buffers: ensure_tensor_buffers; pruning needs seeds, so train_rows)
+        if (c->dmin_cap < need || c->gmask_cap < ngroups2) return akm_fail(h, AKM_ERR_STATE, "pruning buffers were not reserved");
         AKM_CUDA(h, cudaMemsetAsync(c->gmask, 0, sizeof(uint32_t) * (size_t)ngroups2, h->stream));
         AKM_CUDA(h, cudaMemsetAsync(c->dmin, 0x7F, sizeof(float) * need, h->stream));     // 3.4e38: "no other centroid in this tile"
         centroid_tile_dist_kernel<<<dim3((k + 31) / 32, (k + 31) / 32), 256, 0, h->stream>>>(C, k, d, ntiles,
