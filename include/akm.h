@@ -260,7 +260,7 @@ typedef struct {
     int32_t storage_bytes;    /* 4 or 8 */
     int64_t rows_exact_all;   /* subset of rows_refined that was evaluated against all k centroids */
     int64_t tiles_total;      /* tensor engine: (256-row groups) x (256-centroid tiles) of the last pass */
-    int64_t tiles_computed;   /* ... of which were evaluated; the rest were pruned by the triangle inequality */
+    int64_t tiles_computed;   /* ... of which were evaluated; the rest were ruled out by bounds ("tile_pruning") */
     int64_t rows_moved;       /* rows whose label differs from the previous pass's (-1: no previous pass to compare with) */
     int32_t accumulate_mode;  /* 0: the accumulator was refilled from every row, 1: only the moved rows were applied */
     int32_t reserved0;
@@ -275,12 +275,15 @@ int akm_get_stats(akm_handle h, akm_stats *out);
  *                       the first pass come from the initial centroids and most of them move again).
  *   "tile_pruning"      (default 1) from the second pass of a training sequence on, the tensor engine skips every
  *                       (256-row group, 256-centroid tile) pair that the triangle inequality proves free of the
- *                       argmin and of every near-tie candidate (bounds from the previous pass;
- *                       akm_stats.tiles_computed / tiles_total reports how much was evaluated); 0 evaluates all.
+ *                       argmin and of every near-tie candidate, and -- on a partition that is kept grouped by
+ *                       cluster -- every row group whose rows provably keep their centroid (a lower bound of each
+ *                       row's distance to its runner-up is carried from pass to pass).  All of it is bounds from
+ *                       the previous pass; akm_stats.tiles_computed / tiles_total reports how much was evaluated;
+ *                       0 evaluates every pair.
  *   "delta_accumulate"  (default 1) once few rows change cluster per pass, the per-cluster sums are kept between
  *                       supersteps and only the rows whose label changed are moved (counts stay exact, sums pick
  *                       up one fp64 rounding per moved value; a full pass runs whenever more than 1/16 of the rows
- *                       moved in the previous pass, every 16 passes, and after any call that rewrites the labels);
+ *                       moved in the previous pass, every 64 passes, and after any call that rewrites the labels);
  *                       0 refills the accumulator from every row in every superstep like the reference does. */
 int akm_set_option(akm_handle h, const char *name, double value);
 

@@ -467,3 +467,39 @@ def test_full_size_baseline_configs_tensor_engine_equals_exact_engine(cfg, n, d,
     kk = e["ks"][1]
     np.testing.assert_allclose(t["model"]["C"][:kk], e["model"]["C"][:kk], rtol=1e-9, atol=1e-12)
     assert (t["model"]["weights"] == e["model"]["weights"]).all()
+
+
+@pytest.mark.parametrize("metric,d,k", [(native.EUCLIDEAN, 2, 300), (native.EUCLIDEAN, 3, 700), (native.COSINE, 3, 260),
+                                        (native.EUCLIDEAN, 5, 100)])
+def test_bounds_on_unstructured_low_dimensional_data(metric, d, k):
+    # Uniform points: no cluster structure, every row has many centroids within 1.5 x the distance of its own (the
+    # recording window of the second-nearest bound fills up, rings overflow), margins are tiny and centroids keep
+    # moving for many passes.  Labels, k and objective must equal the exact engine's after every pass.
+    n, iters = 70000, 16
+    rng = np.random.default_rng(1234 + d + k)
+    X = rng.uniform(-1.0, 1.0, size=(n, d))
+    if metric == native.COSINE:
+        X += 2.0                                                   # keep away from the origin
+    X = X.astype(np.float32).astype(np.float64)
+    C0 = X[rng.choice(n, k, replace=False)].copy()
+    hs = []
+    for engine in (native.ENGINE_TENSOR, native.ENGINE_EXACT):
+        h = native.Handle(d, metric)
+        h.set_engine(engine)
+        h.set_option("reorder_min_rows", 1)
+        h.upload_rows(X)
+        h.set_centroids(C0)
+        hs.append(h)
+    try:
+        for it in range(iters):
+            ra, rb = hs[0].step(0.0), hs[1].step(0.0)
+            la, lb = hs[0].get_labels(), hs[1].get_labels()
+            assert (la == lb).all(), "pass %d: %d labels differ" % (it, int((la != lb).sum()))
+            assert ra[1] == rb[1]
+            np.testing.assert_allclose(ra[2], rb[2], rtol=1e-9)
+        ma, mb = hs[0].get_model(), hs[1].get_model()
+        assert (ma["weights"] == mb["weights"]).all()
+        np.testing.assert_allclose(ma["C"][: ma["k"]], mb["C"][: mb["k"]], rtol=1e-10, atol=1e-12)
+    finally:
+        for h in hs:
+            h.close()
