@@ -19,7 +19,7 @@ KMeansAssignCluster -> AllReduce -> KMeansUpdateCentroids -> KMeansIterTerminati
               Alink caches it on the JVM heap, BaseComQueue.java:497-527; its upload is reported as `upload`.)
   parity    : the CPU leg's rows (the first n_cpu rows of the same data) evaluated from C0 by the oracle and by the
               GPU: labels, k x (d+1) sums and objective compared in the line.
-  configs   : BASELINE configs 3 and 5 (and config 5's KMeansPredictBatchOp pass) run time-boxed after the headline,
+  configs   : BASELINE configs 2, 3 and 5 (and config 5's KMeansPredictBatchOp pass) run time-boxed after the headline,
               each with its own roofline object (HBM-bound shapes against the HBM roof).
 --impl reference times the CPU restatement of Alink's Java arithmetic (oracle/, all host threads, the
 duplicated distance evaluation of KMeansUtil.java:73,124 included) -- the JVM itself cannot run here.
@@ -352,7 +352,7 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-configs", action="store_true", help="skip the BASELINE config 3 / 5 sub-lines")
+    ap.add_argument("--no-configs", action="store_true", help="skip the BASELINE config 2 / 3 / 5 sub-lines")
     ap.add_argument("--upload-gb", type=float, default=8.0, help="host doubles pushed through akm_upload_rows for `upload`")
     ap.add_argument("--max-iter", type=int, default=10, help="steps of the from_init leg (SURVEY 8d: maxIter = 10)")
     args = ap.parse_args()
@@ -670,7 +670,8 @@ def main():
     configs = None
     if rank == 0 and world == 1 and not args.no_configs and (N, d, k, args.metric) == (100_000_000, 128, 1000, 0):
         configs = []
-        for name, (n_c, d_c, k_c, met) in (("cfg3", (10_000_000, 64, 100, 0)), ("cfg5", (20_000_000, 256, 500, 1))):
+        for name, (n_c, d_c, k_c, met) in (("cfg2", (1_000_000, 784, 10, 0)), ("cfg3", (10_000_000, 64, 100, 0)),
+                                           ("cfg5", (20_000_000, 256, 500, 1))):
             try:
                 configs.append(run_config(native, torch, stream, pk, name, n_c, d_c, k_c, met, args.max_iter))
             except Exception as e:                            # a sub-line must never cost the headline
