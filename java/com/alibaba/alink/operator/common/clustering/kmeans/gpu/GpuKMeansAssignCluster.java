@@ -54,8 +54,21 @@ public class GpuKMeansAssignCluster extends ComputeFunction {
             double[] buf = new double[chunk * vectorSize];
             int filled = 0;
             for (FastDistanceVectorData sample : trainData) {
-                double[] v = ((com.alibaba.alink.common.linalg.DenseVector) sample.getVector()).getData();
-                System.arraycopy(v, 0, buf, filled * vectorSize, vectorSize);
+                com.alibaba.alink.common.linalg.Vector vec = sample.getVector();
+                if (vec instanceof com.alibaba.alink.common.linalg.DenseVector) {
+                    System.arraycopy(((com.alibaba.alink.common.linalg.DenseVector) vec).getData(), 0, buf,
+                        filled * vectorSize, vectorSize);
+                } else {
+                    // a prepared SparseVector (already normalised under COSINE) is expanded into the 64 MB chunk only;
+                    // raw sparse tables can go through AkmNative.uploadRowsCsr instead (INTEGRATION.md)
+                    com.alibaba.alink.common.linalg.SparseVector sv = (com.alibaba.alink.common.linalg.SparseVector) vec;
+                    java.util.Arrays.fill(buf, filled * vectorSize, (filled + 1) * vectorSize, 0.0);
+                    int[] idx = sv.getIndices();
+                    double[] val = sv.getValues();
+                    for (int i = 0; i < idx.length; i++) {
+                        buf[filled * vectorSize + idx[i]] = val[i];
+                    }
+                }
                 if (++filled == chunk) {
                     AkmNative.check(handle, AkmNative.uploadRowsPrepared(handle, buf, filled));
                     filled = 0;
