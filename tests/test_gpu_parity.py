@@ -503,3 +503,36 @@ def test_bounds_on_unstructured_low_dimensional_data(metric, d, k):
     finally:
         for h in hs:
             h.close()
+
+
+def test_bounds_stay_valid_over_a_long_run():
+    # 70 passes: second-nearest bounds decay and are refreshed many times, the incremental accumulation goes through
+    # its periodic full pass (every 64), clusters that split blobs keep exchanging rows.  Every pass is compared.
+    n, d, k, nb, iters = 300000, 48, 600, 420, 70
+    X = blobs(n, d, nb, seed=11, spread=6.0)
+    C0 = X[np.random.default_rng(12).choice(n, k, replace=False)].copy()
+    hs = []
+    for engine in (native.ENGINE_TENSOR, native.ENGINE_EXACT):
+        h = native.Handle(d, native.EUCLIDEAN)
+        h.set_engine(engine)
+        h.upload_rows(X)                                      # above reorder_min_rows: regrouped like a big partition
+        h.set_centroids(C0)
+        hs.append(h)
+    skipped = 0
+    try:
+        for it in range(iters):
+            ra, rb = hs[0].step(0.0), hs[1].step(0.0)
+            assert ra[1] == rb[1], "pass %d: k %d vs %d" % (it, ra[1], rb[1])
+            np.testing.assert_allclose(ra[2], rb[2], rtol=1e-9, err_msg="pass %d" % it)
+            st = hs[0].stats()
+            skipped += st["tiles_computed"] * 3 < st["tiles_total"]
+            if it % 10 == 9 or it == iters - 1:
+                la, lb = hs[0].get_labels(), hs[1].get_labels()
+                assert (la == lb).all(), "pass %d: %d labels differ" % (it, int((la != lb).sum()))
+        ma, mb = hs[0].get_model(), hs[1].get_model()
+        assert (ma["weights"] == mb["weights"]).all()
+        np.testing.assert_allclose(ma["C"][: ma["k"]], mb["C"][: mb["k"]], rtol=1e-10, atol=1e-12)
+    finally:
+        for h in hs:
+            h.close()
+    assert skipped > 20                                       # the bounds did carry most of the run
