@@ -693,9 +693,12 @@ def main():
             "objective_last": objective, "k_last": kk, "generate_s": gen_s, "upload": upload,
             "ranks_agree": ranks_agree, "configs": configs, "source_hash": source_hash(),
             "steady_state_note": "value = steps %d..%d of the run (after from_init and %d warm-up steps, epsilon = 0): labels have "
-                                 "mostly stopped moving, which is when seeds, tile pruning and delta accumulation are at their "
-                                 "best; from_init is the run a user gets" % (args.max_iter + args.warmup + 1,
-                                                                              args.max_iter + args.warmup + args.steps, args.warmup),
+                                 "mostly stopped moving, which is when the exact bounds (seeds, tile lemma, second-nearest "
+                                 "bounds: roofline.steady_state.tiles_evaluated_frac of the tiles are searched) and delta "
+                                 "accumulation are at their best -- same results as an exhaustive step, less work; "
+                                 "from_init is the run a user gets (maxIter = 10 from the initial centroids), "
+                                 "full_evaluation the step with nothing skipped, and roofline is taken on the latter"
+                                 % (args.max_iter + args.warmup + 1, args.max_iter + args.warmup + args.steps, args.warmup),
             "engine": {native.ENGINE_TENSOR: "tensor", native.ENGINE_EXACT: "exact"}.get(engine_used, "?"),
         }
         emit(out)
