@@ -168,3 +168,41 @@ def test_world_size_2_gloo_sharded_training_matches_single_process(tmp_path):
     assert (w[0] == ref["weights"]).all()
     p = [np.load(tmp_path / ("p%d.npy" % r)) for r in range(2)]
     assert (p[0] == p[1]).all() and p[0].shape == (4, 5)
+
+
+def test_recording_window_encoding_properties():
+    """The search kernel's per-row window slot carries W' = W * 2^e with e in the five low mantissa bits
+    (kernels_tensor.cu: plain_window / encode_window / decode_window).  A numpy model of the same bit operations:
+    the decoded certifying window is never below W (and at most 63 ulps above), the recording window never below it
+    and within a factor of two of its target."""
+    rng = np.random.default_rng(3)
+    W = np.exp(rng.uniform(np.log(1e-6), np.log(1e6), size=20000)).astype(np.float32)
+    target = (W * np.exp(rng.uniform(0.0, np.log(3e5), size=W.size))).astype(np.float32)
+
+    def bits(x):
+        return x.view(np.uint32)
+
+    def plain(w):
+        return ((bits(w) + np.uint32(31)) & np.uint32(0xFFFFFFE0)).view(np.float32)
+
+    def encode(w, t):
+        _, e = np.frexp((t / w).astype(np.float32))
+        e = np.clip(e - 1, 0, 24).astype(np.int32)
+        scaled = np.ldexp(w, e).astype(np.float32)
+        enc = (((bits(scaled) + np.uint32(31)) & np.uint32(0xFFFFFFE0)) | e.astype(np.uint32)).view(np.float32)
+        return np.where(t > w, enc, plain(w)), e
+
+    def decode(wenc):
+        e = (bits(wenc) & np.uint32(31)).astype(np.int32)
+        return (wenc * np.ldexp(np.float32(1.0), -e)).astype(np.float32), e
+
+    p = plain(W)
+    dp, e0 = decode(p)
+    assert (e0 == 0).all() and (dp == p).all() and (p >= W).all() and (p <= W * np.float32(1 + 2.0 ** -17)).all()
+    enc, e = encode(W, target)
+    dec, e_back = decode(enc)
+    assert (e_back == e).all()
+    assert (dec >= W).all() and (dec <= W * np.float32(1 + 2.0 ** -17)).all()        # certifies with at least W
+    assert (enc >= dec).all()                                                          # records at least what it certifies
+    assert (enc <= target * np.float32(1 + 2.0 ** -17)).all()
+    assert ((enc > target * np.float32(0.5)) | (e == 24)).all()                        # within a factor two of the target
