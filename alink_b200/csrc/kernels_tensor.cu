@@ -100,6 +100,7 @@ struct PassConst {
     float score_scale; // -2 * 2^-(sx+sc) (EUCLIDEAN) or -2^-(sx+sc) (COSINE)
     int sc;            // centroid scale exponent
     int bad;           // non-finite centroid: tensor search disabled for this pass
+    float c_dev;       // max_j | ||c_j|| - 1 | (rounded up): the COSINE bounds are chords between UNIT vectors
 };
 
 struct SearchParams {
@@ -155,8 +156,8 @@ struct SearchParams {
 // every centroid other than its winner: the epilogue records scores up to a window W' >= W above the running minimum
 // (only those within W are candidates; the others just bound lb from above), so whatever was not recorded lies more
 // than W' above the minimum.  In the next pass every other centroid is at least lb - (largest movement of another
-// centroid) away, the own one at most ub: when that gap passes the same margin as the tile lemma, the row needs no
-// tile at all.  W' = W * 2^e travels in the slot of W with e in the five low mantissa bits (encode_window), so the
+// centroid) away, the own one at most ub: when the gap is positive by more than Java's own rounding of the two
+// distances, the row needs no tile at all.  W' = W * 2^e travels in the slot of W with e in the five low mantissa bits (encode_window), so the
 // search kernel's per-row state does not grow.
 // a window without an exponent must decode to itself: its low bits are cleared (rounding up)
 __device__ __forceinline__ float plain_window(float W) {
@@ -210,6 +211,9 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
                float2 *__restrict__ lbv, int lb_valid, const float *__restrict__ top) {
     const float c16_max = pc->c16_max, dc_max = pc->dc_max, c_max = pc->c_max;
     const bool bad = pc->bad != 0;
+    // Alink's COSINE centroid buffers hold unit vectors (updateLabel normalises them); a host that passes anything
+    // else gets Java's arithmetic on it, but no pruning: lemma and bounds are chord geometry on the unit sphere
+    const bool geometry_ok = metric == AKM_EUCLIDEAN || pc->c_dev < 1e-12f;
     // movement of the fastest and second fastest surviving centroid (a row excludes its own)
     const float top1 = (lbv && k_prev > 0) ? top[0] : 0.f, top2 = (lbv && k_prev > 0) ? top[1] : 0.f;
     const int top_a = (lbv && k_prev > 0) ? __float_as_int(top[2]) : -1;
@@ -249,7 +253,8 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
             float Wenc = plain_window(W);
             W = decode_window(Wenc);                        // the value the search certifies with
             // distance^2 (COSINE: chord^2) >= alpha * score + r2lo for a score that is short of the truth by at most W / 2
-            const float r2lo = (metric == AKM_EUCLIDEAN) ? (r * r * 0.999998f - 0.5f * W) : (2.f - W);
+            // (-INF when the centroids of this pass are not unit vectors under COSINE: the epilogue's bound then comes out 0)
+            const float r2lo = (metric == AKM_EUCLIDEAN) ? (r * r * 0.999998f - 0.5f * W) : (geometry_ok ? (2.f - W) : -INFINITY);
             float lb_out = INFINITY;
             uint32_t need = all_tiles;
             const int a = a2[hh];
@@ -271,7 +276,7 @@ rowprep_kernel(int64_t n, int d, int metric, float eta, const PassConst *__restr
                 if (u == u) m0 = u;                                 // NaN: no seed
                 if (!(ut == ut)) ut = INFINITY;
                 const int ja = remap ? remap[a] : a;                // this pass's numbering (-1: cluster dropped)
-                if (dmin != nullptr && ja >= 0 && ja < k && u == u && ub < 3.0e37f && W == W) {
+                if (dmin != nullptr && geometry_ok && ja >= 0 && ja < k && u == u && ub < 3.0e37f && W == W) {
                     const float rhs = ((metric == AKM_EUCLIDEAN) ? 2.f : 4.f) * W * 1.01f + 1e-30f;
                     // (dmin of the row's own tile leaves c_a itself out: when that tile passes too, no other centroid
                     //  can take the row)
@@ -990,6 +995,7 @@ c16_rows_kernel(const double *__restrict__ C, const double *__restrict__ clabel,
                 atomicMax(reinterpret_cast<unsigned *>(&pc->c_max), __float_as_uint(__double2float_ru(sqrt(s2) * (1.0 + 1e-9))));
                 atomicMax(reinterpret_cast<unsigned *>(&pc->dc_max), __float_as_uint(__double2float_ru(sqrt(e2) * (1.0 + 1e-9))));
                 atomicMax(reinterpret_cast<unsigned *>(&pc->c16_max), __float_as_uint(__double2float_ru(sqrt(t2) * (1.0 + 1e-9))));
+                atomicMax(reinterpret_cast<unsigned *>(&pc->c_dev), __float_as_uint(__double2float_ru(fabs(sqrt(s2) - 1.0))));
             } else {
                 cn[j] = PAD_SCORE;
             }

@@ -151,7 +151,9 @@ int akm_num_rows(akm_handle h, int64_t *n_out, int *bytes_per_value_out);
  * FastDistance.calc(vector, matrix) (EuclideanDistance.java:109-116, CosineDistance.java:107-110)
  * and getMinPointIndex (KMeansUtil.java:162-173).
  *   centroids  k0 x d, as stored in FastDistanceMatrixData.vectors (already label-updated:
- *              for COSINE the rows are unit vectors; stale rows >= k are zero)
+ *              for COSINE the rows are unit vectors; stale rows >= k are zero).  COSINE rows that are NOT unit
+ *              vectors get CosineDistance.calc's arithmetic on them as they are (1 - x.c), like in Java; the
+ *              library then evaluates every centroid for every row in that pass (its bounds are unit-sphere geometry)
  *   k0         number of rows of the buffer (= the init matrix's numCols, KMeansPreallocateCentroid.java:22-39)
  *   k          current cluster count (context "k"), only the first k centroids are candidates
  *   sum_out    double[k0*(d+1)], fully overwritten ("Arrays.fill(sumMatrixData, 0.0)" then accumulate)

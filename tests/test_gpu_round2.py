@@ -336,3 +336,39 @@ def test_every_row_on_the_worklist():
         st = h.stats()
     assert (labels == 0).all()                                # first minimum
     assert st["rows_refined"] == n and s.reshape(k0, d + 1)[0, d] == n
+
+
+@pytest.mark.parametrize("metric", [native.EUCLIDEAN, native.COSINE])
+def test_bounds_hold_for_whatever_centroids_the_host_passes_next(metric):
+    # Host-buffer supersteps keep seeds and second-nearest bounds between calls; they are bounds on how far the
+    # centroids the caller passes NEXT lie from the previous ones, so centroids that are not the ones the library
+    # returned (perturbed, permuted, partly replaced) must give the exhaustive answer as well.
+    n, d, k = 60000, 20, 400
+    rng = np.random.default_rng(21)
+    centers = rng.uniform(-8, 8, size=(k, d))
+    X = (centers[rng.integers(0, k, size=n)] + rng.normal(size=(n, d))).astype(np.float32).astype(np.float64)
+    C = X[rng.choice(n, k, replace=False)].copy()
+    with native.Handle(d, metric) as ht, native.Handle(d, metric) as he:
+        ht.set_engine(native.ENGINE_TENSOR); he.set_engine(native.ENGINE_EXACT)
+        ht.set_option("reorder_min_rows", 1)
+        ht.upload_rows(X); he.upload_rows(X)
+        k_cur = k
+        for it in range(12):
+            rt = ht.superstep(C, k=k_cur, step_no=it + 1, tol=0.0, want_sum=True)
+            re_ = he.superstep(C, k=k_cur, step_no=it + 1, tol=0.0, want_sum=True)
+            assert rt["k"] == re_["k"], "pass %d" % it
+            k_cur = re_["k"]                                             # (the big move at the end empties a few clusters)
+            cnt_t = rt["sum"].reshape(k, d + 1)[:, d]
+            cnt_e = re_["sum"].reshape(k, d + 1)[:, d]
+            assert (cnt_t == cnt_e).all(), "pass %d: counts differ in %d clusters" % (it, int((cnt_t != cnt_e).sum()))
+            np.testing.assert_allclose(rt["sum"], re_["sum"], rtol=1e-11, atol=1e-9)
+            np.testing.assert_allclose(rt["objective"], re_["objective"], rtol=1e-9)
+            C = re_["C"].copy()
+            if it == 4:
+                C += rng.normal(scale=0.05, size=C.shape)              # a small nudge: most bounds survive it
+            elif it == 6:
+                C = C[rng.permutation(k)]                                # every label changes, nothing else does
+            elif it == 8:
+                C[::7] = X[rng.choice(n, C[::7].shape[0], replace=False)]  # some centroids jump anywhere
+            elif it == 9:
+                C += rng.normal(scale=1.5, size=C.shape)               # a big move of all of them
